@@ -1,0 +1,689 @@
+// capdec.cu - C ABI + host runtime of the B200-native caption decode engine.
+// See include/capdec.h for the boundary and DESIGN.md for the data layout.
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+
+#include "engine.h"
+#include "epilogue.cuh"
+#include "gemm_simt.cuh"
+#include "gemm_umma.cuh"
+#include "attention.cuh"
+#include "pointwise.cuh"
+
+using namespace capdec;
+
+// ------------------------------------------------------------------ errors
+static std::string g_create_error;
+
+static int fail(capdec_handle h, int code, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  if (h) h->err = buf; else g_create_error = buf;
+  return code;
+}
+
+#define CUDA_TRY(h, expr)                                                                     \
+  do {                                                                                        \
+    cudaError_t e_ = (expr);                                                                  \
+    if (e_ != cudaSuccess)                                                                    \
+      return fail(h, CAPDEC_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e_), \
+                  __FILE__, __LINE__);                                                        \
+  } while (0)
+
+// ------------------------------------------------------------------ TMA tensor maps
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_tiled_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  });
+  return fn;
+}
+
+// bf16 [rows, cols] row-major matrix; box = box_rows x 64 columns, 128B swizzle (one UMMA atom row).
+static int make_map(capdec_handle h, CUtensorMap* m, const void* ptr, int rows, int cols, int box_rows) {
+  EncodeTiledFn fn = encode_tiled_fn();
+  if (!fn) return fail(h, CAPDEC_ERR_CUDA, "cuTensorMapEncodeTiled entry point unavailable");
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)cols * 2};
+  cuuint32_t box[2] = {(cuuint32_t)kUmmaBK, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(h, CAPDEC_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d) rows=%d cols=%d", (int)r, rows, cols);
+  return 0;
+}
+
+static int make_weight_maps(capdec_handle h, WeightMaps* wm, const void* ptr, int n, int k) {
+  const int bns[3] = {32, 64, 128};
+  for (int i = 0; i < 3; ++i) {
+    int rc = make_map(h, &wm->bn[i], ptr, n, k, bns[i]);
+    if (rc) return rc;
+  }
+  return 0;
+}
+
+// ------------------------------------------------------------------ GEMM dispatch
+static const int kMaxDynSmem = 227 * 1024;
+
+template <int BN, typename Epi>
+static int launch_umma_bn(capdec_handle h, cudaStream_t s, const CUtensorMap& ta, const CUtensorMap& tw, int M, int N,
+                          int K, const Epi& epi, const DecState* st) {
+  auto kern = gemm_umma_kernel<BN, Epi>;  // dynamic-smem limit raised once in configure_umma_kernels()
+  const int num_kb = K / kUmmaBK;
+  int stages = std::min(num_kb, 8);
+  while (umma_smem_bytes(BN, stages) > kMaxDynSmem) --stages;
+  dim3 grid(N / BN, (M + kUmmaBM - 1) / kUmmaBM);
+  kern<<<grid, kUmmaThreads, umma_smem_bytes(BN, stages), s>>>(ta, tw, M, N, K, stages, epi, st);
+  CUDA_TRY(h, cudaGetLastError());
+  h->launches_this_enqueue++;
+  return 0;
+}
+
+// Pick the widest N tile that still yields at least one CTA per SM (the step GEMMs have few
+// M tiles: M = number of live sequences).
+template <typename Epi>
+static int launch_umma(capdec_handle h, cudaStream_t s, const CUtensorMap& ta, const WeightMaps& wm, int M, int N, int K,
+                       const Epi& epi, const DecState* st) {
+  if (K % kUmmaBK != 0 || N % 128 != 0) return fail(h, CAPDEC_ERR_INVALID, "tcgen05 GEMM needs K%%64==0, N%%128==0 (N=%d K=%d)", N, K);
+  const int tiles_m = (M + kUmmaBM - 1) / kUmmaBM;
+  if (tiles_m * (N / 128) >= 148) return launch_umma_bn<128, Epi>(h, s, ta, wm.bn[2], M, N, K, epi, st);
+  if (tiles_m * (N / 64) >= 148) return launch_umma_bn<64, Epi>(h, s, ta, wm.bn[1], M, N, K, epi, st);
+  return launch_umma_bn<32, Epi>(h, s, ta, wm.bn[0], M, N, K, epi, st);
+}
+
+template <typename TA, typename TW, typename Epi>
+static int launch_simt(capdec_handle h, cudaStream_t s, const TA* A, int lda, const TW* W, int ldw, int M, int N, int K,
+                       const Epi& epi, const DecState* st) {
+  if (K % kSimtBK != 0 || N % 4 != 0) return fail(h, CAPDEC_ERR_INVALID, "GEMM needs K%%16==0, N%%4==0 (N=%d K=%d)", N, K);
+  dim3 grid((N + kSimtBN - 1) / kSimtBN, (M + kSimtBM - 1) / kSimtBM);
+  gemm_simt_kernel<TA, TW, Epi><<<grid, kSimtThreads, 0, s>>>(A, lda, W, ldw, M, N, K, epi, st);
+  CUDA_TRY(h, cudaGetLastError());
+  h->launches_this_enqueue++;
+  return 0;
+}
+
+template <typename Epi>
+static cudaError_t configure_umma_epi() {
+  cudaError_t e = cudaFuncSetAttribute(gemm_umma_kernel<32, Epi>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(gemm_umma_kernel<64, Epi>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(gemm_umma_kernel<128, Epi>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
+  return e;
+}
+static cudaError_t configure_umma_kernels() {
+  cudaError_t e = configure_umma_epi<EpiLinear<float, false>>();
+  if (e == cudaSuccess) e = configure_umma_epi<EpiLinear<float, true>>();
+  if (e == cudaSuccess) e = configure_umma_epi<EpiLinear<bf16, false>>();
+  if (e == cudaSuccess) e = configure_umma_epi<EpiLinear<bf16, true>>();
+  if (e == cudaSuccess) e = configure_umma_epi<EpiQKV<bf16>>();
+  if (e == cudaSuccess) e = configure_umma_epi<EpiCrossKV<bf16>>();
+  return e;
+}
+
+// One projection of the decode path: routes to tcgen05 (bf16 mode) or CUDA cores.
+// `a_map` is the TMA view of A (bf16 mode only), `a_ptr` the raw pointer.
+template <typename EpiF32, typename EpiB16>
+static int gemm(capdec_handle h, cudaStream_t s, const void* a_ptr, const CUtensorMap* a_map, const void* w_ptr,
+                const WeightMaps* w_maps, int M, int N, int K, const EpiF32& e32, const EpiB16& e16, const DecState* st) {
+  if (!h->bf16)
+    return launch_simt<float, float, EpiF32>(h, s, (const float*)a_ptr, K, (const float*)w_ptr, K, M, N, K, e32, st);
+  if (h->use_umma) return launch_umma<EpiB16>(h, s, *a_map, *w_maps, M, N, K, e16, st);
+  return launch_simt<bf16, bf16, EpiB16>(h, s, (const bf16*)a_ptr, K, (const bf16*)w_ptr, K, M, N, K, e16, st);
+}
+
+// ------------------------------------------------------------------ allocation helpers
+template <typename T>
+static int dev_alloc(capdec_handle h, T** out, size_t count) {
+  void* p = nullptr;
+  cudaError_t e = cudaMalloc(&p, std::max<size_t>(count, 1) * sizeof(T));
+  if (e != cudaSuccess)
+    return fail(h, CAPDEC_ERR_CUDA, "cudaMalloc of %zu bytes failed: %s", count * sizeof(T), cudaGetErrorString(e));
+  h->allocs.push_back(p);
+  *out = static_cast<T*>(p);
+  return 0;
+}
+static int dev_alloc_bytes(capdec_handle h, void** out, size_t bytes) {
+  unsigned char* p = nullptr;
+  int rc = dev_alloc<unsigned char>(h, &p, bytes);
+  *out = p;
+  return rc;
+}
+#define TRY(expr) do { int rc_ = (expr); if (rc_) return rc_; } while (0)
+
+// ------------------------------------------------------------------ lifecycle
+extern "C" int capdec_abi_version(void) { return CAPDEC_ABI_VERSION; }
+
+extern "C" const char* capdec_last_error(capdec_handle h) { return h ? h->err.c_str() : g_create_error.c_str(); }
+
+extern "C" int64_t capdec_launch_count(capdec_handle h) { return h ? h->launches : 0; }
+
+static void free_all(capdec_handle h) {
+  for (auto& kv : h->graphs) {
+    if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
+    if (kv.second.graph) cudaGraphDestroy(kv.second.graph);
+  }
+  h->graphs.clear();
+  for (void* p : h->allocs) cudaFree(p);
+  h->allocs.clear();
+}
+
+extern "C" int capdec_destroy(capdec_handle h) {
+  if (!h) return CAPDEC_OK;
+  cudaSetDevice(h->device);
+  free_all(h);
+  delete h;
+  return CAPDEC_OK;
+}
+
+static int create_impl(capdec_handle h) {
+  const capdec_config& c = h->cfg;
+  const int L = c.n_layer, F = c.d_ff;
+  const size_t M = (size_t)c.max_images * c.max_group;
+  const size_t es = h->esz;
+  LayerParams* lp = h->layer;
+  for (int l = 0; l < L; ++l) {
+    TRY(dev_alloc_bytes(h, &lp[l].w_qkv, (size_t)3 * kD * kD * es));
+    TRY(dev_alloc_bytes(h, &lp[l].w_so, (size_t)kD * kD * es));
+    TRY(dev_alloc_bytes(h, &lp[l].w_cq, (size_t)kD * kD * es));
+    TRY(dev_alloc_bytes(h, &lp[l].w_co, (size_t)kD * kD * es));
+    TRY(dev_alloc_bytes(h, &lp[l].w_1, (size_t)F * kD * es));
+    TRY(dev_alloc_bytes(h, &lp[l].w_2, (size_t)kD * F * es));
+    TRY(dev_alloc(h, &lp[l].b_qkv, 3 * kD));
+    TRY(dev_alloc(h, &lp[l].b_so, kD));
+    TRY(dev_alloc(h, &lp[l].b_cq, kD));
+    TRY(dev_alloc(h, &lp[l].b_co, kD));
+    TRY(dev_alloc(h, &lp[l].b_1, F));
+    TRY(dev_alloc(h, &lp[l].b_2, kD));
+    for (int j = 0; j < 3; ++j) {
+      TRY(dev_alloc(h, &lp[l].ln_w[j], kD));
+      TRY(dev_alloc(h, &lp[l].ln_b[j], kD));
+    }
+  }
+  TRY(dev_alloc_bytes(h, &h->w_ckv, (size_t)L * 2 * kD * kD * es));
+  TRY(dev_alloc(h, &h->b_ckv, (size_t)L * 2 * kD));
+  TRY(dev_alloc(h, &h->emb, (size_t)c.vocab * kD));
+  TRY(dev_alloc(h, &h->pe, (size_t)c.pe_rows * kD));
+  TRY(dev_alloc(h, &h->fc_w, (size_t)kVPad * kD));
+  TRY(dev_alloc(h, &h->fc_b, kVPad));
+
+  h->self_layer_elems = M * kH * h->t_pad * kHD;
+  TRY(dev_alloc_bytes(h, &h->self_k, (size_t)L * h->self_layer_elems * es));
+  TRY(dev_alloc_bytes(h, &h->self_v, (size_t)L * h->self_layer_elems * es));
+  TRY(dev_alloc_bytes(h, &h->cross_kv, (size_t)L * 2 * c.max_images * c.max_mem * kD * es));
+
+  TRY(dev_alloc(h, &h->x, M * kD));
+  TRY(dev_alloc(h, &h->t, M * kD));
+  TRY(dev_alloc(h, &h->logits, M * kVPad));
+  if (h->bf16) {
+    TRY(dev_alloc_bytes(h, &h->xb, M * kD * es));
+    TRY(dev_alloc_bytes(h, &h->mem_b, (size_t)c.max_images * c.max_mem * kD * es));
+  }
+  TRY(dev_alloc_bytes(h, &h->q, M * kD * es));
+  TRY(dev_alloc_bytes(h, &h->a, M * kD * es));
+  TRY(dev_alloc_bytes(h, &h->hbuf, M * F * es));
+  TRY(dev_alloc(h, &h->fin, M));
+  TRY(dev_alloc(h, &h->st, 1));
+  TRY(dev_alloc(h, &h->cp, 1));
+  CUDA_TRY(h, cudaMemset(h->st, 0, sizeof(DecState)));
+  if (h->use_umma) CUDA_TRY(h, configure_umma_kernels());
+  return 0;
+}
+
+extern "C" int capdec_create(const capdec_config* cfg, int device, capdec_handle* out) {
+  if (!cfg || !out) return fail(nullptr, CAPDEC_ERR_INVALID, "null argument");
+  *out = nullptr;
+  if (cfg->d_model != kD || cfg->n_head != kH)
+    return fail(nullptr, CAPDEC_ERR_INVALID, "only d_model=512, nhead=8 are built (got %d, %d)", cfg->d_model, cfg->n_head);
+  if (cfg->n_layer < 1 || cfg->n_layer > CAPDEC_MAX_LAYERS) return fail(nullptr, CAPDEC_ERR_INVALID, "n_layer %d out of range", cfg->n_layer);
+  if (cfg->d_ff < 128 || cfg->d_ff % 128 != 0) return fail(nullptr, CAPDEC_ERR_INVALID, "d_ff %d must be a multiple of 128", cfg->d_ff);
+  if (cfg->vocab < 2 || cfg->vocab > kVPad) return fail(nullptr, CAPDEC_ERR_INVALID, "vocab %d must be in [2,%d]", cfg->vocab, kVPad);
+  if (cfg->max_len < 2 || cfg->max_len > 128) return fail(nullptr, CAPDEC_ERR_INVALID, "max_len %d must be in [2,128]", cfg->max_len);
+  if (cfg->pe_rows < 1 || cfg->max_mem < 1 || cfg->max_images < 1 || cfg->max_group < 1)
+    return fail(nullptr, CAPDEC_ERR_INVALID, "sizes must be positive");
+  if (cfg->precision != CAPDEC_PREC_FP32 && cfg->precision != CAPDEC_PREC_BF16)
+    return fail(nullptr, CAPDEC_ERR_INVALID, "unknown precision %d", cfg->precision);
+
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev) {
+    cudaGetLastError();
+    return fail(nullptr, CAPDEC_ERR_NO_DEVICE, "CUDA device %d not available (%d visible)", device, ndev);
+  }
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, device) != cudaSuccess || prop.major != 10)
+    return fail(nullptr, CAPDEC_ERR_NO_DEVICE, "device %d is not sm_100-class (this library is built for sm_100a only)", device);
+  if (cudaSetDevice(device) != cudaSuccess) return fail(nullptr, CAPDEC_ERR_CUDA, "cudaSetDevice(%d) failed", device);
+
+  capdec_handle h = new capdec_engine();
+  h->cfg = *cfg;
+  h->device = device;
+  h->bf16 = cfg->precision == CAPDEC_PREC_BF16;
+  h->use_umma = h->bf16 && !(cfg->flags & CAPDEC_FLAG_NO_UMMA);
+  h->use_graph = !(cfg->flags & CAPDEC_FLAG_NO_GRAPH);
+  h->esz = h->bf16 ? 2 : 4;
+  h->t_pad = cfg->max_len <= 64 ? 64 : 128;
+  int rc = create_impl(h);
+  if (rc) {
+    g_create_error = h->err;
+    free_all(h);
+    delete h;
+    return rc;
+  }
+  *out = h;
+  return CAPDEC_OK;
+}
+
+// ------------------------------------------------------------------ weights
+static int pack_matrix(capdec_handle h, cudaStream_t s, const float* src, void* dst, int rows, int cols, int rows_out) {
+  const size_t n = (size_t)rows_out * cols;
+  const int threads = 256;
+  const unsigned blocks = (unsigned)((n + threads - 1) / threads);
+  if (h->bf16) pack_rows_kernel<bf16><<<blocks, threads, 0, s>>>(src, (bf16*)dst, rows, cols, rows_out);
+  else pack_rows_kernel<float><<<blocks, threads, 0, s>>>(src, (float*)dst, rows, cols, rows_out);
+  CUDA_TRY(h, cudaGetLastError());
+  h->launches++;
+  return 0;
+}
+static int copy_f32(capdec_handle h, cudaStream_t s, const float* src, float* dst, size_t n) {
+  CUDA_TRY(h, cudaMemcpyAsync(dst, src, n * sizeof(float), cudaMemcpyDeviceToDevice, s));
+  return 0;
+}
+
+extern "C" int capdec_set_weights(capdec_handle h, const capdec_weights* w, void* stream) {
+  if (!h || !w) return fail(h, CAPDEC_ERR_INVALID, "null argument");
+  cudaStream_t s = (cudaStream_t)stream;
+  CUDA_TRY(h, cudaSetDevice(h->device));
+  const int L = h->cfg.n_layer, F = h->cfg.d_ff, V = h->cfg.vocab;
+  if (!w->embedding || !w->pe || !w->fc_out_w || !w->fc_out_b) return fail(h, CAPDEC_ERR_INVALID, "null weight pointer");
+  TRY(copy_f32(h, s, w->embedding, h->emb, (size_t)V * kD));
+  TRY(copy_f32(h, s, w->pe, h->pe, (size_t)h->cfg.pe_rows * kD));
+  // vocabulary projection stays fp32 in both modes; rows V..127 are zero
+  pack_rows_kernel<float><<<(kVPad * kD + 255) / 256, 256, 0, s>>>(w->fc_out_w, h->fc_w, V, kD, kVPad);
+  pack_rows_kernel<float><<<1, 256, 0, s>>>(w->fc_out_b, h->fc_b, 1, V, 1);
+  CUDA_TRY(h, cudaMemsetAsync(h->fc_b + V, 0, (kVPad - V) * sizeof(float), s));
+  h->launches += 2;
+  for (int l = 0; l < L; ++l) {
+    const capdec_layer_weights& lw = w->layer[l];
+    LayerParams& lp = h->layer[l];
+    const void* ptrs[] = {lw.self_in_w, lw.self_in_b, lw.self_out_w, lw.self_out_b, lw.cross_in_w, lw.cross_in_b,
+                          lw.cross_out_w, lw.cross_out_b, lw.lin1_w, lw.lin1_b, lw.lin2_w, lw.lin2_b,
+                          lw.norm_w[0], lw.norm_w[1], lw.norm_w[2], lw.norm_b[0], lw.norm_b[1], lw.norm_b[2]};
+    for (const void* p : ptrs) if (!p) return fail(h, CAPDEC_ERR_INVALID, "null weight pointer in layer %d", l);
+    TRY(pack_matrix(h, s, lw.self_in_w, lp.w_qkv, 3 * kD, kD, 3 * kD));
+    TRY(pack_matrix(h, s, lw.self_out_w, lp.w_so, kD, kD, kD));
+    TRY(pack_matrix(h, s, lw.cross_in_w, lp.w_cq, kD, kD, kD));  // rows [0,512): the q projection
+    TRY(pack_matrix(h, s, lw.cross_out_w, lp.w_co, kD, kD, kD));
+    TRY(pack_matrix(h, s, lw.lin1_w, lp.w_1, F, kD, F));
+    TRY(pack_matrix(h, s, lw.lin2_w, lp.w_2, kD, F, kD));
+    // rows [512,1536) of the cross in_proj: K then V projection, concatenated over layers
+    TRY(pack_matrix(h, s, lw.cross_in_w + (size_t)kD * kD, (char*)h->w_ckv + (size_t)l * 2 * kD * kD * h->esz, 2 * kD, kD, 2 * kD));
+    TRY(copy_f32(h, s, lw.cross_in_b + kD, h->b_ckv + (size_t)l * 2 * kD, 2 * kD));
+    TRY(copy_f32(h, s, lw.self_in_b, lp.b_qkv, 3 * kD));
+    TRY(copy_f32(h, s, lw.self_out_b, lp.b_so, kD));
+    TRY(copy_f32(h, s, lw.cross_in_b, lp.b_cq, kD));
+    TRY(copy_f32(h, s, lw.cross_out_b, lp.b_co, kD));
+    TRY(copy_f32(h, s, lw.lin1_b, lp.b_1, F));
+    TRY(copy_f32(h, s, lw.lin2_b, lp.b_2, kD));
+    for (int j = 0; j < 3; ++j) {
+      TRY(copy_f32(h, s, lw.norm_w[j], lp.ln_w[j], kD));
+      TRY(copy_f32(h, s, lw.norm_b[j], lp.ln_b[j], kD));
+    }
+    if (h->use_umma) {
+      TRY(make_weight_maps(h, &lp.m_qkv, lp.w_qkv, 3 * kD, kD));
+      TRY(make_weight_maps(h, &lp.m_so, lp.w_so, kD, kD));
+      TRY(make_weight_maps(h, &lp.m_cq, lp.w_cq, kD, kD));
+      TRY(make_weight_maps(h, &lp.m_co, lp.w_co, kD, kD));
+      TRY(make_weight_maps(h, &lp.m_1, lp.w_1, F, kD));
+      TRY(make_weight_maps(h, &lp.m_2, lp.w_2, kD, F));
+    }
+  }
+  if (h->use_umma) TRY(make_weight_maps(h, &h->m_ckv, h->w_ckv, L * 2 * kD, kD));
+  h->have_weights = true;
+  return CAPDEC_OK;
+}
+
+// ------------------------------------------------------------------ prefill
+extern "C" int capdec_prefill(capdec_handle h, const float* memory, int32_t n_images, int32_t mem_len, void* stream) {
+  if (!h || !memory) return fail(h, CAPDEC_ERR_INVALID, "null argument");
+  if (!h->have_weights) return fail(h, CAPDEC_ERR_STATE, "capdec_prefill before capdec_set_weights");
+  if (n_images < 1 || mem_len < 1) return fail(h, CAPDEC_ERR_INVALID, "n_images and mem_len must be positive");
+  if (n_images > h->cfg.max_images || mem_len > h->cfg.max_mem)
+    return fail(h, CAPDEC_ERR_CAPACITY, "prefill of %d images x %d exceeds capacity %d x %d", n_images, mem_len,
+                h->cfg.max_images, h->cfg.max_mem);
+  cudaStream_t s = (cudaStream_t)stream;
+  CUDA_TRY(h, cudaSetDevice(h->device));
+  h->prefilled = false;
+  h->launches_this_enqueue = 0;
+  const int M = n_images * mem_len, N = h->cfg.n_layer * 2 * kD;
+  if (h->bf16) {
+    const size_t n4 = (size_t)M * kD / 4;
+    convert_kernel<bf16><<<(unsigned)((n4 + 255) / 256), 256, 0, s>>>(memory, (bf16*)h->mem_b, n4);
+    CUDA_TRY(h, cudaGetLastError());
+    h->launches_this_enqueue++;
+  }
+  EpiCrossKV<float> e32{(float*)h->cross_kv, h->b_ckv, n_images, mem_len};
+  EpiCrossKV<bf16> e16{(bf16*)h->cross_kv, h->b_ckv, n_images, mem_len};
+  CUtensorMap tm_mem;
+  if (h->use_umma) TRY(make_map(h, &tm_mem, h->mem_b, M, kD, kUmmaBM));
+  TRY(gemm(h, s, h->bf16 ? h->mem_b : (const void*)memory, &tm_mem, h->w_ckv, &h->m_ckv, M, N, kD, e32, e16, nullptr));
+  h->launches += h->launches_this_enqueue;
+  h->n_images = n_images;
+  h->mem_len = mem_len;
+  h->prefilled = true;
+  return CAPDEC_OK;
+}
+
+// ------------------------------------------------------------------ one decode step
+template <typename Elem>
+static int launch_self_attn(capdec_handle h, cudaStream_t s, int l, int M) {
+  const Elem* kc = (const Elem*)h->self_k + (size_t)l * h->self_layer_elems;
+  const Elem* vc = (const Elem*)h->self_v + (size_t)l * h->self_layer_elems;
+  const int blocks = (M * kH + kAttnWarps - 1) / kAttnWarps;
+  if (h->t_pad == 64)
+    self_attn_kernel<Elem, 16><<<blocks, kAttnWarps * 32, 0, s>>>((const Elem*)h->q, kc, vc, (Elem*)h->a, M, h->t_pad, h->st);
+  else
+    self_attn_kernel<Elem, 32><<<blocks, kAttnWarps * 32, 0, s>>>((const Elem*)h->q, kc, vc, (Elem*)h->a, M, h->t_pad, h->st);
+  CUDA_TRY(h, cudaGetLastError());
+  h->launches_this_enqueue++;
+  return 0;
+}
+
+template <typename Elem, int GT>
+static int launch_cross_gt(capdec_handle h, cudaStream_t s, const Elem* ck, const Elem* cv, int n_images, int group, int S) {
+  const int warps = n_images * kH * (group / GT);
+  cross_attn_kernel<Elem, GT><<<(warps + kAttnWarps - 1) / kAttnWarps, kAttnWarps * 32, 0, s>>>(
+      (const Elem*)h->q, ck, cv, (Elem*)h->a, n_images, group, S, h->st);
+  CUDA_TRY(h, cudaGetLastError());
+  h->launches_this_enqueue++;
+  return 0;
+}
+
+template <typename Elem>
+static int launch_cross_attn(capdec_handle h, cudaStream_t s, int l, int n_images, int group, int S) {
+  const size_t tile = (size_t)n_images * kH * S * kHD;  // one (layer, kv) block
+  const Elem* ck = (const Elem*)h->cross_kv + (size_t)(2 * l) * tile;
+  const Elem* cv = ck + tile;
+  if (group % 6 == 0) return launch_cross_gt<Elem, 6>(h, s, ck, cv, n_images, group, S);
+  if (group % 4 == 0) return launch_cross_gt<Elem, 4>(h, s, ck, cv, n_images, group, S);
+  if (group % 2 == 0) return launch_cross_gt<Elem, 2>(h, s, ck, cv, n_images, group, S);
+  return launch_cross_gt<Elem, 1>(h, s, ck, cv, n_images, group, S);
+}
+
+template <typename Elem>
+static int launch_add_ln(capdec_handle h, cudaStream_t s, int l, int which, int M) {
+  add_ln_kernel<Elem><<<(M + 3) / 4, 128, 0, s>>>(h->x, h->t, h->layer[l].ln_w[which], h->layer[l].ln_b[which],
+                                                   (Elem*)h->xb, M, h->st);
+  CUDA_TRY(h, cudaGetLastError());
+  h->launches_this_enqueue++;
+  return 0;
+}
+
+template <typename Elem>
+static int enqueue_step_t(capdec_handle h, cudaStream_t s, int n_images, int S, int group) {
+  const int M = n_images * group, L = h->cfg.n_layer, F = h->cfg.d_ff;
+  const DecState* st = h->st;
+  const void* xin = h->bf16 ? h->xb : (void*)h->x;  // GEMM A operand view of the residual stream
+  embed_pe_kernel<Elem><<<(M * (kD / 4) + 255) / 256, 256, 0, s>>>(h->st, h->cp, h->emb, h->pe, h->x, (Elem*)h->xb, M);
+  CUDA_TRY(h, cudaGetLastError());
+  h->launches_this_enqueue++;
+  for (int l = 0; l < L; ++l) {
+    LayerParams& lp = h->layer[l];
+    {  // self-attention block
+      float* kc32 = (float*)h->self_k + (size_t)l * h->self_layer_elems;
+      float* vc32 = (float*)h->self_v + (size_t)l * h->self_layer_elems;
+      bf16* kc16 = (bf16*)h->self_k + (size_t)l * h->self_layer_elems;
+      bf16* vc16 = (bf16*)h->self_v + (size_t)l * h->self_layer_elems;
+      EpiQKV<float> e32{(float*)h->q, kc32, vc32, lp.b_qkv, st, h->t_pad};
+      EpiQKV<bf16> e16{(bf16*)h->q, kc16, vc16, lp.b_qkv, st, h->t_pad};
+      TRY(gemm(h, s, xin, &h->tm_xb, lp.w_qkv, &lp.m_qkv, M, 3 * kD, kD, e32, e16, st));
+      TRY(launch_self_attn<Elem>(h, s, l, M));
+      EpiLinear<float, false> eo{h->t, lp.b_so, kD};
+      TRY(gemm(h, s, h->a, &h->tm_a, lp.w_so, &lp.m_so, M, kD, kD, eo, eo, st));
+      TRY(launch_add_ln<Elem>(h, s, l, 0, M));
+    }
+    {  // cross-attention block
+      EpiLinear<float, false> q32{(float*)h->q, lp.b_cq, kD};
+      EpiLinear<bf16, false> q16{(bf16*)h->q, lp.b_cq, kD};
+      TRY(gemm(h, s, xin, &h->tm_xb, lp.w_cq, &lp.m_cq, M, kD, kD, q32, q16, st));
+      TRY(launch_cross_attn<Elem>(h, s, l, n_images, group, S));
+      EpiLinear<float, false> eo{h->t, lp.b_co, kD};
+      TRY(gemm(h, s, h->a, &h->tm_a, lp.w_co, &lp.m_co, M, kD, kD, eo, eo, st));
+      TRY(launch_add_ln<Elem>(h, s, l, 1, M));
+    }
+    {  // feed-forward block
+      EpiLinear<float, true> h32{(float*)h->hbuf, lp.b_1, F};
+      EpiLinear<bf16, true> h16{(bf16*)h->hbuf, lp.b_1, F};
+      TRY(gemm(h, s, xin, &h->tm_xb, lp.w_1, &lp.m_1, M, F, kD, h32, h16, st));
+      EpiLinear<float, false> eo{h->t, lp.b_2, kD};
+      TRY(gemm(h, s, h->hbuf, &h->tm_h, lp.w_2, &lp.m_2, M, kD, F, eo, eo, st));
+      TRY(launch_add_ln<Elem>(h, s, l, 2, M));
+    }
+  }
+  // vocabulary projection in fp32 on the fp32 residual stream, then pick/sample
+  EpiLinear<float, false> ev{h->logits, h->fc_b, kVPad};
+  TRY((launch_simt<float, float, EpiLinear<float, false>>(h, s, h->x, kD, h->fc_w, kD, M, kVPad, kD, ev, st)));
+  head_kernel<<<(M + 3) / 4, 128, 0, s>>>(h->st, h->cp, h->logits, h->fin, M, h->cfg.vocab);
+  CUDA_TRY(h, cudaGetLastError());
+  h->launches_this_enqueue++;
+  return 0;
+}
+
+static int enqueue_step(capdec_handle h, cudaStream_t s, int n_images, int S, int group) {
+  h->launches_this_enqueue = 0;
+  return h->bf16 ? enqueue_step_t<bf16>(h, s, n_images, S, group) : enqueue_step_t<float>(h, s, n_images, S, group);
+}
+
+static int ensure_activation_maps(capdec_handle h, int M) {
+  if (!h->use_umma || h->maps_for_m == M) return 0;
+  TRY(make_map(h, &h->tm_xb, h->xb, M, kD, kUmmaBM));
+  TRY(make_map(h, &h->tm_a, h->a, M, kD, kUmmaBM));
+  TRY(make_map(h, &h->tm_h, h->hbuf, M, h->cfg.d_ff, kUmmaBM));
+  h->maps_for_m = M;
+  return 0;
+}
+
+// Capture one step into a graph (on a private stream: the caller's may be the legacy stream).
+static int get_step_graph(capdec_handle h, int n_images, int S, int group, StepGraph** out) {
+  auto key = std::make_tuple(n_images, S, group);
+  auto it = h->graphs.find(key);
+  if (it != h->graphs.end()) { *out = &it->second; return 0; }
+  cudaStream_t cs;
+  CUDA_TRY(h, cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking));
+  StepGraph g;
+  cudaError_t e = cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal);
+  int rc = 0;
+  if (e == cudaSuccess) {
+    rc = enqueue_step(h, cs, n_images, S, group);
+    e = cudaStreamEndCapture(cs, &g.graph);
+  }
+  if (rc == 0 && e == cudaSuccess) e = cudaGraphInstantiate(&g.exec, g.graph, 0);
+  cudaStreamDestroy(cs);
+  if (rc) return rc;
+  if (e != cudaSuccess) {
+    if (g.graph) cudaGraphDestroy(g.graph);
+    return fail(h, CAPDEC_ERR_CUDA, "step graph capture failed: %s", cudaGetErrorString(e));
+  }
+  g.kernels = h->launches_this_enqueue;
+  auto ins = h->graphs.emplace(key, g);
+  *out = &ins.first->second;
+  return 0;
+}
+
+// ------------------------------------------------------------------ decode
+static int validate_decode(capdec_handle h, const capdec_decode_args* a) {
+  if (!h->prefilled) return fail(h, CAPDEC_ERR_STATE, "capdec_decode before capdec_prefill");
+  if (a->group < 1 || a->n_sample < 0 || a->n_sample > a->group) return fail(h, CAPDEC_ERR_INVALID, "bad group/n_sample (%d/%d)", a->group, a->n_sample);
+  if (a->group > h->cfg.max_group) return fail(h, CAPDEC_ERR_CAPACITY, "group %d exceeds capacity %d", a->group, h->cfg.max_group);
+  if (a->max_len < 2 || a->max_len > h->cfg.max_len) return fail(h, CAPDEC_ERR_CAPACITY, "max_len %d outside [2,%d]", a->max_len, h->cfg.max_len);
+  if (a->max_len - 1 > h->cfg.pe_rows)  // the reference fails at vit:32 (prefix longer than the pe table)
+    return fail(h, CAPDEC_ERR_INVALID, "max_len %d needs %d positional rows, table has %d", a->max_len, a->max_len - 1, h->cfg.pe_rows);
+  const int V = h->cfg.vocab;
+  if (a->start_token < 0 || a->start_token >= V || a->end_token < 0 || a->end_token >= V)
+    return fail(h, CAPDEC_ERR_INVALID, "start/end token outside the vocabulary");
+  if (!a->ids_out) return fail(h, CAPDEC_ERR_INVALID, "ids_out is null");
+  return 0;
+}
+
+extern "C" int capdec_decode(capdec_handle h, const capdec_decode_args* a, void* stream) {
+  if (!h || !a) return fail(h, CAPDEC_ERR_INVALID, "null argument");
+  TRY(validate_decode(h, a));
+  cudaStream_t s = (cudaStream_t)stream;
+  CUDA_TRY(h, cudaSetDevice(h->device));
+  const int n_images = h->n_images, S = h->mem_len, group = a->group, M = n_images * group;
+  TRY(ensure_activation_maps(h, M));
+
+  CallParams cp;
+  cp.ids = (long long*)a->ids_out;
+  cp.logp = a->logp_out;
+  cp.logits_dump = a->logits_out;
+  cp.seed = a->seed;
+  cp.seq_id_base = a->seq_id_base;
+  cp.max_len = a->max_len;
+  cp.group = group;
+  cp.n_sample = a->n_sample;
+  cp.start_token = a->start_token;
+  cp.end_token = a->end_token;
+  cp.pad_token = a->pad_token;
+  cp.no_early_stop = (a->flags & CAPDEC_DECODE_NO_EARLY_STOP) ? 1 : 0;
+  cp.n_sample_rows = n_images * a->n_sample;
+  cp.n_greedy_rows = M - cp.n_sample_rows;
+  // pageable source: the runtime stages it before returning, so `cp` may die with this frame
+  CUDA_TRY(h, cudaMemcpyAsync(h->cp, &cp, sizeof cp, cudaMemcpyHostToDevice, s));
+  init_rollout_kernel<<<std::min((M * a->max_len + 255) / 256, 1024), 256, 0, s>>>(h->st, h->cp, h->fin, M);
+  CUDA_TRY(h, cudaGetLastError());
+  h->launches++;
+
+  const int T = a->max_len - 1;
+  if (h->use_graph) {
+    StepGraph* g = nullptr;
+    TRY(get_step_graph(h, n_images, S, group, &g));
+    for (int t = 0; t < T; ++t) CUDA_TRY(h, cudaGraphLaunch(g->exec, s));
+    h->launches += (long long)g->kernels * T;
+  } else {
+    for (int t = 0; t < T; ++t) {
+      TRY(enqueue_step(h, s, n_images, S, group));
+      h->launches += h->launches_this_enqueue;
+    }
+  }
+  if (a->steps_out) {
+    int steps = 0;
+    CUDA_TRY(h, cudaMemcpyAsync(&steps, &h->st->steps_executed, sizeof(int), cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(h, cudaStreamSynchronize(s));
+    *a->steps_out = steps;
+  }
+  return CAPDEC_OK;
+}
+
+extern "C" int capdec_generate_host(capdec_handle h, const float* memory_host, int32_t n_images, int32_t mem_len,
+                                    const capdec_decode_args* ah, void* stream) {
+  if (!h || !memory_host || !ah) return fail(h, CAPDEC_ERR_INVALID, "null argument");
+  if (ah->logits_out) return fail(h, CAPDEC_ERR_INVALID, "logits_out is not supported by capdec_generate_host");
+  if (n_images < 1 || mem_len < 1 || n_images > h->cfg.max_images || mem_len > h->cfg.max_mem)
+    return fail(h, CAPDEC_ERR_CAPACITY, "%d images x %d exceeds capacity %d x %d", n_images, mem_len, h->cfg.max_images, h->cfg.max_mem);
+  if (ah->group < 1 || ah->group > h->cfg.max_group || ah->max_len < 2 || ah->max_len > h->cfg.max_len)
+    return fail(h, CAPDEC_ERR_CAPACITY, "group/max_len outside capacity");
+  cudaStream_t s = (cudaStream_t)stream;
+  CUDA_TRY(h, cudaSetDevice(h->device));
+  const size_t Mmax = (size_t)h->cfg.max_images * h->cfg.max_group;
+  if (!h->stage_mem) {
+    TRY(dev_alloc(h, &h->stage_mem, (size_t)h->cfg.max_images * h->cfg.max_mem * kD));
+    TRY(dev_alloc(h, &h->stage_ids, Mmax * h->cfg.max_len));
+    TRY(dev_alloc(h, &h->stage_logp, Mmax * h->cfg.max_len));
+  }
+  const size_t M = (size_t)n_images * ah->group;
+  CUDA_TRY(h, cudaMemcpyAsync(h->stage_mem, memory_host, (size_t)n_images * mem_len * kD * sizeof(float), cudaMemcpyHostToDevice, s));
+  TRY(capdec_prefill(h, h->stage_mem, n_images, mem_len, stream));
+  capdec_decode_args ad = *ah;
+  ad.ids_out = (int64_t*)h->stage_ids;
+  ad.logp_out = ah->logp_out ? h->stage_logp : nullptr;
+  int steps = 0;
+  ad.steps_out = nullptr;
+  TRY(capdec_decode(h, &ad, stream));
+  CUDA_TRY(h, cudaMemcpyAsync(ah->ids_out, h->stage_ids, M * ah->max_len * sizeof(int64_t), cudaMemcpyDeviceToHost, s));
+  if (ah->logp_out)
+    CUDA_TRY(h, cudaMemcpyAsync(ah->logp_out, h->stage_logp, M * (ah->max_len - 1) * sizeof(float), cudaMemcpyDeviceToHost, s));
+  CUDA_TRY(h, cudaMemcpyAsync(&steps, &h->st->steps_executed, sizeof(int), cudaMemcpyDeviceToHost, s));
+  CUDA_TRY(h, cudaStreamSynchronize(s));
+  if (ah->steps_out) *ah->steps_out = steps;
+  return CAPDEC_OK;
+}
+
+extern "C" int capdec_sample_logits(capdec_handle h, const float* logits, int32_t n_rows, int32_t mode, uint64_t seed,
+                                    uint64_t seq_id_base, int32_t step, int64_t* ids_out, float* logp_out, void* stream) {
+  if (!h || !logits || !ids_out || n_rows < 1) return fail(h, CAPDEC_ERR_INVALID, "bad argument");
+  CUDA_TRY(h, cudaSetDevice(h->device));
+  sample_rows_kernel<<<(n_rows + 3) / 4, 128, 0, (cudaStream_t)stream>>>(logits, n_rows, h->cfg.vocab, mode, seed, seq_id_base,
+                                                                         step, (long long*)ids_out, logp_out);
+  CUDA_TRY(h, cudaGetLastError());
+  h->launches++;
+  return CAPDEC_OK;
+}
+
+// ------------------------------------------------------------------ diagnostics
+extern "C" int capdec_debug_gemm(capdec_handle h, const float* a, const float* w, const float* bias, float* c, int32_t m,
+                                 int32_t n, int32_t k, int32_t relu, void* stream) {
+  if (!h || !a || !w || !c || m < 1) return fail(h, CAPDEC_ERR_INVALID, "bad argument");
+  cudaStream_t s = (cudaStream_t)stream;
+  CUDA_TRY(h, cudaSetDevice(h->device));
+  h->launches_this_enqueue = 0;
+  int rc = 0;
+  if (!h->bf16) {
+    if (relu) { EpiLinear<float, true> e{c, bias, n}; rc = launch_simt<float, float, EpiLinear<float, true>>(h, s, a, k, w, k, m, n, k, e, nullptr); }
+    else { EpiLinear<float, false> e{c, bias, n}; rc = launch_simt<float, float, EpiLinear<float, false>>(h, s, a, k, w, k, m, n, k, e, nullptr); }
+  } else {
+    bf16 *ab = nullptr, *wb = nullptr;
+    CUDA_TRY(h, cudaMalloc(&ab, (size_t)m * k * 2));
+    CUDA_TRY(h, cudaMalloc(&wb, (size_t)n * k * 2));
+    pack_rows_kernel<bf16><<<(unsigned)(((size_t)m * k + 255) / 256), 256, 0, s>>>(a, ab, m, k, m);
+    pack_rows_kernel<bf16><<<(unsigned)(((size_t)n * k + 255) / 256), 256, 0, s>>>(w, wb, n, k, n);
+    if (h->use_umma) {
+      CUtensorMap ta;
+      WeightMaps wm;
+      rc = make_map(h, &ta, ab, m, k, kUmmaBM);
+      if (!rc) rc = make_weight_maps(h, &wm, wb, n, k);
+      if (!rc) {
+        if (relu) { EpiLinear<float, true> e{c, bias, n}; rc = launch_umma(h, s, ta, wm, m, n, k, e, nullptr); }
+        else { EpiLinear<float, false> e{c, bias, n}; rc = launch_umma(h, s, ta, wm, m, n, k, e, nullptr); }
+      }
+    } else {
+      if (relu) { EpiLinear<float, true> e{c, bias, n}; rc = launch_simt<bf16, bf16, EpiLinear<float, true>>(h, s, ab, k, wb, k, m, n, k, e, nullptr); }
+      else { EpiLinear<float, false> e{c, bias, n}; rc = launch_simt<bf16, bf16, EpiLinear<float, false>>(h, s, ab, k, wb, k, m, n, k, e, nullptr); }
+    }
+    cudaError_t e2 = cudaStreamSynchronize(s);
+    cudaFree(ab);
+    cudaFree(wb);
+    if (!rc && e2 != cudaSuccess) rc = fail(h, CAPDEC_ERR_CUDA, "debug gemm failed: %s", cudaGetErrorString(e2));
+  }
+  h->launches += h->launches_this_enqueue + (h->bf16 ? 2 : 0);
+  return rc;
+}
+
+extern "C" int capdec_debug_cross_kv(capdec_handle h, int32_t layer, int32_t which, float* out, void* stream) {
+  if (!h || !out || layer < 0 || layer >= h->cfg.n_layer || which < 0 || which > 1) return fail(h, CAPDEC_ERR_INVALID, "bad argument");
+  if (!h->prefilled) return fail(h, CAPDEC_ERR_STATE, "no prefill");
+  CUDA_TRY(h, cudaSetDevice(h->device));
+  const size_t tile = (size_t)h->n_images * kH * h->mem_len * kHD;
+  const size_t n = (size_t)h->n_images * h->mem_len * kD;
+  const unsigned blocks = (unsigned)((n + 255) / 256);
+  if (h->bf16)
+    gather_cross_kernel<bf16><<<blocks, 256, 0, (cudaStream_t)stream>>>((const bf16*)h->cross_kv + (size_t)(2 * layer + which) * tile, out, h->n_images, h->mem_len);
+  else
+    gather_cross_kernel<float><<<blocks, 256, 0, (cudaStream_t)stream>>>((const float*)h->cross_kv + (size_t)(2 * layer + which) * tile, out, h->n_images, h->mem_len);
+  CUDA_TRY(h, cudaGetLastError());
+  h->launches++;
+  return CAPDEC_OK;
+}

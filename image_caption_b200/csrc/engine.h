@@ -1,0 +1,80 @@
+// engine.h - host-side state of one caption decode engine (one per process and device).
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <map>
+#include <string>
+#include <tuple>
+#include <vector>
+
+#include "../../include/capdec.h"
+#include "common.cuh"
+
+namespace capdec {
+
+// W operand tensor maps for the three N-tile widths the tcgen05 GEMM is instantiated for.
+struct WeightMaps {
+  CUtensorMap bn[3];  // 32, 64, 128
+};
+
+struct LayerParams {
+  // GEMM weights in the engine's element type, [N, K] row-major (nn.Linear layout, K-major)
+  void *w_qkv, *w_so, *w_cq, *w_co, *w_1, *w_2;
+  float *b_qkv, *b_so, *b_cq, *b_co, *b_1, *b_2;
+  float *ln_w[3], *ln_b[3];
+  WeightMaps m_qkv, m_so, m_cq, m_co, m_1, m_2;
+};
+
+struct StepGraph {
+  cudaGraph_t graph = nullptr;
+  cudaGraphExec_t exec = nullptr;
+  int kernels = 0;
+};
+
+}  // namespace capdec
+
+struct capdec_engine {
+  capdec_config cfg;
+  int device = 0;
+  bool bf16 = false;
+  bool use_umma = false;
+  bool use_graph = true;
+  size_t esz = 4;
+  int t_pad = 64;
+  std::string err;
+
+  // ---- parameters (engine-owned copies)
+  std::vector<void*> allocs;  // everything to cudaFree at destroy
+  capdec::LayerParams layer[CAPDEC_MAX_LAYERS];
+  void* w_ckv = nullptr;      // [L*1024, 512] cross K|V projection rows of every layer
+  float* b_ckv = nullptr;
+  capdec::WeightMaps m_ckv;
+  float *emb = nullptr, *pe = nullptr, *fc_w = nullptr, *fc_b = nullptr;  // fc padded to kVPad rows
+  bool have_weights = false;
+
+  // ---- caches
+  void *self_k = nullptr, *self_v = nullptr;  // [L][M_max][H][t_pad][64]
+  void* cross_kv = nullptr;                   // [L][2][n_images][H][S][64]
+  size_t self_layer_elems = 0;
+
+  // ---- step workspace
+  float *x = nullptr, *t = nullptr, *logits = nullptr;
+  void *xb = nullptr, *q = nullptr, *a = nullptr, *hbuf = nullptr, *mem_b = nullptr;
+  unsigned char* fin = nullptr;
+  capdec::DecState* st = nullptr;
+  capdec::CallParams* cp = nullptr;
+  CUtensorMap tm_xb, tm_a, tm_h;  // A-operand maps for the current M
+  int maps_for_m = -1;
+
+  // ---- host-buffer entry point staging (device side)
+  float* stage_mem = nullptr;
+  long long* stage_ids = nullptr;
+  float* stage_logp = nullptr;
+
+  // ---- current rollout
+  int n_images = 0, mem_len = 0;
+  bool prefilled = false;
+  std::map<std::tuple<int, int, int>, capdec::StepGraph> graphs;  // (n_images, mem_len, group)
+  long long launches = 0;
+  int launches_this_enqueue = 0;
+};

@@ -1,0 +1,239 @@
+// pointwise.cuh - the non-GEMM, non-attention kernels of the decode step:
+//   init_rollout_kernel  rollout state, ids[:,0] = <start>          (vit:307, scst:216-218)
+//   embed_pe_kernel      embedding * sqrt(d) + pe[n]                 (vit:166-169)
+//   add_ln_kernel        x = LayerNorm(x + t), eps 1e-5              (torch post-LN blocks, K5/K9/K10)
+//   head_kernel          argmax | softmax-sample + log-prob, finished bookkeeping,
+//                        stop condition and step advance               (vit:315-323, scst:226-249, K12/K13)
+//   convert / gather helpers for prefill and diagnostics
+#pragma once
+#include "common.cuh"
+
+namespace capdec {
+
+__global__ void init_rollout_kernel(DecState* st, const CallParams* cp, unsigned char* fin, int M) {
+  const CallParams p = *cp;
+  const int tid = blockIdx.x * blockDim.x + threadIdx.x;
+  if (tid == 0) {
+    st->step = 0; st->done = 0; st->steps_executed = 0; st->ticket = 0u;
+    st->cnt_end_now = 0; st->cnt_finished = 0;
+    st->greedy_done = (p.n_greedy_rows == 0);
+    st->sample_done = (p.n_sample_rows == 0);
+  }
+  const int total = M * p.max_len;
+  for (int i = tid; i < total; i += gridDim.x * blockDim.x) {
+    p.ids[i] = (i % p.max_len == 0) ? p.start_token : p.pad_token;
+    if (p.logp != nullptr && i < M * (p.max_len - 1)) p.logp[i] = 0.f;
+  }
+  if (tid < M) fin[tid] = 0;
+}
+
+// x[m,:] = emb[tok]*sqrt(512) + pe[n,:]; separate multiply and add (no FMA contraction) so the
+// fp32 mode reproduces the reference's two-op rounding.
+template <typename Elem>
+__global__ void embed_pe_kernel(const DecState* st, const CallParams* cp, const float* __restrict__ emb,
+                                const float* __restrict__ pe, float* __restrict__ x, Elem* __restrict__ xb, int M) {
+  if (st->done) return;
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;  // one float4 each
+  if (idx >= M * (kD / 4)) return;
+  const int m = idx / (kD / 4), c = (idx % (kD / 4)) * 4;
+  const int n = st->step;
+  const long long tok = cp->ids[(size_t)m * cp->max_len + n];
+  const float4 e = __ldg(reinterpret_cast<const float4*>(emb + (size_t)tok * kD + c));
+  const float4 p = __ldg(reinterpret_cast<const float4*>(pe + (size_t)n * kD + c));
+  const float sc = 22.627416997969522f;  // sqrt(512) rounded to fp32, as torch does for the scalar
+  float4 r;
+  r.x = __fadd_rn(__fmul_rn(e.x, sc), p.x); r.y = __fadd_rn(__fmul_rn(e.y, sc), p.y);
+  r.z = __fadd_rn(__fmul_rn(e.z, sc), p.z); r.w = __fadd_rn(__fmul_rn(e.w, sc), p.w);
+  *reinterpret_cast<float4*>(x + (size_t)m * kD + c) = r;
+  if (xb != nullptr) store4(xb + (size_t)m * kD + c, r.x, r.y, r.z, r.w);
+}
+
+// One warp per row of 512: x <- LN(x + t) * gamma + beta (biased variance, eps inside sqrt).
+template <typename Elem>
+__global__ void __launch_bounds__(128)
+add_ln_kernel(float* __restrict__ x, const float* __restrict__ t, const float* __restrict__ gamma,
+              const float* __restrict__ beta, Elem* __restrict__ xb, int M, const DecState* st) {
+  if (st->done) return;
+  const int row = blockIdx.x * 4 + (threadIdx.x >> 5);
+  if (row >= M) return;
+  const int lane = threadIdx.x & 31;
+  float v[16];
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int c = i * 128 + lane * 4;
+    const float4 a = *reinterpret_cast<const float4*>(x + (size_t)row * kD + c);
+    const float4 b = *reinterpret_cast<const float4*>(t + (size_t)row * kD + c);
+    v[4 * i] = a.x + b.x; v[4 * i + 1] = a.y + b.y; v[4 * i + 2] = a.z + b.z; v[4 * i + 3] = a.w + b.w;
+    s += (v[4 * i] + v[4 * i + 1]) + (v[4 * i + 2] + v[4 * i + 3]);
+  }
+  const float mean = warp_sum(s) * (1.f / kD);
+  float q = 0.f;
+#pragma unroll
+  for (int i = 0; i < 16; ++i) { v[i] -= mean; q = fmaf(v[i], v[i], q); }
+  const float rstd = rsqrtf(warp_sum(q) * (1.f / kD) + 1e-5f);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int c = i * 128 + lane * 4;
+    const float4 g = __ldg(reinterpret_cast<const float4*>(gamma + c));
+    const float4 b = __ldg(reinterpret_cast<const float4*>(beta + c));
+    const float r0 = v[4 * i] * rstd * g.x + b.x, r1 = v[4 * i + 1] * rstd * g.y + b.y;
+    const float r2 = v[4 * i + 2] * rstd * g.z + b.z, r3 = v[4 * i + 3] * rstd * g.w + b.w;
+    *reinterpret_cast<float4*>(x + (size_t)row * kD + c) = make_float4(r0, r1, r2, r3);
+    if (xb != nullptr) store4(xb + (size_t)row * kD + c, r0, r1, r2, r3);
+  }
+}
+
+// Warp-level argmax / categorical draw over one row of kVPad logits (entries >= V are -inf).
+// Lane l owns vocabulary entries 4l .. 4l+3.  Returns token; *logp_out = log_softmax[token].
+__device__ __forceinline__ int warp_pick(const float (&l)[4], int lane, bool sample, float u, int V, float* logp_out) {
+  float mx = fmaxf(fmaxf(l[0], l[1]), fmaxf(l[2], l[3]));
+  mx = warp_max(mx);
+  float e[4];
+  float ls = 0.f;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) { e[i] = expf(l[i] - mx); ls += e[i]; }  // exp(-inf) = 0 for padding
+  // inclusive scan of lane sums
+  float inc = ls;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const float t = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += t;
+  }
+  const float total = __shfl_sync(0xffffffffu, inc, 31);
+  int tok;
+  if (!sample) {
+    // first index attaining the maximum (torch.argmax tie rule)
+    int best = 0x7fffffff;
+#pragma unroll
+    for (int i = 3; i >= 0; --i) if (l[i] == mx) best = lane * 4 + i;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, o));
+    tok = best;
+  } else {
+    const float target = u * total;
+    float run = inc - ls;  // exclusive prefix
+    int cand = 0x7fffffff;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      run += e[i];
+      if (cand == 0x7fffffff && run > target && lane * 4 + i < V) cand = lane * 4 + i;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) cand = min(cand, __shfl_xor_sync(0xffffffffu, cand, o));
+    tok = (cand == 0x7fffffff) ? V - 1 : cand;
+  }
+  float lt = 0.f;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) if (lane * 4 + i == tok) lt = l[i];
+  lt = __shfl_sync(0xffffffffu, lt, tok >> 2);
+  *logp_out = (lt - mx) - logf(total);
+  return tok;
+}
+
+__device__ __forceinline__ void load_logits_row(const float* __restrict__ row, int lane, int V, float (&l)[4]) {
+  const float4 r = *reinterpret_cast<const float4*>(row + lane * 4);
+  l[0] = r.x; l[1] = r.y; l[2] = r.z; l[3] = r.w;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) if (lane * 4 + i >= V) l[i] = -INFINITY;
+}
+
+// logits: [M, kVPad] fp32 (bias already added).  One warp per sequence.
+__global__ void __launch_bounds__(128)
+head_kernel(DecState* st, const CallParams* cp, const float* __restrict__ logits, unsigned char* fin, int M, int V) {
+  if (st->done) return;
+  const CallParams p = *cp;
+  const int n = st->step;
+  const int m = blockIdx.x * 4 + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (m < M) {
+    float l[4];
+    load_logits_row(logits + (size_t)m * kVPad, lane, V, l);
+    if (p.logits_dump != nullptr) {
+      float* d = p.logits_dump + ((size_t)m * (p.max_len - 1) + n) * V;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) if (lane * 4 + i < V) d[lane * 4 + i] = l[i];
+    }
+    const bool sample = (m % p.group) < p.n_sample;
+    const float u = sample ? philox_uniform(p.seed, p.seq_id_base + (unsigned long long)m, n) : 0.f;
+    float lp;
+    const int tok = warp_pick(l, lane, sample, u, V, &lp);
+    if (lane == 0) {
+      p.ids[(size_t)m * p.max_len + n + 1] = tok;
+      const bool ended = tok == p.end_token;
+      if (sample) {
+        const bool was = fin[m] != 0;
+        if (p.logp != nullptr) p.logp[(size_t)m * (p.max_len - 1) + n] = was ? 0.f : lp;  // scst:239
+        if (ended) fin[m] = 1;
+        if (was || ended) atomicAdd(&st->cnt_finished, 1);
+      } else if (ended) {
+        atomicAdd(&st->cnt_end_now, 1);
+      }
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    const unsigned t = atomicAdd(&st->ticket, 1u);
+    if (t == gridDim.x - 1) {  // last block: evaluate the stop condition, advance the step
+      __threadfence();
+      const int ce = atomicAdd(&st->cnt_end_now, 0), cf = atomicAdd(&st->cnt_finished, 0);
+      if (p.n_greedy_rows > 0 && ce == p.n_greedy_rows) st->greedy_done = 1;  // vit:322
+      if (p.n_sample_rows > 0 && cf == p.n_sample_rows) st->sample_done = 1;  // scst:248
+      st->cnt_end_now = 0; st->cnt_finished = 0; st->ticket = 0u;
+      st->steps_executed = n + 1;
+      st->step = n + 1;
+      if (st->greedy_done && st->sample_done && !p.no_early_stop) st->done = 1;
+      __threadfence();
+    }
+  }
+}
+
+// Stand-alone sampler for capdec_sample_logits: logits [rows, V] (unpadded).
+__global__ void __launch_bounds__(128)
+sample_rows_kernel(const float* __restrict__ logits, int rows, int V, int mode, unsigned long long seed,
+                   unsigned long long seq_id_base, int step, long long* __restrict__ ids, float* __restrict__ logp) {
+  const int r = blockIdx.x * 4 + (threadIdx.x >> 5);
+  if (r >= rows) return;
+  const int lane = threadIdx.x & 31;
+  float l[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int v = lane * 4 + i;
+    l[i] = v < V ? __ldg(logits + (size_t)r * V + v) : -INFINITY;
+  }
+  const float u = mode ? philox_uniform(seed, seq_id_base + (unsigned long long)r, step) : 0.f;
+  float lp;
+  const int tok = warp_pick(l, lane, mode != 0, u, V, &lp);
+  if (lane == 0) { ids[r] = tok; if (logp) logp[r] = lp; }
+}
+
+template <typename Out>
+__global__ void convert_kernel(const float* __restrict__ in, Out* __restrict__ out, size_t n4) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n4) return;
+  const float4 v = __ldg(reinterpret_cast<const float4*>(in) + i);
+  store4(out + i * 4, v.x, v.y, v.z, v.w);
+}
+
+// pack rows [r0, r0+rows) of a [*, cols] fp32 matrix into out (Out), optional zero row padding
+template <typename Out>
+__global__ void pack_rows_kernel(const float* __restrict__ in, Out* __restrict__ out, int rows, int cols, int rows_out) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (size_t)rows_out * cols) return;
+  const int r = (int)(i / cols);
+  out[i] = from_f32<Out>(r < rows ? in[i] : 0.f);
+}
+
+// diagnostics: cache tile [n_images][H][S][64] -> fp32 [n_images, S, 512]
+template <typename Elem>
+__global__ void gather_cross_kernel(const Elem* __restrict__ src, float* __restrict__ out, int n_images, int S) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (size_t)n_images * S * kD) return;
+  const int d = (int)(i % kD);
+  const size_t r = i / kD;
+  const int s = (int)(r % S), img = (int)(r / S);
+  out[i] = to_f32(src[(((size_t)img * kH + (d >> 6)) * S + s) * kHD + (d & 63)]);
+}
+
+}  // namespace capdec

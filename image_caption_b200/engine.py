@@ -1,0 +1,293 @@
+"""Host-side mirror of the reference's decode entry points over libcapdec.so.
+
+``CaptionDecodeEngine`` wraps a live reference decoder module (``model.decoder`` of
+``ViTTransformerCaptioning`` / ``GridTransformerCaptioning``; models/vit_transformer_model.py:103-182,
+models/grid_transformer_model.py:113-158) and serves
+
+* ``generate(model, images, start_token, end_token, max_len=50, method='greedy')``
+  - models/vit_transformer_model.py:276-325, models/grid_transformer_model.py:222-251
+* ``sample_with_log_probs(model, images, start_token, end_token, max_len, device)``
+  - utils/scst_loss.py:202-254
+* ``decode_from_memory(memory, ...)`` - the same loops entered after the encoder, used by the
+  benchmarks and by multi-sample SCST (``group`` rollouts per image sharing one cross K/V).
+
+PyTorch is used for device memory, streams and the (untouched) encoders only; every decode
+kernel lives in the C-ABI library.  There is no CPU or eager fallback.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+from typing import Optional, Tuple
+
+import torch
+
+from . import _lib
+
+_LAYER_FIELDS = (
+    ("self_in_w", "self_attn.in_proj_weight"), ("self_in_b", "self_attn.in_proj_bias"),
+    ("self_out_w", "self_attn.out_proj.weight"), ("self_out_b", "self_attn.out_proj.bias"),
+    ("cross_in_w", "multihead_attn.in_proj_weight"), ("cross_in_b", "multihead_attn.in_proj_bias"),
+    ("cross_out_w", "multihead_attn.out_proj.weight"), ("cross_out_b", "multihead_attn.out_proj.bias"),
+    ("lin1_w", "linear1.weight"), ("lin1_b", "linear1.bias"), ("lin2_w", "linear2.weight"), ("lin2_b", "linear2.bias"),
+)
+
+
+@dataclass
+class Rollout:
+    """Result of one rollout.  ``ids`` (M, L) int64 with column 0 = <start>; ``logp`` (M, L-1)
+    float32 (0 for greedy rows and after a sampled row finished) or None; ``logits`` (M, L-1, V) or
+    None; ``steps`` = L-1."""
+    ids: torch.Tensor
+    logp: Optional[torch.Tensor]
+    steps: int
+    logits: Optional[torch.Tensor] = None
+
+
+def _stream_ptr(device: torch.device) -> int:
+    return torch.cuda.current_stream(device).cuda_stream
+
+
+class CaptionDecodeEngine:
+    def __init__(self, decoder: torch.nn.Module, precision: str = "bf16", max_images: int = 64,
+                 max_group: int = 1, max_mem: int = 196, max_len: int = 50, use_graph: bool = True,
+                 use_umma: bool = True):
+        self._lib = _lib.load()
+        self.decoder = decoder
+        sd = dict(decoder.state_dict())
+        emb = sd["embedding.weight"]
+        if not emb.is_cuda:
+            raise RuntimeError("CaptionDecodeEngine needs the decoder on a CUDA device (no CPU path exists)")
+        self.device = emb.device
+        self.vocab, self.d_model = emb.shape
+        self.n_layer = len(decoder.transformer_decoder.layers)
+        first = decoder.transformer_decoder.layers[0]
+        self.n_head = first.self_attn.num_heads
+        self.d_ff = first.linear1.out_features
+        self.pe_rows = sd["pos_encoder.pe"].shape[1]
+        if getattr(first, "norm_first", False):
+            raise ValueError("only post-LN decoder layers (norm_first=False) are supported, as in the reference")
+        if precision not in ("bf16", "fp32"):
+            raise ValueError(f"precision must be 'bf16' or 'fp32', got {precision!r}")
+        self.precision = precision
+        self._flags = (0 if use_graph else _lib.FLAG_NO_GRAPH) | (0 if use_umma else _lib.FLAG_NO_UMMA)
+        self._cap = dict(max_images=max_images, max_group=max_group, max_mem=max_mem, max_len=max_len)
+        self._h = C.c_void_p()
+        self._weights_sig = None
+        self._keep = []  # fp32 contiguous views handed to set_weights
+        self._create()
+
+    # ------------------------------------------------------------------ handle management
+    def _create(self) -> None:
+        cfg = _lib.Config(vocab=self.vocab, d_model=self.d_model, n_head=self.n_head, n_layer=self.n_layer,
+                          d_ff=self.d_ff, pe_rows=self.pe_rows, max_mem=self._cap["max_mem"],
+                          max_images=self._cap["max_images"], max_group=self._cap["max_group"],
+                          max_len=self._cap["max_len"],
+                          precision=_lib.PREC_BF16 if self.precision == "bf16" else _lib.PREC_FP32,
+                          flags=self._flags)
+        h = C.c_void_p()
+        rc = self._lib.capdec_create(C.byref(cfg), self.device.index or 0, C.byref(h))
+        _lib.check(None, rc)
+        self._h = h
+        self._weights_sig = None
+
+    def close(self) -> None:
+        if getattr(self, "_h", None) is not None and self._h.value:
+            self._lib.capdec_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _ensure_capacity(self, n_images: int, group: int, mem_len: int, max_len: int) -> None:
+        need = dict(max_images=n_images, max_group=group, max_mem=mem_len, max_len=max_len)
+        if all(need[k] <= self._cap[k] for k in need):
+            return
+        torch.cuda.synchronize(self.device)
+        self.close()
+        self._cap = {k: max(self._cap[k], need[k]) for k in need}
+        self._create()
+
+    # ------------------------------------------------------------------ weights
+    def _signature(self):
+        return tuple((p.data_ptr(), p._version) for p in self.decoder.state_dict().values())
+
+    def sync_weights(self, force: bool = False) -> None:
+        """Re-pack the module's parameters if any was updated in place (optimiser step) or rebound
+        (EMA ``apply_shadow``/``restore``, utils/optimizations.py:444-456)."""
+        sig = self._signature()
+        if not force and sig == self._weights_sig:
+            return
+        sd = self.decoder.state_dict()
+        keep = []
+
+        def ptr(name: str) -> int:
+            t = sd[name].detach()
+            if t.device != self.device:
+                raise RuntimeError(f"parameter {name} is on {t.device}, engine on {self.device}")
+            t = t.to(torch.float32).contiguous()
+            keep.append(t)
+            return t.data_ptr()
+
+        w = _lib.Weights()
+        w.embedding, w.pe = ptr("embedding.weight"), ptr("pos_encoder.pe")
+        w.fc_out_w, w.fc_out_b = ptr("fc_out.weight"), ptr("fc_out.bias")
+        for i in range(self.n_layer):
+            pre = f"transformer_decoder.layers.{i}."
+            lw = w.layer[i]
+            for field, key in _LAYER_FIELDS:
+                setattr(lw, field, ptr(pre + key))
+            for j in range(3):
+                lw.norm_w[j] = ptr(f"{pre}norm{j + 1}.weight")
+                lw.norm_b[j] = ptr(f"{pre}norm{j + 1}.bias")
+        _lib.check(self._h, self._lib.capdec_set_weights(self._h, C.byref(w), _stream_ptr(self.device)))
+        self._keep = keep  # released on the next repack; the pack kernels are stream-ordered before that
+        self._weights_sig = sig
+
+    # ------------------------------------------------------------------ decode
+    def _check_lengths(self, max_len: int) -> None:
+        if max_len < 2:
+            raise ValueError("max_len must be >= 2")
+        if max_len - 1 > self.pe_rows:  # the reference fails with a shape error at vit:32
+            raise ValueError(f"max_len={max_len} needs {max_len - 1} positions but pos_encoder.pe has {self.pe_rows}")
+        if max_len > 128:
+            raise ValueError("max_len > 128 is not built")
+
+    def decode_from_memory(self, memory: torch.Tensor, start_token: int, end_token: int, max_len: int = 50,
+                           group: int = 1, n_sample: int = 0, seed: int = 0, seq_id_base: int = 0,
+                           pad_token: int = 0, return_logits: bool = False, trim: bool = True,
+                           early_stop: bool = True) -> Rollout:
+        """Decode ``group`` sequences per image of ``memory`` (B, S, 512) float32: rows ``g < n_sample``
+        of each group are sampled, the rest greedy.  A CUDA ``memory`` runs on the current stream and
+        returns CUDA tensors; a CPU ``memory`` takes the host-buffer entry point
+        (capdec_generate_host) and returns CPU tensors."""
+        if memory.dim() != 3 or memory.shape[2] != self.d_model:
+            raise ValueError(f"memory must be (B, S, {self.d_model}), got {tuple(memory.shape)}")
+        self._check_lengths(max_len)
+        n_images, mem_len = memory.shape[0], memory.shape[1]
+        m = n_images * group
+        self._ensure_capacity(n_images, group, mem_len, max_len)
+        self.sync_weights()
+        memory = memory.detach().to(torch.float32).contiguous()
+        steps = C.c_int32(0)
+        args = _lib.DecodeArgs(group=group, n_sample=n_sample, start_token=start_token, end_token=end_token,
+                               pad_token=pad_token, max_len=max_len, seed=seed, seq_id_base=seq_id_base,
+                               flags=0 if early_stop else _lib.DECODE_NO_EARLY_STOP,
+                               steps_out=C.pointer(steps))
+        want_logp = n_sample > 0
+        stream = _stream_ptr(self.device)
+        if memory.is_cuda:
+            if memory.device != self.device:
+                raise RuntimeError("memory and decoder are on different devices")
+            ids = torch.empty((m, max_len), dtype=torch.int64, device=self.device)
+            logp = torch.empty((m, max_len - 1), dtype=torch.float32, device=self.device) if want_logp else None
+            logits = (torch.empty((m, max_len - 1, self.vocab), dtype=torch.float32, device=self.device)
+                      if return_logits else None)
+            args.ids_out = ids.data_ptr()
+            args.logp_out = logp.data_ptr() if want_logp else None
+            args.logits_out = logits.data_ptr() if return_logits else None
+            _lib.check(self._h, self._lib.capdec_prefill(self._h, memory.data_ptr(), n_images, mem_len, stream))
+            _lib.check(self._h, self._lib.capdec_decode(self._h, C.byref(args), stream))
+        else:
+            if return_logits:
+                raise ValueError("return_logits needs a CUDA memory tensor")
+            ids = torch.empty((m, max_len), dtype=torch.int64, pin_memory=True)
+            logp = torch.empty((m, max_len - 1), dtype=torch.float32, pin_memory=True) if want_logp else None
+            logits = None
+            args.ids_out = ids.data_ptr()
+            args.logp_out = logp.data_ptr() if want_logp else None
+            _lib.check(self._h, self._lib.capdec_generate_host(self._h, memory.data_ptr(), n_images, mem_len,
+                                                               C.byref(args), stream))
+        n = int(steps.value)
+        if trim:
+            ids = ids[:, :n + 1]
+            logp = logp[:, :n] if logp is not None else None
+            logits = logits[:, :n] if logits is not None else None
+        return Rollout(ids=ids, logp=logp, steps=n, logits=logits)
+
+    # ------------------------------------------------------------------ reference-facing entry points
+    @torch.no_grad()
+    def generate(self, model: torch.nn.Module, images: torch.Tensor, start_token: int, end_token: int,
+                 max_len: int = 50, method: str = "greedy", beam_size: int = 5) -> torch.Tensor:
+        """Drop-in for ``model.generate`` (vit:276-294 / grid:222-228).  Greedy runs on the engine;
+        ``beam_search`` is delegated to the reference's own implementation."""
+        if method == "greedy":
+            model.eval()  # vit:298 - a side effect the reference never undoes
+            memory = model.encoder(images)
+            return self.decode_from_memory(memory, start_token, end_token, max_len).ids
+        if method == "beam_search":
+            ref = getattr(model, "_capdec_reference_generate", None)
+            if ref is None:
+                raise NotImplementedError("beam_search is served by the reference implementation; install() keeps it")
+            try:
+                return ref(images, start_token, end_token, max_len, method="beam_search", beam_size=beam_size)
+            except TypeError:  # ViT signature has no beam_size (vit:276)
+                return ref(images, start_token, end_token, max_len, method="beam_search")
+        raise ValueError(f"Unknown generation method: {method}")
+
+    def sample_with_log_probs(self, model: torch.nn.Module, images: torch.Tensor, start_token: int,
+                              end_token: int, max_len: int, device=None, seed: Optional[int] = None
+                              ) -> Tuple[torch.Tensor, torch.Tensor]:
+        """Drop-in for ``SCSTLoss._sample_with_log_probs`` (scst:202-254).
+
+        The rollout samples from the eval-mode distribution on the engine.  When autograd is
+        enabled the returned log-probs are recomputed by ONE teacher-forced pass of the reference
+        decoder over the sampled ids (row k of that pass is the step-k distribution), so
+        ``loss.backward()`` reaches decoder and encoder exactly as scst:183-191 expects."""
+        memory = model.encoder(images)  # scst:213
+        if seed is None:
+            seed = int(torch.randint(0, 2 ** 62, (1,)).item())  # follows torch's global generator
+        out = self.decode_from_memory(memory, start_token, end_token, max_len, group=1, n_sample=1, seed=seed)
+        if not torch.is_grad_enabled():
+            return out.ids, out.logp
+        ids = out.ids
+        t = ids.size(1) - 1
+        mask = model.decoder.generate_square_subsequent_mask(t, ids.device)
+        logits = model.decoder(ids[:, :-1], memory, tgt_mask=mask)
+        lp = torch.log_softmax(logits, dim=-1).gather(2, ids[:, 1:, None]).squeeze(2)
+        ended = ids[:, 1:] == end_token
+        finished_before = (ended.cumsum(1) - ended.long()) > 0  # finished strictly before this step
+        return ids, lp.masked_fill(finished_before, 0.0)
+
+    # ------------------------------------------------------------------ diagnostics
+    def launch_count(self) -> int:
+        return int(self._lib.capdec_launch_count(self._h))
+
+    def sample_logits(self, logits: torch.Tensor, mode: int, seed: int = 0, seq_id_base: int = 0, step: int = 0):
+        logits = logits.to(self.device, torch.float32).contiguous()
+        if logits.dim() != 2 or logits.shape[1] != self.vocab:
+            raise ValueError("logits must be (rows, vocab)")
+        ids = torch.empty(logits.shape[0], dtype=torch.int64, device=self.device)
+        lp = torch.empty(logits.shape[0], dtype=torch.float32, device=self.device)
+        _lib.check(self._h, self._lib.capdec_sample_logits(self._h, logits.data_ptr(), logits.shape[0], mode, seed,
+                                                           seq_id_base, step, ids.data_ptr(), lp.data_ptr(),
+                                                           _stream_ptr(self.device)))
+        return ids, lp
+
+    def debug_gemm(self, a: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = None, relu: bool = False):
+        a = a.to(self.device, torch.float32).contiguous()
+        w = w.to(self.device, torch.float32).contiguous()
+        bias = bias.to(self.device, torch.float32).contiguous() if bias is not None else None
+        c = torch.empty((a.shape[0], w.shape[0]), dtype=torch.float32, device=self.device)
+        _lib.check(self._h, self._lib.capdec_debug_gemm(self._h, a.data_ptr(), w.data_ptr(),
+                                                        bias.data_ptr() if bias is not None else None, c.data_ptr(),
+                                                        a.shape[0], w.shape[0], a.shape[1], int(relu),
+                                                        _stream_ptr(self.device)))
+        return c
+
+    def debug_cross_kv(self, layer: int, which: int, n_images: int, mem_len: int) -> torch.Tensor:
+        out = torch.empty((n_images, mem_len, self.d_model), dtype=torch.float32, device=self.device)
+        _lib.check(self._h, self._lib.capdec_debug_cross_kv(self._h, layer, which, out.data_ptr(),
+                                                            _stream_ptr(self.device)))
+        return out
+
+    def prefill(self, memory: torch.Tensor) -> None:
+        memory = memory.detach().to(self.device, torch.float32).contiguous()
+        self._ensure_capacity(memory.shape[0], 1, memory.shape[1], 2)
+        self.sync_weights()
+        self._keep_mem = memory
+        _lib.check(self._h, self._lib.capdec_prefill(self._h, memory.data_ptr(), memory.shape[0], memory.shape[1],
+                                                     _stream_ptr(self.device)))

@@ -1,0 +1,168 @@
+/*
+ * capdec.h - C ABI of the B200-native caption decode engine (libcapdec.so).
+ *
+ * Drop-in boundary for the batched autoregressive decoding path of
+ * wonder-dream/image_caption.  Plain pointers and sizes only; no torch types, no C++
+ * exceptions cross this boundary.  Every entry point returns 0 on success or a negative
+ * capdec_status; capdec_last_error() gives the text.
+ *
+ * What each entry point replaces in the reference (paths relative to the reference root):
+ *   capdec_set_weights   the decoder's nn.Module parameters, read by state-dict name
+ *                        (models/vit_transformer_model.py:111-139, grid_transformer_model.py:119-134)
+ *   capdec_prefill       the memory->K,V projection torch redoes inside every decoder call
+ *                        (vit_transformer_model.py:312 -> nn.TransformerDecoderLayer._mha_block)
+ *   capdec_decode        the greedy loop  vit_transformer_model.py:307-323 / grid_transformer_model.py:237-249
+ *                        and the sampling loop utils/scst_loss.py:216-252 (one call = one rollout)
+ *   capdec_generate_host the same two loops entered with HOST buffers (what generate()/SCSTLoss see
+ *                        when tensors live on the CPU): H2D, prefill, decode, D2H in one call
+ *   capdec_sample_logits softmax + multinomial + log_softmax.gather of utils/scst_loss.py:229-239
+ *                        on caller-provided logits (used to test the sampling distribution)
+ *
+ * Sequences are image-major: sequence m belongs to image m / group; inside a group rows
+ * g < n_sample are sampled (scst semantics: cumulative `finished`, log-prob 0 once finished),
+ * rows g >= n_sample are greedy (vit semantics).  Plain greedy = {group 1, n_sample 0}; the
+ * reference's single-sample rollout = {group 1, n_sample 1}; multi-sample SCST with a greedy
+ * baseline (BASELINE.json config 3) = {group 6, n_sample 5}.
+ *
+ * Threading: one handle per (process, device); calls on one handle must be serialised by the
+ * caller.  Work is enqueued on the caller's stream; only capdec_decode's read-back of the
+ * step count and capdec_generate_host synchronise.
+ */
+#ifndef CAPDEC_H_
+#define CAPDEC_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CAPDEC_ABI_VERSION 1
+#define CAPDEC_MAX_LAYERS 12
+
+typedef struct capdec_engine* capdec_handle;
+
+typedef enum {
+  CAPDEC_OK = 0,
+  CAPDEC_ERR_INVALID = -1,     /* bad argument / unsupported shape                */
+  CAPDEC_ERR_CUDA = -2,        /* a CUDA runtime/driver call failed               */
+  CAPDEC_ERR_STATE = -3,       /* call order violated (e.g. decode before prefill) */
+  CAPDEC_ERR_CAPACITY = -4,    /* exceeds the sizes given to capdec_create         */
+  CAPDEC_ERR_NO_DEVICE = -5    /* no usable sm_100 device                          */
+} capdec_status;
+
+typedef enum {
+  CAPDEC_PREC_FP32 = 0, /* fp32 weights / KV / CUDA-core GEMMs: the strict-parity mode         */
+  CAPDEC_PREC_BF16 = 1  /* bf16 weights / KV, tcgen05 GEMMs with fp32 accumulate; fp32 residual */
+} capdec_precision;
+
+typedef struct {
+  int32_t vocab;       /* V   (data/vocab.json: 109)                          */
+  int32_t d_model;     /* must be 512                                          */
+  int32_t n_head;      /* must be 8 (head dim 64)                              */
+  int32_t n_layer;     /* 1..CAPDEC_MAX_LAYERS                                 */
+  int32_t d_ff;        /* multiple of 64                                       */
+  int32_t pe_rows;     /* rows of pos_encoder.pe (the model's max_len)         */
+  int32_t max_mem;     /* largest memory length S (196 ViT, 49 grid)           */
+  int32_t max_images;  /* largest number of images per call                    */
+  int32_t max_group;   /* largest sequences-per-image                          */
+  int32_t max_len;     /* largest generate(max_len=...)                        */
+  int32_t precision;   /* capdec_precision                                     */
+  int32_t flags;       /* CAPDEC_FLAG_*                                        */
+} capdec_config;
+
+#define CAPDEC_FLAG_NO_GRAPH 1   /* launch step kernels directly instead of replaying a CUDA graph */
+#define CAPDEC_FLAG_NO_UMMA 2    /* bf16 mode: route GEMMs through the CUDA-core kernel (debug)     */
+
+/* fp32 DEVICE pointers, borrowed for the duration of capdec_set_weights only. */
+typedef struct {
+  const float* self_in_w;   /* [3D, D]  self_attn.in_proj_weight       */
+  const float* self_in_b;   /* [3D]                                      */
+  const float* self_out_w;  /* [D, D]   self_attn.out_proj.weight      */
+  const float* self_out_b;  /* [D]                                       */
+  const float* cross_in_w;  /* [3D, D]  multihead_attn.in_proj_weight  */
+  const float* cross_in_b;  /* [3D]                                      */
+  const float* cross_out_w; /* [D, D]   multihead_attn.out_proj.weight */
+  const float* cross_out_b; /* [D]                                       */
+  const float* lin1_w;      /* [F, D]   linear1.weight                  */
+  const float* lin1_b;      /* [F]                                       */
+  const float* lin2_w;      /* [D, F]   linear2.weight                  */
+  const float* lin2_b;      /* [D]                                       */
+  const float* norm_w[3];   /* [D]      norm1/2/3.weight                */
+  const float* norm_b[3];   /* [D]      norm1/2/3.bias                  */
+} capdec_layer_weights;
+
+typedef struct {
+  const float* embedding;   /* [V, D]        embedding.weight  */
+  const float* pe;          /* [pe_rows, D]  pos_encoder.pe    */
+  const float* fc_out_w;    /* [V, D]        fc_out.weight     */
+  const float* fc_out_b;    /* [V]           fc_out.bias       */
+  capdec_layer_weights layer[CAPDEC_MAX_LAYERS];
+} capdec_weights;
+
+typedef struct {
+  int32_t group;        /* sequences per image (>= 1)                                          */
+  int32_t n_sample;     /* rows g < n_sample of each group are sampled, the rest greedy        */
+  int32_t start_token;
+  int32_t end_token;
+  int32_t pad_token;    /* fills ids_out beyond the last executed step                         */
+  int32_t max_len;      /* as generate(max_len=...): at most max_len-1 steps                   */
+  int32_t flags;        /* CAPDEC_DECODE_*                                                      */
+  int32_t reserved;     /* must be 0                                                            */
+  uint64_t seed;        /* Philox key                                                           */
+  uint64_t seq_id_base; /* global index of this call's first sequence (sharding invariance)    */
+  int64_t* ids_out;     /* [n_seq, max_len]                                                     */
+  float* logp_out;      /* [n_seq, max_len-1] or NULL; 0 for greedy rows and finished rows      */
+  float* logits_out;    /* NULL, or [n_seq, max_len-1, vocab]: every step's logits (parity)     */
+  int32_t* steps_out;   /* HOST int: number of steps executed (L = steps+1); may be NULL       */
+} capdec_decode_args;
+
+/* Run all max_len-1 steps even if the stop condition is met (sharded greedy rollouts: the
+ * global "all rows emit <end> on one step" test of vit:322 needs every rank's later tokens). */
+#define CAPDEC_DECODE_NO_EARLY_STOP 1
+
+int capdec_abi_version(void);
+const char* capdec_last_error(capdec_handle h); /* h may be NULL: error of a failed create */
+
+int capdec_create(const capdec_config* cfg, int device, capdec_handle* out);
+int capdec_destroy(capdec_handle h);
+
+/* Re-pack (and in bf16 mode round) the module's fp32 parameters into engine-owned buffers. */
+int capdec_set_weights(capdec_handle h, const capdec_weights* w, void* cuda_stream);
+
+/* memory: DEVICE fp32 [n_images, mem_len, D] contiguous.  Projects it once to every layer's
+ * cross-attention K and V. */
+int capdec_prefill(capdec_handle h, const float* memory, int32_t n_images, int32_t mem_len, void* cuda_stream);
+
+/* One rollout over the images of the last prefill.  ids_out/logp_out/logits_out are DEVICE
+ * pointers.  Synchronises the stream only if steps_out != NULL. */
+int capdec_decode(capdec_handle h, const capdec_decode_args* args, void* cuda_stream);
+
+/* Same with HOST pointers for memory, ids_out, logp_out (logits_out must be NULL): copies in,
+ * prefills, decodes, copies out and synchronises. */
+int capdec_generate_host(capdec_handle h, const float* memory_host, int32_t n_images, int32_t mem_len,
+                         const capdec_decode_args* args_host, void* cuda_stream);
+
+/* Sampler alone: logits DEVICE fp32 [n_rows, vocab]; row r uses sequence id seq_id_base + r.
+ * mode 0 = argmax, 1 = sample.  ids_out DEVICE int64 [n_rows], logp_out DEVICE fp32 [n_rows] or NULL. */
+int capdec_sample_logits(capdec_handle h, const float* logits, int32_t n_rows, int32_t mode, uint64_t seed,
+                         uint64_t seq_id_base, int32_t step, int64_t* ids_out, float* logp_out, void* cuda_stream);
+
+/* Number of kernels this handle has launched (graph replays count their kernel nodes). */
+int64_t capdec_launch_count(capdec_handle h);
+
+/* ---- diagnostics (used by the parity tests; not part of the reference-facing surface) ---- */
+
+/* C[M,N] = A[M,K] * W[N,K]^T + bias through the engine's GEMM of the handle's precision
+ * (bf16 mode: operands are rounded to bf16, tcgen05 path).  All DEVICE fp32. relu: 0/1. */
+int capdec_debug_gemm(capdec_handle h, const float* a, const float* w, const float* bias, float* c,
+                      int32_t m, int32_t n, int32_t k, int32_t relu, void* cuda_stream);
+
+/* Copy layer `layer`'s cross K (which=0) or V (which=1) of the last prefill to out as DEVICE fp32
+ * [n_images, mem_len, D] (the reference's memory @ W^T + b layout). */
+int capdec_debug_cross_kv(capdec_handle h, int32_t layer, int32_t which, float* out, void* cuda_stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CAPDEC_H_ */
