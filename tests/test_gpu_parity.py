@@ -1,0 +1,297 @@
+"""Parity of the CUDA path (through the C ABI) against the CPU oracle.  Run on the B200 box:
+    python -m pytest tests -m gpu
+
+Tolerances (stated once, used everywhere):
+  fp32 mode  max |logit - oracle| <= 2e-4   (summation-order differences only; measured ~1e-5)
+  bf16 mode  max |logit - oracle| <= 1e-1   (weights, KV and GEMM inputs rounded to bf16, fp32
+             accumulate; weight rounding alone moves logits by 2.2e-2)
+Greedy ids must equal argmax of the oracle's logits wherever the oracle's top-2 gap exceeds
+twice the mode's tolerance; sampled log-probs must equal log_softmax(oracle logits)[id] within the
+tolerance and be exactly 0 after a row's <end>.  All checks are teacher-forced on the engine's own
+ids so that one legitimate near-tie cannot cascade.
+"""
+import numpy as np
+import pytest
+import torch
+
+from conftest import END, PAD, START, VOCAB
+from oracle import decoder_np, philox, torch_port
+
+pytestmark = pytest.mark.gpu
+
+TOL = {"fp32": 2e-4, "bf16": 1e-1}
+
+
+@pytest.fixture(scope="module")
+def dev():
+    return torch.device("cuda:0")
+
+
+def make_engine(dec, precision, **kw):
+    from image_caption_b200 import CaptionDecodeEngine
+    return CaptionDecodeEngine(dec, precision=precision, **kw)
+
+
+def small_decoder(seed=1, layers=2, pe_rows=24, end_bias=0.0):
+    dec = torch_port.build_decoder(seed, num_layers=layers, max_len=pe_rows, perturb=0.02)
+    with torch.no_grad():
+        dec.fc_out.bias[END] += end_bias
+    return dec
+
+
+def oracle_logits(w, ids, mem, group):
+    memr = np.repeat(mem, group, 0) if group > 1 else mem
+    return decoder_np.decoder_forward(w, ids[:, :-1], memr)
+
+
+def check_rollout(out, w, mem, group, n_sample, tol, seed=0, seq_id_base=0):
+    ids = out.ids.cpu().numpy()
+    m, L = ids.shape
+    assert L == out.steps + 1 and (ids[:, 0] == START).all()
+    ref = oracle_logits(w, ids, mem, group)
+    if out.logits is not None:
+        err = np.abs(out.logits.cpu().numpy() - ref).max()
+        assert err <= tol, f"logits differ by {err}"
+    is_sample = (np.arange(m) % group) < n_sample
+    # greedy rows: argmax of the oracle's logits unless the oracle's top-2 gap is inside the tolerance
+    srt = np.sort(ref, -1)
+    gap = srt[..., -1] - srt[..., -2]
+    want = ref.argmax(-1)
+    g = ~is_sample
+    bad = (ids[g, 1:] != want[g]) & (gap[g] > 2 * tol)
+    assert not bad.any(), f"{bad.sum()} greedy tokens differ outside the tie tolerance"
+    if n_sample:
+        lp = out.logp.cpu().numpy()
+        lsm = decoder_np.log_softmax(ref)
+        tok = ids[:, 1:]
+        picked = np.take_along_axis(lsm, tok[..., None], -1)[..., 0]
+        ended = tok == END
+        after = (np.cumsum(ended, 1) - ended) > 0
+        s = is_sample
+        assert (lp[s][after[s]] == 0).all(), "log-prob after <end> must be exactly 0 (scst:239)"
+        live = ~after[s]
+        assert np.abs(lp[s][live] - picked[s][live]).max() <= tol
+        assert (lp[g] == 0).all()
+        # the draw itself: Philox uniform + inverse CDF on the engine's own logits
+        if out.logits is not None:
+            el = out.logits.cpu().numpy()
+            rows = np.nonzero(s)[0]
+            for n in range(L - 1):
+                u = philox.uniform(seed, seq_id_base + rows.astype(np.uint64), n)
+                ok = philox.draw_consistent(el[rows, n], u, tok[rows, n])
+                assert ok.all(), f"step {n}: draws inconsistent with Philox/inverse-CDF"
+    return ref
+
+
+# ------------------------------------------------------------------ building blocks
+@pytest.mark.parametrize("precision,umma", [("fp32", True), ("bf16", True), ("bf16", False)])
+@pytest.mark.parametrize("m,n,k", [(5, 128, 512), (128, 512, 512), (300, 1536, 512), (257, 512, 2048), (1000, 2048, 512)])
+def test_gemm(dev, precision, umma, m, n, k):
+    eng = make_engine(small_decoder(layers=1).to(dev), precision, use_umma=umma, max_images=1, max_mem=1, max_len=4)
+    g = torch.Generator().manual_seed(m + n)
+    a = torch.randn(m, k, generator=g)
+    w = torch.randn(n, k, generator=g) * 0.05
+    b = torch.randn(n, generator=g)
+    for relu in (False, True):
+        c = eng.debug_gemm(a.to(dev), w.to(dev), b.to(dev), relu=relu).cpu()
+        if precision == "bf16":
+            ref = a.bfloat16().double() @ w.bfloat16().double().T + b.double()
+        else:
+            ref = a.double() @ w.double().T + b.double()
+        ref = ref.clamp_min(0) if relu else ref
+        assert (c.double() - ref).abs().max() < 2e-4, (precision, umma, m, n, k)
+    eng.close()
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_prefill_cross_kv(dev, precision):
+    dec = small_decoder(layers=3)
+    w = torch_port.weights_to_numpy(dec)
+    mem = torch_port.synthetic_memory(5, 49)
+    eng = make_engine(dec.to(dev), precision, max_images=8, max_mem=49)
+    eng.prefill(mem.to(dev))
+    tol = 1e-4 if precision == "fp32" else 6e-2
+    for layer in range(3):
+        wi = w[f"transformer_decoder.layers.{layer}.multihead_attn.in_proj_weight"]
+        bi = w[f"transformer_decoder.layers.{layer}.multihead_attn.in_proj_bias"]
+        for which in (0, 1):
+            lo = 512 * (1 + which)
+            ref = mem.numpy() @ wi[lo:lo + 512].T + bi[lo:lo + 512]
+            got = eng.debug_cross_kv(layer, which, 5, 49).cpu().numpy()
+            assert np.abs(got - ref).max() < tol, (layer, which)
+    eng.close()
+
+
+def test_sampler_distribution(dev):
+    """chi-square goodness of fit of 2^20 engine draws against softmax(logits)."""
+    eng = make_engine(small_decoder(layers=1).to(dev), "fp32", max_images=1, max_mem=1, max_len=4)
+    g = torch.Generator().manual_seed(3)
+    row = torch.randn(VOCAB, generator=g) * 1.3
+    n = 1 << 20
+    ids, lp = eng.sample_logits(row.repeat(n, 1), mode=1, seed=2024, seq_id_base=77, step=3)
+    ids = ids.cpu().numpy()
+    p = torch.softmax(row.double(), 0).numpy()
+    cnt = np.bincount(ids, minlength=VOCAB)
+    chi2 = ((cnt - n * p) ** 2 / (n * p)).sum()
+    # dof = 108: mean 108, sd 14.7; 180 is ~5 sigma
+    assert chi2 < 180, chi2
+    assert np.abs(cnt / n - p).max() < 4 * np.sqrt(p.max() / n) + 1e-4
+    # exact agreement with the restated scheme
+    u = philox.uniform(2024, 77 + np.arange(4096, dtype=np.uint64), 3)
+    assert philox.draw_consistent(np.tile(row.numpy(), (4096, 1)), u, ids[:4096]).all()
+    want = torch.log_softmax(row, 0)[torch.from_numpy(ids[:4096])]
+    assert (lp[:4096].cpu() - want).abs().max() < 1e-5
+    a_ids, _ = eng.sample_logits(row.repeat(8, 1), mode=0)
+    assert (a_ids.cpu() == row.argmax()).all()
+    eng.close()
+
+
+# ------------------------------------------------------------------ rollouts
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+@pytest.mark.parametrize("mem_len", [49, 196])
+def test_greedy_rollout(dev, precision, mem_len):
+    dec = small_decoder(layers=3)
+    w = torch_port.weights_to_numpy(dec)
+    mem = torch_port.synthetic_memory(6, mem_len)
+    eng = make_engine(dec.to(dev), precision, max_images=8, max_mem=mem_len, max_len=16)
+    out = eng.decode_from_memory(mem.to(dev), START, END, max_len=16, return_logits=True)
+    assert out.logp is None
+    check_rollout(out, w, mem.numpy(), 1, 0, TOL[precision])
+    if precision == "fp32":  # end to end against the reference-form loop
+        ref_ids = decoder_np.greedy_search(w, mem.numpy(), START, END, 16)
+        np.testing.assert_array_equal(out.ids.cpu().numpy(), ref_ids)
+    eng.close()
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_sampled_rollout_stops_and_zeroes(dev, precision):
+    dec = small_decoder(layers=2, end_bias=4.0)  # <end> is likely: rows finish, rollout stops early
+    w = torch_port.weights_to_numpy(dec)
+    mem = torch_port.synthetic_memory(7, 49)
+    eng = make_engine(dec.to(dev), precision, max_images=8, max_mem=49, max_len=24)
+    out = eng.decode_from_memory(mem.to(dev), START, END, max_len=24, group=1, n_sample=1, seed=99,
+                                 seq_id_base=1000, return_logits=True)
+    ids = out.ids.cpu().numpy()
+    assert out.steps < 23, "with end_bias=4 every row should finish early"
+    fin = (np.cumsum(ids[:, 1:] == END, 1) > 0)
+    assert fin[:, -1].all() and not fin[:, -2].all(), "stops at the first step where all rows finished (scst:248)"
+    check_rollout(out, w, mem.numpy(), 1, 1, TOL[precision], seed=99, seq_id_base=1000)
+    eng.close()
+
+
+def test_greedy_early_exit_matches_reference_rule(dev):
+    """vit:322 - stop only when ALL rows emit <end> on the same step."""
+    dec = small_decoder(layers=2, end_bias=6.0)
+    w = torch_port.weights_to_numpy(dec)
+    mem = torch_port.synthetic_memory(5, 49)
+    ref_ids = decoder_np.greedy_search(w, mem.numpy(), START, END, 20)
+    eng = make_engine(dec.to(dev), "fp32", max_images=8, max_mem=49, max_len=20)
+    out = eng.decode_from_memory(mem.to(dev), START, END, max_len=20)
+    np.testing.assert_array_equal(out.ids.cpu().numpy(), ref_ids)
+    assert ref_ids.shape[1] < 20
+    full = eng.decode_from_memory(mem.to(dev), START, END, max_len=20, early_stop=False, trim=False)
+    assert full.steps == 19 and full.ids.shape[1] == 20
+    np.testing.assert_array_equal(full.ids.cpu().numpy()[:, :ref_ids.shape[1]], ref_ids)
+    eng.close()
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+@pytest.mark.parametrize("group,n_sample", [(6, 5), (4, 2), (3, 3), (2, 0)])
+def test_grouped_rollout_shares_cross_kv(dev, precision, group, n_sample):
+    dec = small_decoder(layers=2, end_bias=2.0)
+    w = torch_port.weights_to_numpy(dec)
+    mem = torch_port.synthetic_memory(4, 49)
+    eng = make_engine(dec.to(dev), precision, max_images=4, max_group=6, max_mem=49, max_len=14)
+    out = eng.decode_from_memory(mem.to(dev), START, END, max_len=14, group=group, n_sample=n_sample, seed=5,
+                                 return_logits=True)
+    check_rollout(out, w, mem.numpy(), group, n_sample, TOL[precision], seed=5)
+    if precision == "fp32":  # the oracle's grouped rollout, driven by the same Philox scheme
+        ids, lp, steps, _ = decoder_np.rollout_cached(w, mem.numpy(), START, END, 14, group, n_sample,
+                                                      draw=philox.make_draw(5))
+        assert steps == out.steps
+        same = out.ids.cpu().numpy() == ids[:, :steps + 1]
+        assert same.mean() > 0.98  # identical unless a draw sits on a float32 CDF boundary
+    eng.close()
+
+
+def test_golden_fixtures_fp32(dev, golden_case):
+    """Engine against outputs of the real reference (tests/golden)."""
+    name, z, dec, mem = golden_case
+    max_len = int(z["max_len"])
+    eng = make_engine(dec.to(dev), "fp32", max_images=8, max_mem=int(z["mem_len"]), max_len=max_len)
+    out = eng.decode_from_memory(mem.to(dev), START, END, max_len=max_len, return_logits=True)
+    np.testing.assert_array_equal(out.ids.cpu().numpy(), z["greedy_ids"])
+    # sampled ids of the reference replayed teacher-forced: its log-probs from our logits
+    w = torch_port.weights_to_numpy(dec)
+    ref_l = z["sample_logits"]
+    mine = decoder_np.decoder_forward(w, z["sample_ids"][:, :-1], mem.numpy())
+    assert np.abs(mine - ref_l).max() < 3e-5
+    eng.close()
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_graph_and_direct_launch_agree(dev, precision):
+    dec = small_decoder(layers=2).to(dev)
+    mem = torch_port.synthetic_memory(3, 49).to(dev)
+    outs = []
+    for use_graph in (True, False):
+        eng = make_engine(dec, precision, use_graph=use_graph, max_images=4, max_group=2, max_mem=49, max_len=10)
+        o = eng.decode_from_memory(mem, START, END, max_len=10, group=2, n_sample=1, seed=1, return_logits=True)
+        outs.append((o.ids.cpu(), o.logits.cpu(), o.logp.cpu()))
+        assert eng.launch_count() > 0
+        eng.close()
+    assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1]) and torch.equal(outs[0][2], outs[1][2])
+
+
+def test_bf16_simt_route_matches_umma_route(dev):
+    dec = small_decoder(layers=2).to(dev)
+    mem = torch_port.synthetic_memory(3, 49).to(dev)
+    res = []
+    for umma in (True, False):
+        eng = make_engine(dec, "bf16", use_umma=umma, max_images=4, max_mem=49, max_len=10)
+        res.append(eng.decode_from_memory(mem, START, END, max_len=10, return_logits=True).logits.cpu())
+        eng.close()
+    assert (res[0] - res[1]).abs().max() < 2e-2  # same roundings, different summation order
+
+
+def test_weight_updates_are_picked_up(dev):
+    """Optimiser steps mutate parameters in place; EMA rebinds param.data (optimizations.py:444-456)."""
+    dec = small_decoder(layers=2).to(dev)
+    mem = torch_port.synthetic_memory(3, 49)
+    eng = make_engine(dec, "fp32", max_images=4, max_mem=49, max_len=8)
+    a = eng.decode_from_memory(mem.to(dev), START, END, max_len=8, return_logits=True).logits.cpu()
+    with torch.no_grad():
+        dec.fc_out.bias.add_(torch.linspace(-1, 1, VOCAB, device=dev))  # in place
+    b = eng.decode_from_memory(mem.to(dev), START, END, max_len=8, return_logits=True)
+    w = torch_port.weights_to_numpy(dec)
+    check_rollout(b, w, mem.numpy(), 1, 0, TOL["fp32"])
+    assert (a - b.logits.cpu()).abs().max() > 0.5
+    p = dec.transformer_decoder.layers[1].linear1.weight
+    p.data = p.data * 0.5  # rebinding, as EMA.apply_shadow does
+    c = eng.decode_from_memory(mem.to(dev), START, END, max_len=8, return_logits=True)
+    check_rollout(c, torch_port.weights_to_numpy(dec), mem.numpy(), 1, 0, TOL["fp32"])
+    eng.close()
+
+
+def test_host_buffer_entry_point(dev):
+    dec = small_decoder(layers=2, end_bias=2.0).to(dev)
+    mem = torch_port.synthetic_memory(5, 49)
+    eng = make_engine(dec, "bf16", max_images=8, max_group=2, max_mem=49, max_len=12)
+    d = eng.decode_from_memory(mem.to(dev), START, END, max_len=12, group=2, n_sample=1, seed=3)
+    h = eng.decode_from_memory(mem, START, END, max_len=12, group=2, n_sample=1, seed=3)
+    assert not h.ids.is_cuda and h.steps == d.steps
+    assert torch.equal(h.ids, d.ids.cpu()) and torch.equal(h.logp, d.logp.cpu())
+    eng.close()
+
+
+def test_capacity_grows_and_limits_raise(dev):
+    dec = small_decoder(layers=1, pe_rows=10).to(dev)
+    eng = make_engine(dec, "fp32", max_images=2, max_mem=8, max_len=6)
+    mem = torch_port.synthetic_memory(5, 20).to(dev)
+    out = eng.decode_from_memory(mem, START, END, max_len=9)  # grows images, mem and max_len
+    assert out.ids.shape[0] == 5
+    with pytest.raises(ValueError):
+        eng.decode_from_memory(mem, START, END, max_len=12)  # 11 positions > 10 pe rows (vit:32)
+    with pytest.raises(ValueError):
+        eng.decode_from_memory(mem[:, :, :100], START, END)
+    eng.close()
