@@ -17,7 +17,7 @@ DECODE_NO_EARLY_STOP = 1
 EXPORTS = (
     "capdec_abi_version", "capdec_last_error", "capdec_create", "capdec_destroy", "capdec_set_weights",
     "capdec_prefill", "capdec_decode", "capdec_generate_host", "capdec_sample_logits", "capdec_launch_count",
-    "capdec_debug_gemm", "capdec_debug_cross_kv",
+    "capdec_debug_gemm", "capdec_debug_cross_kv", "capdec_profile_enable", "capdec_profile_report",
 )
 
 
@@ -88,6 +88,8 @@ def load() -> C.CDLL:
     lib.capdec_debug_gemm.argtypes = [H, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32,
                                       C.c_int32, C.c_int32, C.c_void_p]
     lib.capdec_debug_cross_kv.argtypes = [H, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]
+    lib.capdec_profile_enable.argtypes = [H, C.c_int32]
+    lib.capdec_profile_report.argtypes = [H, C.c_char_p, C.c_int32]
     for name in EXPORTS:
         if name not in ("capdec_last_error", "capdec_launch_count"):
             getattr(lib, name).restype = C.c_int

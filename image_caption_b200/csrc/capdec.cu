@@ -36,6 +36,32 @@ static int fail(capdec_handle h, int code, const char* fmt, ...) {
                   __FILE__, __LINE__);                                                        \
   } while (0)
 
+// ------------------------------------------------------------------ per-launch timing
+// When profiling is on (direct launches only), every kernel launch is bracketed by a pair of
+// events on the launching stream; capdec_profile_report() reduces them per tag.
+struct ProfScope {
+  capdec_handle h;
+  cudaStream_t s;
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  ProfScope(capdec_handle h_, cudaStream_t s_) : h(h_), s(s_) {
+    if (!h->profiling) return;
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    cudaEventRecord(e0, s);
+  }
+  ~ProfScope() {
+    if (!e0) return;
+    cudaEventRecord(e1, s);
+    h->prof.push_back({h->tag, e0, e1, h->tag_bytes});
+  }
+};
+static inline void set_tag(capdec_handle h, const char* tag, double bytes) { h->tag = tag; h->tag_bytes = bytes; }
+
+// Algorithmic bytes of one projection: weights + input rows + output rows (SURVEY 8d terms).
+static inline double gemm_bytes(int M, int N, int K, size_t ew, size_t ea, size_t eo) {
+  return (double)N * K * ew + (double)M * K * ea + (double)M * N * eo + (double)N * 4;
+}
+
 // ------------------------------------------------------------------ TMA tensor maps
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
@@ -89,6 +115,7 @@ static int launch_umma_bn(capdec_handle h, cudaStream_t s, const CUtensorMap& ta
   int stages = std::min(num_kb, 8);
   while (umma_smem_bytes(BN, stages) > kMaxDynSmem) --stages;
   dim3 grid(N / BN, (M + kUmmaBM - 1) / kUmmaBM);
+  ProfScope ps(h, s);
   kern<<<grid, kUmmaThreads, umma_smem_bytes(BN, stages), s>>>(ta, tw, M, N, K, stages, epi, st);
   CUDA_TRY(h, cudaGetLastError());
   h->launches_this_enqueue++;
@@ -112,6 +139,7 @@ static int launch_simt(capdec_handle h, cudaStream_t s, const TA* A, int lda, co
                        const Epi& epi, const DecState* st) {
   if (K % kSimtBK != 0 || N % 4 != 0) return fail(h, CAPDEC_ERR_INVALID, "GEMM needs K%%16==0, N%%4==0 (N=%d K=%d)", N, K);
   dim3 grid((N + kSimtBN - 1) / kSimtBN, (M + kSimtBM - 1) / kSimtBM);
+  ProfScope ps(h, s);
   gemm_simt_kernel<TA, TW, Epi><<<grid, kSimtThreads, 0, s>>>(A, lda, W, ldw, M, N, K, epi, st);
   CUDA_TRY(h, cudaGetLastError());
   h->launches_this_enqueue++;
@@ -173,6 +201,8 @@ extern "C" const char* capdec_last_error(capdec_handle h) { return h ? h->err.c_
 extern "C" int64_t capdec_launch_count(capdec_handle h) { return h ? h->launches : 0; }
 
 static void free_all(capdec_handle h) {
+  for (auto& r : h->prof) { cudaEventDestroy(r.e0); cudaEventDestroy(r.e1); }
+  h->prof.clear();
   for (auto& kv : h->graphs) {
     if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
     if (kv.second.graph) cudaGraphDestroy(kv.second.graph);
@@ -371,6 +401,8 @@ extern "C" int capdec_prefill(capdec_handle h, const float* memory, int32_t n_im
   const int M = n_images * mem_len, N = h->cfg.n_layer * 2 * kD;
   if (h->bf16) {
     const size_t n4 = (size_t)M * kD / 4;
+    set_tag(h, "prefill_convert", (double)M * kD * 6);
+    ProfScope ps(h, s);
     convert_kernel<bf16><<<(unsigned)((n4 + 255) / 256), 256, 0, s>>>(memory, (bf16*)h->mem_b, n4);
     CUDA_TRY(h, cudaGetLastError());
     h->launches_this_enqueue++;
@@ -379,6 +411,7 @@ extern "C" int capdec_prefill(capdec_handle h, const float* memory, int32_t n_im
   EpiCrossKV<bf16> e16{(bf16*)h->cross_kv, h->b_ckv, n_images, mem_len};
   CUtensorMap tm_mem;
   if (h->use_umma) TRY(make_map(h, &tm_mem, h->mem_b, M, kD, kUmmaBM));
+  set_tag(h, "prefill_gemm_cross_kv", gemm_bytes(M, N, kD, h->esz, h->esz, h->esz));
   TRY(gemm(h, s, h->bf16 ? h->mem_b : (const void*)memory, &tm_mem, h->w_ckv, &h->m_ckv, M, N, kD, e32, e16, nullptr));
   h->launches += h->launches_this_enqueue;
   h->n_images = n_images;
@@ -393,6 +426,7 @@ static int launch_self_attn(capdec_handle h, cudaStream_t s, int l, int M) {
   const Elem* kc = (const Elem*)h->self_k + (size_t)l * h->self_layer_elems;
   const Elem* vc = (const Elem*)h->self_v + (size_t)l * h->self_layer_elems;
   const int blocks = (M * kH + kAttnWarps - 1) / kAttnWarps;
+  ProfScope ps(h, s);
   if (h->t_pad == 64)
     self_attn_kernel<Elem, 16><<<blocks, kAttnWarps * 32, 0, s>>>((const Elem*)h->q, kc, vc, (Elem*)h->a, M, h->t_pad, h->st);
   else
@@ -405,6 +439,7 @@ static int launch_self_attn(capdec_handle h, cudaStream_t s, int l, int M) {
 template <typename Elem, int GT>
 static int launch_cross_gt(capdec_handle h, cudaStream_t s, const Elem* ck, const Elem* cv, int n_images, int group, int S) {
   const int warps = n_images * kH * (group / GT);
+  ProfScope ps(h, s);
   cross_attn_kernel<Elem, GT><<<(warps + kAttnWarps - 1) / kAttnWarps, kAttnWarps * 32, 0, s>>>(
       (const Elem*)h->q, ck, cv, (Elem*)h->a, n_images, group, S, h->st);
   CUDA_TRY(h, cudaGetLastError());
@@ -425,6 +460,7 @@ static int launch_cross_attn(capdec_handle h, cudaStream_t s, int l, int n_image
 
 template <typename Elem>
 static int launch_add_ln(capdec_handle h, cudaStream_t s, int l, int which, int M) {
+  ProfScope ps(h, s);
   add_ln_kernel<Elem><<<(M + 3) / 4, 128, 0, s>>>(h->x, h->t, h->layer[l].ln_w[which], h->layer[l].ln_b[which],
                                                    (Elem*)h->xb, M, h->st);
   CUDA_TRY(h, cudaGetLastError());
@@ -435,9 +471,15 @@ static int launch_add_ln(capdec_handle h, cudaStream_t s, int l, int which, int 
 template <typename Elem>
 static int enqueue_step_t(capdec_handle h, cudaStream_t s, int n_images, int S, int group) {
   const int M = n_images * group, L = h->cfg.n_layer, F = h->cfg.d_ff;
+  const size_t es = h->esz;
   const DecState* st = h->st;
   const void* xin = h->bf16 ? h->xb : (void*)h->x;  // GEMM A operand view of the residual stream
-  embed_pe_kernel<Elem><<<(M * (kD / 4) + 255) / 256, 256, 0, s>>>(h->st, h->cp, h->emb, h->pe, h->x, (Elem*)h->xb, M);
+  const double ln_bytes = (double)M * kD * (4 + 4 + 4 + (h->bf16 ? 2 : 0)) + 2.0 * kD * 4;
+  {
+    set_tag(h, "embed_pe", (double)M * kD * (4 + 4 + (h->bf16 ? 2 : 0)));
+    ProfScope ps(h, s);
+    embed_pe_kernel<Elem><<<(M * (kD / 4) + 255) / 256, 256, 0, s>>>(h->st, h->cp, h->emb, h->pe, h->x, (Elem*)h->xb, M);
+  }
   CUDA_TRY(h, cudaGetLastError());
   h->launches_this_enqueue++;
   for (int l = 0; l < L; ++l) {
@@ -449,34 +491,52 @@ static int enqueue_step_t(capdec_handle h, cudaStream_t s, int n_images, int S, 
       bf16* vc16 = (bf16*)h->self_v + (size_t)l * h->self_layer_elems;
       EpiQKV<float> e32{(float*)h->q, kc32, vc32, lp.b_qkv, st, h->t_pad};
       EpiQKV<bf16> e16{(bf16*)h->q, kc16, vc16, lp.b_qkv, st, h->t_pad};
+      set_tag(h, "gemm_qkv", gemm_bytes(M, 3 * kD, kD, es, es, es));
       TRY(gemm(h, s, xin, &h->tm_xb, lp.w_qkv, &lp.m_qkv, M, 3 * kD, kD, e32, e16, st));
+      // bytes: mean cached length over a rollout is filled in by the reporter (per-step n varies);
+      // here the launch is tagged with the bytes at the CURRENT host-side step estimate
+      set_tag(h, "self_attn", (double)M * kD * es * 2 + (double)M * 2 * kD * es * h->prof_step_n);
       TRY(launch_self_attn<Elem>(h, s, l, M));
       EpiLinear<float, false> eo{h->t, lp.b_so, kD};
+      set_tag(h, "gemm_self_out", gemm_bytes(M, kD, kD, es, es, 4));
       TRY(gemm(h, s, h->a, &h->tm_a, lp.w_so, &lp.m_so, M, kD, kD, eo, eo, st));
+      set_tag(h, "add_ln", ln_bytes);
       TRY(launch_add_ln<Elem>(h, s, l, 0, M));
     }
     {  // cross-attention block
       EpiLinear<float, false> q32{(float*)h->q, lp.b_cq, kD};
       EpiLinear<bf16, false> q16{(bf16*)h->q, lp.b_cq, kD};
+      set_tag(h, "gemm_cross_q", gemm_bytes(M, kD, kD, es, es, es));
       TRY(gemm(h, s, xin, &h->tm_xb, lp.w_cq, &lp.m_cq, M, kD, kD, q32, q16, st));
+      set_tag(h, "cross_attn", (double)n_images * S * 2 * kD * es + (double)M * kD * es * 2);
       TRY(launch_cross_attn<Elem>(h, s, l, n_images, group, S));
       EpiLinear<float, false> eo{h->t, lp.b_co, kD};
+      set_tag(h, "gemm_cross_out", gemm_bytes(M, kD, kD, es, es, 4));
       TRY(gemm(h, s, h->a, &h->tm_a, lp.w_co, &lp.m_co, M, kD, kD, eo, eo, st));
+      set_tag(h, "add_ln", ln_bytes);
       TRY(launch_add_ln<Elem>(h, s, l, 1, M));
     }
     {  // feed-forward block
       EpiLinear<float, true> h32{(float*)h->hbuf, lp.b_1, F};
       EpiLinear<bf16, true> h16{(bf16*)h->hbuf, lp.b_1, F};
+      set_tag(h, "gemm_ffn1", gemm_bytes(M, F, kD, es, es, es));
       TRY(gemm(h, s, xin, &h->tm_xb, lp.w_1, &lp.m_1, M, F, kD, h32, h16, st));
       EpiLinear<float, false> eo{h->t, lp.b_2, kD};
+      set_tag(h, "gemm_ffn2", gemm_bytes(M, kD, F, es, es, 4));
       TRY(gemm(h, s, h->hbuf, &h->tm_h, lp.w_2, &lp.m_2, M, kD, F, eo, eo, st));
+      set_tag(h, "add_ln", ln_bytes);
       TRY(launch_add_ln<Elem>(h, s, l, 2, M));
     }
   }
   // vocabulary projection in fp32 on the fp32 residual stream, then pick/sample
   EpiLinear<float, false> ev{h->logits, h->fc_b, kVPad};
+  set_tag(h, "gemm_vocab", gemm_bytes(M, kVPad, kD, 4, 4, 4));
   TRY((launch_simt<float, float, EpiLinear<float, false>>(h, s, h->x, kD, h->fc_w, kD, M, kVPad, kD, ev, st)));
-  head_kernel<<<(M + 3) / 4, 128, 0, s>>>(h->st, h->cp, h->logits, h->fin, M, h->cfg.vocab);
+  {
+    set_tag(h, "head", (double)M * (kVPad * 4 + 8 + 4));
+    ProfScope ps(h, s);
+    head_kernel<<<(M + 3) / 4, 128, 0, s>>>(h->st, h->cp, h->logits, h->fin, M, h->cfg.vocab);
+  }
   CUDA_TRY(h, cudaGetLastError());
   h->launches_this_enqueue++;
   return 0;
@@ -568,13 +628,14 @@ extern "C" int capdec_decode(capdec_handle h, const capdec_decode_args* a, void*
   h->launches++;
 
   const int T = a->max_len - 1;
-  if (h->use_graph) {
+  if (h->use_graph && !h->profiling) {
     StepGraph* g = nullptr;
     TRY(get_step_graph(h, n_images, S, group, &g));
     for (int t = 0; t < T; ++t) CUDA_TRY(h, cudaGraphLaunch(g->exec, s));
     h->launches += (long long)g->kernels * T;
   } else {
     for (int t = 0; t < T; ++t) {
+      h->prof_step_n = t + 1;
       TRY(enqueue_step(h, s, n_images, S, group));
       h->launches += h->launches_this_enqueue;
     }
@@ -630,6 +691,44 @@ extern "C" int capdec_sample_logits(capdec_handle h, const float* logits, int32_
                                                                          step, (long long*)ids_out, logp_out);
   CUDA_TRY(h, cudaGetLastError());
   h->launches++;
+  return CAPDEC_OK;
+}
+
+// ------------------------------------------------------------------ per-kernel timing
+extern "C" int capdec_profile_enable(capdec_handle h, int32_t on) {
+  if (!h) return fail(h, CAPDEC_ERR_INVALID, "null handle");
+  CUDA_TRY(h, cudaSetDevice(h->device));
+  for (auto& r : h->prof) { cudaEventDestroy(r.e0); cudaEventDestroy(r.e1); }
+  h->prof.clear();
+  h->profiling = on != 0;
+  return CAPDEC_OK;
+}
+
+// JSON: {"tag": {"launches": n, "ms": total device ms, "bytes": total algorithmic bytes}, ...}
+extern "C" int capdec_profile_report(capdec_handle h, char* buf, int32_t buf_len) {
+  if (!h || !buf || buf_len < 2) return fail(h, CAPDEC_ERR_INVALID, "bad argument");
+  CUDA_TRY(h, cudaSetDevice(h->device));
+  CUDA_TRY(h, cudaDeviceSynchronize());
+  struct Acc { long long n = 0; double ms = 0, bytes = 0; };
+  std::map<std::string, Acc> acc;
+  for (auto& r : h->prof) {
+    float ms = 0.f;
+    CUDA_TRY(h, cudaEventElapsedTime(&ms, r.e0, r.e1));
+    Acc& a = acc[r.tag];
+    a.n++; a.ms += ms; a.bytes += r.bytes;
+  }
+  std::string out = "{";
+  bool first = true;
+  for (auto& kv : acc) {
+    char line[256];
+    snprintf(line, sizeof line, "%s\"%s\": {\"launches\": %lld, \"ms\": %.6f, \"bytes\": %.0f}", first ? "" : ", ",
+             kv.first.c_str(), kv.second.n, kv.second.ms, kv.second.bytes);
+    out += line;
+    first = false;
+  }
+  out += "}";
+  if ((int)out.size() + 1 > buf_len) return fail(h, CAPDEC_ERR_CAPACITY, "profile report needs %zu bytes", out.size() + 1);
+  memcpy(buf, out.c_str(), out.size() + 1);
   return CAPDEC_OK;
 }
 

@@ -77,4 +77,13 @@ struct capdec_engine {
   std::map<std::tuple<int, int, int>, capdec::StepGraph> graphs;  // (n_images, mem_len, group)
   long long launches = 0;
   int launches_this_enqueue = 0;
+
+  // ---- per-kernel timing (capdec_profile_*): events around every launch of a direct (non-graph) rollout
+  struct ProfRec { const char* tag; cudaEvent_t e0, e1; double bytes; };
+  bool profiling = false;
+  const char* tag = "other";
+  int prof_step_n = 1;             // cached self positions of the step being enqueued (direct launches)
+  double tag_bytes = 0.0;          // algorithmic bytes of the launch being enqueued
+  std::vector<ProfRec> prof;
+  std::string prof_report;
 };

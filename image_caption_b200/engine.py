@@ -253,6 +253,16 @@ class CaptionDecodeEngine:
         return ids, lp.masked_fill(finished_before, 0.0)
 
     # ------------------------------------------------------------------ diagnostics
+    def profile(self, on: bool) -> None:
+        """Per-kernel CUDA-event timing of the following rollouts (direct launches, no graph)."""
+        _lib.check(self._h, self._lib.capdec_profile_enable(self._h, int(on)))
+
+    def profile_report(self) -> dict:
+        import json
+        buf = C.create_string_buffer(1 << 16)
+        _lib.check(self._h, self._lib.capdec_profile_report(self._h, buf, len(buf)))
+        return json.loads(buf.value.decode())
+
     def launch_count(self) -> int:
         return int(self._lib.capdec_launch_count(self._h))
 

@@ -151,6 +151,13 @@ int capdec_sample_logits(capdec_handle h, const float* logits, int32_t n_rows, i
 /* Number of kernels this handle has launched (graph replays count their kernel nodes). */
 int64_t capdec_launch_count(capdec_handle h);
 
+/* Per-kernel device timing for bench.py's roofline: while enabled, rollouts launch their kernels
+ * directly (no graph) with a CUDA-event pair around every launch on the launching stream.
+ * capdec_profile_report synchronises and writes JSON {"tag": {"launches","ms","bytes"}} where
+ * bytes are the ALGORITHMIC bytes of those launches (DESIGN.md lists the formula per tag). */
+int capdec_profile_enable(capdec_handle h, int32_t on);
+int capdec_profile_report(capdec_handle h, char* buf, int32_t buf_len);
+
 /* ---- diagnostics (used by the parity tests; not part of the reference-facing surface) ---- */
 
 /* C[M,N] = A[M,K] * W[N,K]^T + bias through the engine's GEMM of the handle's precision
