@@ -1,0 +1,164 @@
+"""CPU-side checks: the C-ABI library loads and exports every symbol of include/capdec.h (no
+compute calls), host logic of the sharded rollout (world-size-2 gloo), Philox restatement
+known-answer vectors, and the no-fallback rule."""
+import os
+import re
+import socket
+import sys
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from conftest import END, PAD, ROOT, START
+from oracle import philox
+
+
+# ------------------------------------------------------------------ C ABI
+def _declared_symbols():
+    text = open(os.path.join(ROOT, "include", "capdec.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(capdec_[a-z_0-9]+)\s*\(", text)))
+
+
+def test_library_exports_every_declared_symbol():
+    import __graft_entry__ as entry
+    entry.build()
+    from image_caption_b200 import _lib
+    lib = _lib.load()
+    names = _declared_symbols()
+    assert len(names) >= 12
+    for n in names:
+        assert hasattr(lib, n), f"libcapdec.so does not export {n}"
+    assert set(names) == set(_lib.EXPORTS), "ctypes binding and header disagree"
+    assert lib.capdec_abi_version() == _lib.ABI_VERSION
+
+
+def test_create_without_gpu_fails_loudly():
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    import ctypes as C
+    from image_caption_b200 import _lib
+    lib = _lib.load()
+    cfg = _lib.Config(vocab=109, d_model=512, n_head=8, n_layer=1, d_ff=2048, pe_rows=52, max_mem=49,
+                      max_images=1, max_group=1, max_len=8, precision=1, flags=0)
+    h = C.c_void_p()
+    rc = lib.capdec_create(C.byref(cfg), 0, C.byref(h))
+    assert rc == -5 and not h.value  # CAPDEC_ERR_NO_DEVICE: no CPU fallback exists
+    assert b"not available" in lib.capdec_last_error(None)
+    bad = _lib.Config(vocab=109, d_model=256, n_head=8, n_layer=1, d_ff=2048, pe_rows=52, max_mem=49,
+                      max_images=1, max_group=1, max_len=8, precision=1, flags=0)
+    assert lib.capdec_create(C.byref(bad), 0, C.byref(h)) == -1
+
+
+def test_engine_refuses_cpu_decoder():
+    from image_caption_b200 import CaptionDecodeEngine
+    from image_caption_b200.synthetic import random_decoder
+    with pytest.raises(RuntimeError, match="CUDA"):
+        CaptionDecodeEngine(random_decoder(0, layers=1))
+
+
+def test_product_does_not_import_oracle():
+    pkg = os.path.join(ROOT, "image_caption_b200")
+    for f in os.listdir(pkg):
+        if f.endswith(".py"):
+            src = open(os.path.join(pkg, f)).read()
+            assert not re.search(r"^\s*(from|import)\s+oracle", src, flags=re.M), f
+
+
+# ------------------------------------------------------------------ Philox known answers
+def test_philox_known_answer_vectors():
+    """Random123 kat_vectors for philox4x32-10."""
+    r = philox.philox4x32_10(0, 0, 0, 0, 0, 0)
+    assert [int(x) for x in r] == [0x6627e8d5, 0xe169c58d, 0xbc57ac4c, 0x9b00dbd8]
+    f = 0xffffffff
+    r = philox.philox4x32_10(f, f, f, f, f, f)
+    assert [int(x) for x in r] == [0x408f276d, 0x41c83b0e, 0xa20bc7c6, 0x6d5451fd]
+    r = philox.philox4x32_10(0x243f6a88, 0x85a308d3, 0x13198a2e, 0x03707344, 0xa4093822, 0x299f31d0)
+    assert [int(x) for x in r] == [0xd16cfe09, 0x94fdcceb, 0x5001e420, 0x24126ea1]
+
+
+def test_inverse_cdf_draw():
+    logits = np.log(np.array([[0.1, 0.2, 0.3, 0.4]]))
+    for u, want in [(0.0, 0), (0.0999, 0), (0.1001, 1), (0.31, 2), (0.999, 3)]:
+        assert philox.categorical_from_uniform(logits, np.array([u]))[0] == want
+
+
+# ------------------------------------------------------------------ sharding host logic
+def test_shard_bounds_cover_and_balance():
+    from image_caption_b200.dist import shard_bounds
+    for n in (1, 7, 8, 256, 513):
+        for w in (1, 2, 4, 8):
+            b = [shard_bounds(n, w, r) for r in range(w)]
+            assert b[0][0] == 0 and b[-1][1] == n
+            assert all(b[i][1] == b[i + 1][0] for i in range(w - 1))
+            sizes = [hi - lo for lo, hi in b]
+            assert max(sizes) - min(sizes) <= 1
+
+
+def test_reference_width_rules():
+    from image_caption_b200.dist import reference_width
+    E = END
+    ids = torch.tensor([[START, 5, E, 7, E, 9],
+                        [START, 6, 7, E, E, 9]])
+    none = torch.zeros(2, dtype=torch.bool)
+    # greedy: first step where ALL rows emit <end> simultaneously is step index 3 -> width 5 (vit:322)
+    assert reference_width(ids, none, E) == 5
+    # sampled: all rows have finished after step index 2 -> width 4 (scst:248)
+    assert reference_width(ids, ~none, E) == 4
+    # never: full width
+    assert reference_width(torch.tensor([[START, 1, 2, 3]]), torch.zeros(1, dtype=torch.bool), E) == 4
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _fake_decode(n_images_global, group, n_sample, max_len):
+    """Deterministic stand-in for the engine: tokens depend only on the GLOBAL sequence id."""
+    def table():
+        g = torch.Generator().manual_seed(11)
+        ids = torch.randint(1, 107, (n_images_global * group, max_len), generator=g)
+        ids[:, 0] = START
+        for m in range(ids.size(0)):
+            ids[m, 3 + m % 4:] = END  # every row ends; the last one at step 6
+        lp = -torch.rand((n_images_global * group, max_len - 1), generator=g)
+        return ids, lp
+    return table
+
+
+def _worker(rank, world, port, n_images, group, n_sample, max_len, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from image_caption_b200.dist import sharded_rollout
+    ids_all, lp_all = _fake_decode(n_images, group, n_sample, max_len)()
+
+    def local(lo, hi, base):
+        assert base == lo * group
+        return ids_all[lo * group: hi * group].clone(), lp_all[lo * group: hi * group].clone()
+
+    ids, lp = sharded_rollout(local, n_images, START, END, max_len, group=group, n_sample=n_sample)
+    if rank == 0:
+        torch.save((ids, lp), out)
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("n_images,group,n_sample", [(5, 2, 1), (4, 1, 0), (3, 3, 3)])
+def test_sharded_rollout_world2_gloo(tmp_path, n_images, group, n_sample):
+    from image_caption_b200.dist import reference_width
+    max_len = 12
+    out = str(tmp_path / "r.pt")
+    mp.spawn(_worker, args=(2, _free_port(), n_images, group, n_sample, max_len, out), nprocs=2, join=True)
+    ids, lp = torch.load(out)
+    ids_all, lp_all = _fake_decode(n_images, group, n_sample, max_len)()
+    is_s = (torch.arange(n_images * group) % group) < n_sample
+    w = reference_width(ids_all, is_s, END)
+    assert w < max_len
+    assert torch.equal(ids, ids_all[:, :w]) and torch.equal(lp, lp_all[:, : w - 1])
+    assert ids.dtype == torch.int64
