@@ -17,6 +17,8 @@ template <typename Elem, int NIT>
 __global__ void __launch_bounds__(kAttnWarps * 32)
 self_attn_kernel(const Elem* __restrict__ q, const Elem* __restrict__ kc, const Elem* __restrict__ vc,
                  Elem* __restrict__ out, int M, int t_pad, const DecState* st) {
+  asm volatile("griddepcontrol.wait;" ::: "memory");  // q and the appended K/V rows (PDL launches)
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   if (st->done) return;
   const int gw = blockIdx.x * kAttnWarps + (threadIdx.x >> 5);
   if (gw >= M * kH) return;

@@ -5,11 +5,15 @@
 #include <cstdio>
 #include <cstring>
 #include <mutex>
+#include <cstdlib>
+#include <utility>
 
 #include "engine.h"
 #include "epilogue.cuh"
 #include "gemm_simt.cuh"
 #include "gemm_umma.cuh"
+#include "gemm_swap.cuh"
+#include "cross_attn_tma.cuh"
 #include "attention.cuh"
 #include "pointwise.cuh"
 
@@ -174,6 +178,94 @@ static int gemm(capdec_handle h, cudaStream_t s, const void* a_ptr, const CUtens
   return launch_simt<bf16, bf16, EpiB16>(h, s, (const bf16*)a_ptr, K, (const bf16*)w_ptr, K, M, N, K, e16, st);
 }
 
+// ------------------------------------------------------------------ v2 launchers (bf16 + tcgen05)
+// All v2 step kernels begin with griddepcontrol.wait, so they may be chained with programmatic
+// dependent launch: the next kernel's prologue (barrier init, TMEM alloc, descriptor prefetch)
+// overlaps the tail of the current one.
+template <typename... KArgs, typename... Args>
+static cudaError_t launch_ex(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, int cluster_x,
+                             bool pdl, Args&&... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute attrs[2];
+  int na = 0;
+  if (cluster_x > 1) {
+    attrs[na].id = cudaLaunchAttributeClusterDimension;
+    attrs[na].val.clusterDim.x = cluster_x;
+    attrs[na].val.clusterDim.y = 1;
+    attrs[na].val.clusterDim.z = 1;
+    ++na;
+  }
+  if (pdl) {
+    attrs[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attrs[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
+  cfg.attrs = attrs;
+  cfg.numAttrs = na;
+  return cudaLaunchKernelEx(&cfg, kern, KArgs(std::forward<Args>(args))...);
+}
+
+static int swap_stages(capdec_handle h, int bnb, int K, int ctas) {
+  const int num_kb = K / kSwapBK;
+  if (h->force_stages > 0) return std::min(num_kb, std::min(h->force_stages, 12));
+  // few CTAs: everything in flight at once; more CTAs than SMs: leave room for two per SM
+  const int budget = (ctas > 148 ? 100 : 200) * 1024;
+  int stages = std::min(num_kb, 12);
+  while (stages > 2 && swap_smem_bytes(bnb, stages) > budget) --stages;
+  return stages;
+}
+
+template <int BNB, bool kLN, typename Epi>
+static int launch_swap_bnb(capdec_handle h, cudaStream_t s, const CUtensorMap& tw, const CUtensorMap& tx, int M, int n_out,
+                           int K, const Epi& epi, const SwapLNParams& ln, const DecState* st) {
+  dim3 grid(n_out / kSwapBF, (M + BNB - 1) / BNB);
+  const int stages = swap_stages(h, BNB, K, grid.x * grid.y);
+  ProfScope ps(h, s);
+  cudaError_t e = launch_ex(gemm_swap_kernel<BNB, kLN, Epi>, grid, dim3(kSwapThreads), swap_smem_bytes(BNB, stages), s,
+                            kLN ? 4 : 1, h->use_pdl, tw, tx, M, K, stages, epi, ln, st);
+  if (e != cudaSuccess) return fail(h, CAPDEC_ERR_CUDA, "gemm_swap launch failed: %s (BNB=%d n_out=%d K=%d stages=%d)",
+                                    cudaGetErrorString(e), BNB, n_out, K, stages);
+  h->launches_this_enqueue++;
+  return 0;
+}
+
+template <bool kLN, typename Epi>
+static int launch_swap(capdec_handle h, cudaStream_t s, const CUtensorMap& tw, const CUtensorMap& tx, int M, int n_out, int K,
+                       const Epi& epi, const SwapLNParams& ln, const DecState* st) {
+  if (K % kSwapBK != 0 || n_out % kSwapBF != 0 || (kLN && n_out != kD))
+    return fail(h, CAPDEC_ERR_INVALID, "swap GEMM shape (n_out=%d K=%d ln=%d)", n_out, K, (int)kLN);
+  switch (h->bnb) {
+    case 32: return launch_swap_bnb<32, kLN, Epi>(h, s, tw, tx, M, n_out, K, epi, ln, st);
+    case 64: return launch_swap_bnb<64, kLN, Epi>(h, s, tw, tx, M, n_out, K, epi, ln, st);
+    default: return launch_swap_bnb<128, kLN, Epi>(h, s, tw, tx, M, n_out, K, epi, ln, st);
+  }
+}
+
+template <bool kLN, typename Epi>
+static cudaError_t configure_swap_epi() {
+  cudaError_t e = cudaFuncSetAttribute(gemm_swap_kernel<32, kLN, Epi>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(gemm_swap_kernel<64, kLN, Epi>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(gemm_swap_kernel<128, kLN, Epi>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
+  return e;
+}
+static cudaError_t configure_fast_kernels() {
+  cudaError_t e = configure_swap_epi<false, SwapLinear<bf16, false>>();
+  if (e == cudaSuccess) e = configure_swap_epi<false, SwapLinear<bf16, true>>();
+  if (e == cudaSuccess) e = configure_swap_epi<false, SwapLinear<float, false>>();
+  if (e == cudaSuccess) e = configure_swap_epi<false, SwapLinear<float, true>>();
+  if (e == cudaSuccess) e = configure_swap_epi<false, SwapQKV<bf16>>();
+  if (e == cudaSuccess) e = configure_swap_epi<true, SwapNoLN>();
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(cross_attn_tma_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(cross_attn_tma_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(cross_attn_tma_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(vocab_head_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kVhSmemBytes);
+  return e;
+}
+
 // ------------------------------------------------------------------ allocation helpers
 template <typename T>
 static int dev_alloc(capdec_handle h, T** out, size_t count) {
@@ -271,6 +363,10 @@ static int create_impl(capdec_handle h) {
   TRY(dev_alloc(h, &h->cp, 1));
   CUDA_TRY(h, cudaMemset(h->st, 0, sizeof(DecState)));
   if (h->use_umma) CUDA_TRY(h, configure_umma_kernels());
+  if (h->fast) {
+    TRY(dev_alloc(h, &h->fc_wT, (size_t)kD * kVPad));
+    CUDA_TRY(h, configure_fast_kernels());
+  }
   return 0;
 }
 
@@ -306,6 +402,11 @@ extern "C" int capdec_create(const capdec_config* cfg, int device, capdec_handle
   h->use_graph = !(cfg->flags & CAPDEC_FLAG_NO_GRAPH);
   h->esz = h->bf16 ? 2 : 4;
   h->t_pad = cfg->max_len <= 64 ? 64 : 128;
+  h->fast = h->use_umma && !(cfg->flags & CAPDEC_FLAG_V1_STEP);
+  h->use_pdl = h->fast && !(cfg->flags & CAPDEC_FLAG_NO_PDL);
+  if (const char* e = getenv("CAPDEC_BNB")) h->force_bnb = atoi(e);
+  if (const char* e = getenv("CAPDEC_STAGES")) h->force_stages = atoi(e);
+  if (const char* e = getenv("CAPDEC_NO_PDL")) { if (atoi(e)) h->use_pdl = false; }
   int rc = create_impl(h);
   if (rc) {
     g_create_error = h->err;
@@ -346,6 +447,11 @@ extern "C" int capdec_set_weights(capdec_handle h, const capdec_weights* w, void
   pack_rows_kernel<float><<<1, 256, 0, s>>>(w->fc_out_b, h->fc_b, 1, V, 1);
   CUDA_TRY(h, cudaMemsetAsync(h->fc_b + V, 0, (kVPad - V) * sizeof(float), s));
   h->launches += 2;
+  if (h->fast) {
+    transpose_pad_kernel<<<(kD * kVPad + 255) / 256, 256, 0, s>>>(w->fc_out_w, h->fc_wT, V, kD, kVPad);
+    CUDA_TRY(h, cudaGetLastError());
+    h->launches++;
+  }
   for (int l = 0; l < L; ++l) {
     const capdec_layer_weights& lw = w->layer[l];
     LayerParams& lp = h->layer[l];
@@ -414,6 +520,11 @@ extern "C" int capdec_prefill(capdec_handle h, const float* memory, int32_t n_im
   set_tag(h, "prefill_gemm_cross_kv", gemm_bytes(M, N, kD, h->esz, h->esz, h->esz));
   TRY(gemm(h, s, h->bf16 ? h->mem_b : (const void*)memory, &tm_mem, h->w_ckv, &h->m_ckv, M, N, kD, e32, e16, nullptr));
   h->launches += h->launches_this_enqueue;
+  if (h->fast && (h->n_images != n_images || h->mem_len != mem_len || !h->prefilled_once)) {
+    if (mem_len > 256) return fail(h, CAPDEC_ERR_CAPACITY, "memory length %d > 256 is not supported by the TMA cross-attention", mem_len);
+    TRY(make_map(h, &h->tm_ckv, h->cross_kv, h->cfg.n_layer * 2 * n_images * kH * mem_len, kHD, ca_key_rows(mem_len)));
+    h->prefilled_once = true;
+  }
   h->n_images = n_images;
   h->mem_len = mem_len;
   h->prefilled = true;
@@ -542,8 +653,94 @@ static int enqueue_step_t(capdec_handle h, cudaStream_t s, int n_images, int S, 
   return 0;
 }
 
+// v2 step (bf16 + tcgen05): 8 kernels per layer instead of 11, no separate LayerNorm / vocabulary / head passes.
+static int enqueue_step_fast(capdec_handle h, cudaStream_t s, int n_images, int S, int group) {
+  const int M = n_images * group, L = h->cfg.n_layer, F = h->cfg.d_ff;
+  const DecState* st = h->st;
+  const SwapLNParams no_ln{};
+  cudaError_t e;
+  {
+    set_tag(h, "embed_pe", (double)M * kD * (4 + 4 + 2));
+    ProfScope ps(h, s);
+    e = launch_ex(embed_pe_kernel<bf16>, dim3((M * (kD / 4) + 255) / 256), dim3(256), 0, s, 1, h->use_pdl,
+                  (const DecState*)h->st, (const CallParams*)h->cp, (const float*)h->emb, (const float*)h->pe, h->x, (bf16*)h->xb, M);
+  }
+  CUDA_TRY(h, e);
+  h->launches_this_enqueue++;
+  const double ln_extra = (double)M * kD * (4 + 4 + 2);  // residual read, x and xb written
+  for (int l = 0; l < L; ++l) {
+    LayerParams& lp = h->layer[l];
+    bf16* kc = (bf16*)h->self_k + (size_t)l * h->self_layer_elems;
+    bf16* vc = (bf16*)h->self_v + (size_t)l * h->self_layer_elems;
+    {  // self-attention block
+      SwapQKV<bf16> eq{(bf16*)h->q, kc, vc, lp.b_qkv, st, h->t_pad};
+      set_tag(h, "gemm_qkv", gemm_bytes(M, 3 * kD, kD, 2, 2, 2));
+      TRY((launch_swap<false>(h, s, lp.m_qkv.bn[2], h->tx_xb, M, 3 * kD, kD, eq, no_ln, st)));
+      set_tag(h, "self_attn", (double)M * kD * 2 * 2 + (double)M * 2 * kD * 2 * h->prof_step_n);
+      {
+        const int blocks = (M * kH + kAttnWarps - 1) / kAttnWarps;
+        ProfScope ps(h, s);
+        if (h->t_pad == 64)
+          e = launch_ex(self_attn_kernel<bf16, 16>, dim3(blocks), dim3(kAttnWarps * 32), 0, s, 1, h->use_pdl, (const bf16*)h->q,
+                        (const bf16*)kc, (const bf16*)vc, (bf16*)h->a, M, h->t_pad, st);
+        else
+          e = launch_ex(self_attn_kernel<bf16, 32>, dim3(blocks), dim3(kAttnWarps * 32), 0, s, 1, h->use_pdl, (const bf16*)h->q,
+                        (const bf16*)kc, (const bf16*)vc, (bf16*)h->a, M, h->t_pad, st);
+      }
+      CUDA_TRY(h, e);
+      h->launches_this_enqueue++;
+      SwapLNParams ln{h->x, (bf16*)h->xb, lp.b_so, lp.ln_w[0], lp.ln_b[0]};
+      set_tag(h, "gemm_self_out_ln", gemm_bytes(M, kD, kD, 2, 2, 0) + ln_extra);
+      TRY((launch_swap<true>(h, s, lp.m_so.bn[2], h->tx_a, M, kD, kD, SwapNoLN{}, ln, st)));
+    }
+    {  // cross-attention block
+      SwapLinear<bf16, false> eq{(bf16*)h->q, lp.b_cq, kD};
+      set_tag(h, "gemm_cross_q", gemm_bytes(M, kD, kD, 2, 2, 2));
+      TRY((launch_swap<false>(h, s, lp.m_cq.bn[2], h->tx_xb, M, kD, kD, eq, no_ln, st)));
+      set_tag(h, "cross_attn", (double)n_images * S * 2 * kD * 2 + (double)M * kD * 2 * 2);
+      {
+        const int KT = ca_key_rows(S) / 16;
+        const int per_warp = (KT + 3) / 4;
+        ProfScope ps(h, s);
+        if (per_warp <= 1)
+          e = launch_ex(cross_attn_tma_kernel<1>, dim3(n_images * kH), dim3(kCaThreads), ca_smem_bytes(S), s, 1, h->use_pdl,
+                        h->tm_ckv, (const bf16*)h->q, (bf16*)h->a, l, n_images, group, S, st);
+        else if (per_warp <= 2)
+          e = launch_ex(cross_attn_tma_kernel<2>, dim3(n_images * kH), dim3(kCaThreads), ca_smem_bytes(S), s, 1, h->use_pdl,
+                        h->tm_ckv, (const bf16*)h->q, (bf16*)h->a, l, n_images, group, S, st);
+        else
+          e = launch_ex(cross_attn_tma_kernel<4>, dim3(n_images * kH), dim3(kCaThreads), ca_smem_bytes(S), s, 1, h->use_pdl,
+                        h->tm_ckv, (const bf16*)h->q, (bf16*)h->a, l, n_images, group, S, st);
+      }
+      CUDA_TRY(h, e);
+      h->launches_this_enqueue++;
+      SwapLNParams ln{h->x, (bf16*)h->xb, lp.b_co, lp.ln_w[1], lp.ln_b[1]};
+      set_tag(h, "gemm_cross_out_ln", gemm_bytes(M, kD, kD, 2, 2, 0) + ln_extra);
+      TRY((launch_swap<true>(h, s, lp.m_co.bn[2], h->tx_a, M, kD, kD, SwapNoLN{}, ln, st)));
+    }
+    {  // feed-forward block
+      SwapLinear<bf16, true> e1{(bf16*)h->hbuf, lp.b_1, F};
+      set_tag(h, "gemm_ffn1", gemm_bytes(M, F, kD, 2, 2, 2));
+      TRY((launch_swap<false>(h, s, lp.m_1.bn[2], h->tx_xb, M, F, kD, e1, no_ln, st)));
+      SwapLNParams ln{h->x, (bf16*)h->xb, lp.b_2, lp.ln_w[2], lp.ln_b[2]};
+      set_tag(h, "gemm_ffn2_ln", gemm_bytes(M, kD, F, 2, 2, 0) + ln_extra);
+      TRY((launch_swap<true>(h, s, lp.m_2.bn[2], h->tx_h, M, kD, F, SwapNoLN{}, ln, st)));
+    }
+  }
+  {
+    set_tag(h, "vocab_head", (double)kD * kVPad * 4 + (double)M * (kD * 4 + 8 + 4));
+    ProfScope ps(h, s);
+    e = launch_ex(vocab_head_kernel, dim3((M + kVhRows - 1) / kVhRows), dim3(kVhThreads), kVhSmemBytes, s, 1, h->use_pdl, h->st,
+                  (const CallParams*)h->cp, (const float*)h->x, (const float*)h->fc_wT, (const float*)h->fc_b, h->fin, M, h->cfg.vocab);
+  }
+  CUDA_TRY(h, e);
+  h->launches_this_enqueue++;
+  return 0;
+}
+
 static int enqueue_step(capdec_handle h, cudaStream_t s, int n_images, int S, int group) {
   h->launches_this_enqueue = 0;
+  if (h->fast) return enqueue_step_fast(h, s, n_images, S, group);
   return h->bf16 ? enqueue_step_t<bf16>(h, s, n_images, S, group) : enqueue_step_t<float>(h, s, n_images, S, group);
 }
 
@@ -552,6 +749,14 @@ static int ensure_activation_maps(capdec_handle h, int M) {
   TRY(make_map(h, &h->tm_xb, h->xb, M, kD, kUmmaBM));
   TRY(make_map(h, &h->tm_a, h->a, M, kD, kUmmaBM));
   TRY(make_map(h, &h->tm_h, h->hbuf, M, h->cfg.d_ff, kUmmaBM));
+  if (h->fast) {
+    // sequences per GEMM CTA: small enough that (n_out/128) x (M/bnb) CTAs cover the SMs
+    h->bnb = h->force_bnb ? h->force_bnb : (M <= 768 ? 32 : (M <= 2048 ? 64 : 128));
+    if (h->bnb != 32 && h->bnb != 64 && h->bnb != 128) return fail(h, CAPDEC_ERR_INVALID, "CAPDEC_BNB must be 32, 64 or 128");
+    TRY(make_map(h, &h->tx_xb, h->xb, M, kD, h->bnb));
+    TRY(make_map(h, &h->tx_a, h->a, M, kD, h->bnb));
+    TRY(make_map(h, &h->tx_h, h->hbuf, M, h->cfg.d_ff, h->bnb));
+  }
   h->maps_for_m = M;
   return 0;
 }

@@ -66,6 +66,15 @@ struct capdec_engine {
   CUtensorMap tm_xb, tm_a, tm_h;  // A-operand maps for the current M
   int maps_for_m = -1;
 
+  // ---- v2 step path (bf16 + tcgen05 only): swap-AB GEMMs, TMA cross-attention, fused head
+  bool fast = false;               // v2 kernels in use (off: CAPDEC_FLAG_V1_STEP)
+  bool use_pdl = false;            // programmatic dependent launch between the step's kernels
+  int bnb = 32;                    // sequences per GEMM CTA (UMMA N) for the current M
+  int force_bnb = 0, force_stages = 0;  // tuning overrides (env CAPDEC_BNB / CAPDEC_STAGES)
+  CUtensorMap tx_xb, tx_a, tx_h;   // activation maps with box rows = bnb
+  CUtensorMap tm_ckv;              // whole cross cache as [rows,64], box = 64 x ca_key_rows(S)
+  float* fc_wT = nullptr;          // [512][kVPad] fp32: fc_out.weight transposed + padded
+
   // ---- host-buffer entry point staging (device side)
   float* stage_mem = nullptr;
   long long* stage_ids = nullptr;
@@ -74,6 +83,7 @@ struct capdec_engine {
   // ---- current rollout
   int n_images = 0, mem_len = 0;
   bool prefilled = false;
+  bool prefilled_once = false;
   std::map<std::tuple<int, int, int>, capdec::StepGraph> graphs;  // (n_images, mem_len, group)
   long long launches = 0;
   int launches_this_enqueue = 0;

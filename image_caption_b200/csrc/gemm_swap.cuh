@@ -1,0 +1,275 @@
+// gemm_swap.cuh - decode-step projection on tcgen05 in "swap-AB" form:
+//     C^T[n_out, batch] = W[n_out, K] * X[batch, K]^T
+// The weight rows fill the 128 TMEM lanes (UMMA M = 128), the live sequences are the UMMA N
+// dimension (BNB = 32/64/128 per CTA), so a step with few sequences still launches
+// (n_out/128) x (M/BNB) CTAs, every CTA streams only its 128 x K weight slice once, and the
+// epilogue thread that owns output feature f writes 32 consecutive features per warp for each
+// sequence row (coalesced 128 B fp32 / 64 B bf16 stores).
+//
+// 6 warps: warp 0 TMA producer, warp 1 TMEM allocator + MMA issuer, warps 2-5 epilogue.
+// kLN variant: launched as clusters of 4 CTAs along n_out (= 512 features of the same BNB
+// rows); the epilogue adds bias + residual, exchanges per-row (sum, sum of squares) through
+// distributed shared memory and writes LayerNorm(x + proj) in place (fp32 x and its bf16 mirror):
+// SURVEY K5/K9/K10 "GEMM with residual+LayerNorm epilogue".
+#pragma once
+#include "common.cuh"
+#include "ptx_sm100.cuh"
+
+namespace capdec {
+
+constexpr int kSwapBF = 128;       // output features per CTA (UMMA M)
+constexpr int kSwapBK = 64;        // K per pipeline stage (one 128 B swizzle atom row)
+constexpr int kSwapThreads = 192;
+
+__host__ __device__ constexpr int swap_stage_bytes(int bnb) { return (kSwapBF + bnb) * kSwapBK * 2; }
+// pipeline stages + 1 KB alignment slack + barriers/tmem slot (256 B) + LN scratch (11 * bnb floats)
+__host__ __device__ constexpr int swap_smem_bytes(int bnb, int stages) {
+  return stages * swap_stage_bytes(bnb) + 1024 + 256 + 16 * bnb * 4;
+}
+
+// Sum over the 32 lanes of v[j], for every j: afterwards lane l holds the total of column l.
+// 31 shuffles instead of 32 x 5 (halving exchange).  Destroys v.
+__device__ __forceinline__ float lane_transpose_sum(float (&v)[32], int lane) {
+#pragma unroll
+  for (int o = 16; o >= 1; o >>= 1) {
+    const bool up = (lane & o) != 0;
+#pragma unroll
+    for (int j = 0; j < o; ++j) {
+      const float send = up ? v[j] : v[j + o];
+      const float keep = up ? v[j + o] : v[j];
+      v[j] = keep + __shfl_xor_sync(0xffffffffu, send, o);
+    }
+  }
+  return v[0];
+}
+
+// ---------------------------------------------------------------- epilogues (feature-major)
+// chunk(): called by the thread owning output feature f with 32 accumulators for sequence
+// rows r0 .. r0+31 (rows >= M must be skipped).
+
+// out[row, f] = act(acc + bias[f])
+template <typename OutT, bool kRelu>
+struct SwapLinear {
+  OutT* out;
+  const float* bias;
+  int ldo;
+  __device__ __forceinline__ void chunk(int f, int r0, int M, const float (&v)[32]) const {
+    const float b = bias ? __ldg(bias + f) : 0.f;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+      if (r0 + j < M) {
+        float r = v[j] + b;
+        if (kRelu) r = fmaxf(r, 0.f);
+        out[(size_t)(r0 + j) * ldo + f] = from_f32<OutT>(r);
+      }
+    }
+  }
+};
+
+// self-attention in_proj: f in [0,512) -> q, [512,1024) -> K cache row st->step, [1024,1536) -> V cache
+template <typename Elem>
+struct SwapQKV {
+  Elem* q;
+  Elem* kcache;  // this layer, [M][H][t_pad][64]
+  Elem* vcache;
+  const float* bias;
+  const DecState* st;
+  int t_pad;
+  __device__ __forceinline__ void chunk(int f, int r0, int M, const float (&v)[32]) const {
+    const float b = __ldg(bias + f);
+    const int n = st->step;
+    const int which = f >> 9, c = f & (kD - 1);
+    Elem* base;
+    size_t row_stride, off;
+    if (which == 0) { base = q; row_stride = kD; off = c; }
+    else {
+      base = which == 1 ? kcache : vcache;
+      row_stride = (size_t)kH * t_pad * kHD;
+      off = ((size_t)(c >> 6) * t_pad + n) * kHD + (c & 63);
+    }
+#pragma unroll
+    for (int j = 0; j < 32; ++j)
+      if (r0 + j < M) base[(size_t)(r0 + j) * row_stride + off] = from_f32<Elem>(v[j] + b);
+  }
+};
+
+// x <- LayerNorm(x + acc + bias) * gamma + beta, in place; xb = bf16 mirror (next GEMM's operand)
+struct SwapLNParams {
+  float* x;            // [M, 512] fp32 residual stream
+  bf16* xb;            // [M, 512]
+  const float* bias;   // [512]
+  const float* gamma;
+  const float* beta;
+};
+
+
+struct SwapNoLN {};
+
+// grid = (n_out / 128, ceil(M / BNB)); kLN: n_out == 512 and cluster dims (4,1,1).
+template <int BNB, bool kLN, typename Epi>
+__global__ void __launch_bounds__(kSwapThreads, 2)
+gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CUtensorMap tm_x,
+                 int M, int K, int stages, Epi epi, SwapLNParams ln, const DecState* st) {
+  static_assert(BNB == 32 || BNB == 64 || BNB == 128, "BNB");
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  constexpr int kWBytes = kSwapBF * kSwapBK * 2;
+  constexpr int kXBytes = BNB * kSwapBK * 2;
+  uint8_t* smem_w = smem;
+  uint8_t* smem_x = smem + (size_t)stages * kWBytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_x + (size_t)stages * kXBytes);
+  uint64_t* full = bars;
+  uint64_t* empty = bars + stages;
+  uint64_t* tmem_full = bars + 2 * stages;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * stages + 1);
+  float* red = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 256);  // [2][4][BNB]; later stat[2][BNB]
+  float* clu = red + 8 * BNB;                                                      // [4 ranks][2][BNB]
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int f0 = blockIdx.x * kSwapBF, b0 = blockIdx.y * BNB;
+  const int num_kb = K / kSwapBK;
+
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tensormap(&tm_w);
+    ptx::prefetch_tensormap(&tm_x);
+    for (int s = 0; s < stages; ++s) { ptx::mbar_init(&full[s], 1); ptx::mbar_init(&empty[s], 1); }
+    ptx::mbar_init(tmem_full, 1);
+    ptx::fence_barrier_init();
+  }
+  if (warp == 1) ptx::tmem_alloc(tmem_slot, BNB);
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  if (kLN) ptx::cluster_arrive();  // #1: every CTA of the cluster is resident before any DSMEM store
+
+  ptx::pdl_wait();     // outputs of the previous kernel of the step (activations, DecState) are visible
+  ptx::pdl_trigger();  // let the next kernel's prologue overlap this kernel
+  const bool active = !(st != nullptr && st->done);
+
+  if (warp == 0) {
+    if (lane == 0 && active) {
+      const uint64_t keep = ptx::policy_evict_last();  // weights are re-read every step: keep them in L2
+      for (int kb = 0; kb < num_kb; ++kb) {
+        const int s = kb % stages;
+        const uint32_t ph = (kb / stages) & 1;
+        ptx::mbar_wait(&empty[s], ph ^ 1);
+        ptx::mbar_expect_tx(&full[s], kWBytes + kXBytes);
+        ptx::tma_load_2d_hint(smem_w + (size_t)s * kWBytes, &tm_w, &full[s], kb * kSwapBK, f0, keep);
+        ptx::tma_load_2d(smem_x + (size_t)s * kXBytes, &tm_x, &full[s], kb * kSwapBK, b0);
+      }
+    }
+    __syncwarp();
+    if (kLN) { ptx::cluster_wait(); ptx::cluster_arrive(); ptx::cluster_wait(); }
+  } else if (warp == 1) {
+    if (lane == 0 && active) {
+      constexpr uint32_t idesc = ptx::umma_idesc_bf16(BNB);
+      for (int kb = 0; kb < num_kb; ++kb) {
+        const int s = kb % stages;
+        const uint32_t ph = (kb / stages) & 1;
+        ptx::mbar_wait(&full[s], ph);
+        ptx::tc_fence_after();
+        const uint32_t w_addr = ptx::smem_u32(smem_w + (size_t)s * kWBytes);
+        const uint32_t x_addr = ptx::smem_u32(smem_x + (size_t)s * kXBytes);
+#pragma unroll
+        for (int k = 0; k < kSwapBK / 16; ++k)
+          ptx::umma_f16(tmem_base, ptx::umma_desc_sw128(w_addr + k * 32), ptx::umma_desc_sw128(x_addr + k * 32),
+                        idesc, (kb | k) != 0 ? 1u : 0u);
+        ptx::umma_commit(&empty[s]);
+      }
+      ptx::umma_commit(tmem_full);
+    }
+    __syncwarp();
+    if (kLN) { ptx::cluster_wait(); ptx::cluster_arrive(); ptx::cluster_wait(); }
+  } else {
+    const int quarter = warp & 3;  // TMEM lane quarter this warp may read
+    const int f = f0 + quarter * 32 + lane;
+    const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16);
+    if (active) {
+      ptx::mbar_wait(tmem_full, 0);
+      ptx::tc_fence_after();
+    }
+    if constexpr (!kLN) {
+      if (active) {
+#pragma unroll 1
+        for (int c0 = 0; c0 < BNB; c0 += 32) {
+          float v[32];
+          ptx::tmem_ld32(taddr + (uint32_t)c0, v);
+          epi.chunk(f, b0 + c0, M, v);
+        }
+      }
+    } else {
+      const int e = threadIdx.x - 64;  // 0..127
+      const float bias_f = __ldg(ln.bias + f);
+      if (active) {
+#pragma unroll 1
+        for (int c0 = 0; c0 < BNB; c0 += 32) {
+          float v[32], a[32], q[32];
+          ptx::tmem_ld32(taddr + (uint32_t)c0, v);
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const int row = b0 + c0 + j;
+            v[j] += bias_f + (row < M ? ln.x[(size_t)row * kD + f] : 0.f);
+            a[j] = v[j];
+            q[j] = v[j] * v[j];
+          }
+          ptx::tmem_st32(taddr + (uint32_t)c0, v);  // park x + proj + bias for pass 2
+          const float s1 = lane_transpose_sum(a, lane);
+          const float s2 = lane_transpose_sum(q, lane);
+          red[(0 * 4 + quarter) * BNB + c0 + lane] = s1;
+          red[(1 * 4 + quarter) * BNB + c0 + lane] = s2;
+        }
+      }
+      ptx::bar_sync(1, 128);
+      ptx::cluster_wait();  // #1
+      if (active) {
+        const uint32_t my_rank = ptx::cluster_ctarank();
+        for (int idx = e; idx < 2 * BNB; idx += 128) {
+          const int which = idx / BNB, c = idx - which * BNB;
+          const float tot = (red[(which * 4 + 0) * BNB + c] + red[(which * 4 + 1) * BNB + c]) +
+                            (red[(which * 4 + 2) * BNB + c] + red[(which * 4 + 3) * BNB + c]);
+          float* slot = clu + (my_rank * 2 + which) * BNB + c;
+#pragma unroll
+          for (uint32_t r = 0; r < 4; ++r) ptx::st_cluster_f32(ptx::map_to_cta(slot, r), tot);
+        }
+      }
+      ptx::cluster_arrive();  // #2 (release: the DSMEM stores above)
+      ptx::cluster_wait();
+      if (active) {
+        for (int c = e; c < BNB; c += 128) {
+          const float s1 = (clu[(0 * 2 + 0) * BNB + c] + clu[(1 * 2 + 0) * BNB + c]) +
+                           (clu[(2 * 2 + 0) * BNB + c] + clu[(3 * 2 + 0) * BNB + c]);
+          const float s2 = (clu[(0 * 2 + 1) * BNB + c] + clu[(1 * 2 + 1) * BNB + c]) +
+                           (clu[(2 * 2 + 1) * BNB + c] + clu[(3 * 2 + 1) * BNB + c]);
+          const float mean = s1 * (1.f / kD);
+          const float var = fmaxf(s2 * (1.f / kD) - mean * mean, 0.f);
+          red[c] = mean;
+          red[BNB + c] = rsqrtf(var + 1e-5f);
+        }
+      }
+      ptx::bar_sync(1, 128);
+      if (active) {
+        const float g = __ldg(ln.gamma + f), be = __ldg(ln.beta + f);
+#pragma unroll 1
+        for (int c0 = 0; c0 < BNB; c0 += 32) {
+          float v[32];
+          ptx::tmem_ld32(taddr + (uint32_t)c0, v);
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const int row = b0 + c0 + j;
+            if (row < M) {
+              const float y = (v[j] - red[c0 + j]) * red[BNB + c0 + j] * g + be;
+              ln.x[(size_t)row * kD + f] = y;
+              ln.xb[(size_t)row * kD + f] = __float2bfloat16_rn(y);
+            }
+          }
+        }
+      }
+    }
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) ptx::tmem_dealloc(tmem_base, BNB);
+}
+
+}  // namespace capdec

@@ -32,6 +32,8 @@ __global__ void init_rollout_kernel(DecState* st, const CallParams* cp, unsigned
 template <typename Elem>
 __global__ void embed_pe_kernel(const DecState* st, const CallParams* cp, const float* __restrict__ emb,
                                 const float* __restrict__ pe, float* __restrict__ x, Elem* __restrict__ xb, int M) {
+  asm volatile("griddepcontrol.wait;" ::: "memory");  // ids / DecState of the previous step (PDL launches)
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   if (st->done) return;
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;  // one float4 each
   if (idx >= M * (kD / 4)) return;
@@ -189,6 +191,121 @@ head_kernel(DecState* st, const CallParams* cp, const float* __restrict__ logits
   }
 }
 
+// Fused vocabulary projection + pick (SURVEY K11+K12+K13): logits never round-trip to HBM.
+// wT: fc_out.weight transposed and padded, [512][kVPad] fp32; x: [M,512] fp32 residual stream.
+// CTA = 8 warps x 2 rows; the 256 KB of wT stream through shared memory in 32-row slabs
+// (double buffered); lane l accumulates vocabulary entries 4l..4l+3 of its warp's two rows.
+constexpr int kVhRows = 16, kVhThreads = 256, kVhSlab = 32;
+constexpr int kVhSmemBytes = kVhRows * kD * 4 + 2 * kVhSlab * kVPad * 4;
+
+__global__ void __launch_bounds__(kVhThreads)
+vocab_head_kernel(DecState* st, const CallParams* cp, const float* __restrict__ x, const float* __restrict__ wT,
+                  const float* __restrict__ bias, unsigned char* fin, int M, int V) {
+  extern __shared__ __align__(16) uint8_t vh_smem[];
+  float* xs = reinterpret_cast<float*>(vh_smem);   // [16][512]
+  float* ws = xs + kVhRows * kD;                   // [2][32][128]
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  if (st->done) return;
+  const CallParams p = *cp;
+  const int n = st->step;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int r0 = blockIdx.x * kVhRows;
+  // x rows of this CTA -> smem (rows >= M read as zero)
+  for (int i = tid; i < kVhRows * kD / 4; i += kVhThreads) {
+    const int r = i / (kD / 4), c = i % (kD / 4);
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (r0 + r < M) v = *reinterpret_cast<const float4*>(x + (size_t)(r0 + r) * kD + c * 4);
+    reinterpret_cast<float4*>(xs)[i] = v;
+  }
+  auto load_slab = [&](int slab, int buf) {  // 32 x 128 floats = 1024 float4, 4 per thread
+    const float4* src = reinterpret_cast<const float4*>(wT + (size_t)slab * kVhSlab * kVPad);
+    float4* dst = reinterpret_cast<float4*>(ws + buf * kVhSlab * kVPad);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int idx = tid + i * kVhThreads;
+      const uint32_t d = static_cast<uint32_t>(__cvta_generic_to_shared(dst + idx));
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(src + idx) : "memory");
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  load_slab(0, 0);
+  float acc[2][4];
+#pragma unroll
+  for (int r = 0; r < 2; ++r)
+#pragma unroll
+    for (int i = 0; i < 4; ++i) acc[r][i] = 0.f;
+  const float* xr0 = xs + (warp * 2) * kD;
+  const float* xr1 = xr0 + kD;
+  constexpr int kSlabs = kD / kVhSlab;
+  for (int sl = 0; sl < kSlabs; ++sl) {
+    if (sl + 1 < kSlabs) {
+      load_slab(sl + 1, (sl + 1) & 1);
+      asm volatile("cp.async.wait_group 1;" ::: "memory");
+    } else {
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+    }
+    __syncthreads();
+    const float* wb = ws + (sl & 1) * kVhSlab * kVPad + lane * 4;
+#pragma unroll
+    for (int k = 0; k < kVhSlab; ++k) {
+      const float4 w = *reinterpret_cast<const float4*>(wb + k * kVPad);
+      const float a = xr0[sl * kVhSlab + k], b = xr1[sl * kVhSlab + k];
+      acc[0][0] = fmaf(a, w.x, acc[0][0]); acc[0][1] = fmaf(a, w.y, acc[0][1]);
+      acc[0][2] = fmaf(a, w.z, acc[0][2]); acc[0][3] = fmaf(a, w.w, acc[0][3]);
+      acc[1][0] = fmaf(b, w.x, acc[1][0]); acc[1][1] = fmaf(b, w.y, acc[1][1]);
+      acc[1][2] = fmaf(b, w.z, acc[1][2]); acc[1][3] = fmaf(b, w.w, acc[1][3]);
+    }
+    __syncthreads();  // slab buffer (sl & 1) is refilled two iterations later
+  }
+  const float4 bv = __ldg(reinterpret_cast<const float4*>(bias) + lane);
+#pragma unroll
+  for (int r = 0; r < 2; ++r) {
+    const int m = r0 + warp * 2 + r;
+    if (m >= M) continue;  // warp-uniform
+    float l[4] = {acc[r][0] + bv.x, acc[r][1] + bv.y, acc[r][2] + bv.z, acc[r][3] + bv.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) if (lane * 4 + i >= V) l[i] = -INFINITY;
+    if (p.logits_dump != nullptr) {
+      float* d = p.logits_dump + ((size_t)m * (p.max_len - 1) + n) * V;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) if (lane * 4 + i < V) d[lane * 4 + i] = l[i];
+    }
+    const bool sample = (m % p.group) < p.n_sample;
+    const float u = sample ? philox_uniform(p.seed, p.seq_id_base + (unsigned long long)m, n) : 0.f;
+    float lp;
+    const int tok = warp_pick(l, lane, sample, u, V, &lp);
+    if (lane == 0) {
+      p.ids[(size_t)m * p.max_len + n + 1] = tok;
+      const bool ended = tok == p.end_token;
+      if (sample) {
+        const bool was = fin[m] != 0;
+        if (p.logp != nullptr) p.logp[(size_t)m * (p.max_len - 1) + n] = was ? 0.f : lp;  // scst:239
+        if (ended) fin[m] = 1;
+        if (was || ended) atomicAdd(&st->cnt_finished, 1);
+      } else if (ended) {
+        atomicAdd(&st->cnt_end_now, 1);
+      }
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    const unsigned tk = atomicAdd(&st->ticket, 1u);
+    if (tk == gridDim.x - 1) {  // last block: evaluate the stop condition, advance the step
+      __threadfence();
+      const int ce = atomicAdd(&st->cnt_end_now, 0), cf = atomicAdd(&st->cnt_finished, 0);
+      if (p.n_greedy_rows > 0 && ce == p.n_greedy_rows) st->greedy_done = 1;  // vit:322
+      if (p.n_sample_rows > 0 && cf == p.n_sample_rows) st->sample_done = 1;  // scst:248
+      st->cnt_end_now = 0; st->cnt_finished = 0; st->ticket = 0u;
+      st->steps_executed = n + 1;
+      st->step = n + 1;
+      if (st->greedy_done && st->sample_done && !p.no_early_stop) st->done = 1;
+      __threadfence();
+    }
+  }
+}
+
 // Stand-alone sampler for capdec_sample_logits: logits [rows, V] (unpadded).
 __global__ void __launch_bounds__(128)
 sample_rows_kernel(const float* __restrict__ logits, int rows, int V, int mode, unsigned long long seed,
@@ -223,6 +340,14 @@ __global__ void pack_rows_kernel(const float* __restrict__ in, Out* __restrict__
   if (i >= (size_t)rows_out * cols) return;
   const int r = (int)(i / cols);
   out[i] = from_f32<Out>(r < rows ? in[i] : 0.f);
+}
+
+// out[c][r] = in[r][c] for r < rows (else 0): fc_out.weight [V,512] -> [512][kVPad]
+__global__ void transpose_pad_kernel(const float* __restrict__ in, float* __restrict__ out, int rows, int cols, int rows_out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= cols * rows_out) return;
+  const int c = i / rows_out, r = i % rows_out;
+  out[i] = r < rows ? in[(size_t)r * cols + c] : 0.f;
 }
 
 // diagnostics: cache tile [n_images][H][S][64] -> fp32 [n_images, S, 512]

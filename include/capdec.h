@@ -73,6 +73,9 @@ typedef struct {
 
 #define CAPDEC_FLAG_NO_GRAPH 1   /* launch step kernels directly instead of replaying a CUDA graph */
 #define CAPDEC_FLAG_NO_UMMA 2    /* bf16 mode: route GEMMs through the CUDA-core kernel (debug)     */
+#define CAPDEC_FLAG_V1_STEP 4    /* bf16 mode: the first-generation step kernels (one GEMM tile per CTA,
+                                    separate LayerNorm / vocabulary / head kernels); kept for A/B runs */
+#define CAPDEC_FLAG_NO_PDL 8     /* do not chain the step's kernels with programmatic dependent launch */
 
 /* fp32 DEVICE pointers, borrowed for the duration of capdec_set_weights only. */
 typedef struct {

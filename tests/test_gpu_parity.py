@@ -254,6 +254,51 @@ def test_bf16_simt_route_matches_umma_route(dev):
     assert (res[0] - res[1]).abs().max() < 2e-2  # same roundings, different summation order
 
 
+@pytest.mark.parametrize("bnb", [32, 64, 128])
+@pytest.mark.parametrize("mem_len,group,n_sample", [(196, 6, 5), (49, 1, 0)])
+def test_v2_step_tile_widths(dev, monkeypatch, bnb, mem_len, group, n_sample):
+    """swap-AB GEMMs at every sequences-per-CTA width (ragged last tile), TMA cross-attention at both
+    memory lengths, fused LayerNorm epilogue (cluster of 4) and fused vocabulary head."""
+    monkeypatch.setenv("CAPDEC_BNB", str(bnb))
+    dec = small_decoder(layers=2, end_bias=1.0)
+    w = torch_port.weights_to_numpy(dec)
+    n_img = 150 // group
+    mem = torch_port.synthetic_memory(n_img, mem_len)
+    eng = make_engine(dec.to(dev), "bf16", max_images=n_img, max_group=group, max_mem=mem_len, max_len=10)
+    out = eng.decode_from_memory(mem.to(dev), START, END, max_len=10, group=group, n_sample=n_sample, seed=11,
+                                 return_logits=True)
+    check_rollout(out, w, mem.numpy(), group, n_sample, TOL["bf16"], seed=11)
+    eng.close()
+
+
+def test_v2_cross_attention_many_rollouts_per_image(dev):
+    """group > 16: the cross-attention CTA walks several 16-row query tiles over one staged K/V tile."""
+    dec = small_decoder(layers=2)
+    w = torch_port.weights_to_numpy(dec)
+    mem = torch_port.synthetic_memory(3, 100)
+    eng = make_engine(dec.to(dev), "bf16", max_images=3, max_group=20, max_mem=100, max_len=8)
+    out = eng.decode_from_memory(mem.to(dev), START, END, max_len=8, group=20, n_sample=19, seed=2, return_logits=True)
+    check_rollout(out, w, mem.numpy(), 20, 19, TOL["bf16"], seed=2)
+    eng.close()
+
+
+@pytest.mark.parametrize("pdl", [True, False])
+def test_v2_step_matches_v1_step(dev, pdl):
+    dec = small_decoder(layers=3).to(dev)
+    mem = torch_port.synthetic_memory(9, 49).to(dev)
+    res = []
+    for impl in ("v1", "v2"):
+        eng = make_engine(dec, "bf16", step_impl=impl, pdl=pdl, max_images=9, max_group=2, max_mem=49, max_len=12)
+        o = eng.decode_from_memory(mem, START, END, max_len=12, group=2, n_sample=0, return_logits=True, early_stop=False,
+                                   trim=False)
+        res.append((o.ids.cpu(), o.logits.cpu()))
+        eng.close()
+    # same roundings of weights / KV / GEMM inputs; different summation order and LayerNorm variance formula
+    same = (res[0][0] == res[1][0]).all(1)
+    assert same.float().mean() > 0.8
+    assert (res[0][1][same] - res[1][1][same]).abs().max() < 3e-2
+
+
 def test_weight_updates_are_picked_up(dev):
     """Optimiser steps mutate parameters in place; EMA rebinds param.data (optimizations.py:444-456)."""
     dec = small_decoder(layers=2).to(dev)
