@@ -16,6 +16,7 @@
 #include "cross_attn_tma.cuh"
 #include "attention.cuh"
 #include "pointwise.cuh"
+#include "rollout_cluster.cuh"
 
 using namespace capdec;
 
@@ -307,6 +308,14 @@ static void free_all(capdec_handle h) {
 extern "C" int capdec_destroy(capdec_handle h) {
   if (!h) return CAPDEC_OK;
   cudaSetDevice(h->device);
+  if (h->trace) {  // tuning aid: phase stamps of the cluster rollout kernel (cycles since the layer started)
+    long long t[64];
+    if (cudaMemcpy(t, h->trace, sizeof t, cudaMemcpyDeviceToHost) == cudaSuccess) {
+      fprintf(stderr, "capdec trace (cycles since layer start):");
+      for (int i = 1; i < 64 && t[i]; ++i) fprintf(stderr, " [%d]%lld", i, t[i] - t[0]);
+      fprintf(stderr, "\n");
+    }
+  }
   free_all(h);
   delete h;
   return CAPDEC_OK;
@@ -367,6 +376,13 @@ static int create_impl(capdec_handle h) {
     TRY(dev_alloc(h, &h->fc_wT, (size_t)kD * kVPad));
     CUDA_TRY(h, configure_fast_kernels());
   }
+  if (h->mega) {
+    TRY(dev_alloc(h, &h->wstream, (size_t)kRcCluster * (L * kRcUnitsPerLayer + kRcUnitsHead) * kRcUnitBytes));
+    TRY(dev_alloc(h, &h->counters, (size_t)c.max_len * 4));
+    if (getenv("CAPDEC_TRACE")) { TRY(dev_alloc(h, &h->trace, 64)); CUDA_TRY(h, cudaMemset(h->trace, 0, 64 * sizeof(long long))); }
+    CUDA_TRY(h, cudaFuncSetAttribute(rollout_cluster_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem));
+    CUDA_TRY(h, cudaFuncSetAttribute(rollout_cluster_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem));
+  }
   return 0;
 }
 
@@ -404,6 +420,9 @@ extern "C" int capdec_create(const capdec_config* cfg, int device, capdec_handle
   h->t_pad = cfg->max_len <= 64 ? 64 : 128;
   h->fast = h->use_umma && !(cfg->flags & CAPDEC_FLAG_V1_STEP);
   h->use_pdl = h->fast && !(cfg->flags & CAPDEC_FLAG_NO_PDL);
+  h->mega = h->fast && !(cfg->flags & CAPDEC_FLAG_NO_CLUSTER_ROLLOUT) && cfg->d_ff == 2048 && h->t_pad == 64;
+  if (const char* e = getenv("CAPDEC_RB")) h->mega_rb = atoi(e) == 32 ? 32 : 16;
+  if (const char* e = getenv("CAPDEC_CHUNK")) h->mega_chunk = std::max(1, atoi(e));
   if (const char* e = getenv("CAPDEC_BNB")) h->force_bnb = atoi(e);
   if (const char* e = getenv("CAPDEC_STAGES")) h->force_stages = atoi(e);
   if (const char* e = getenv("CAPDEC_NO_PDL")) { if (atoi(e)) h->use_pdl = false; }
@@ -488,6 +507,20 @@ extern "C" int capdec_set_weights(capdec_handle h, const capdec_weights* w, void
     }
   }
   if (h->use_umma) TRY(make_weight_maps(h, &h->m_ckv, h->w_ckv, L * 2 * kD, kD));
+  if (h->mega) {
+    RcPackSrc src{};
+    src.n_layer = L;
+    src.vocab = V;
+    src.fc_w = w->fc_out_w;
+    for (int l = 0; l < L; ++l) {
+      const capdec_layer_weights& lw = w->layer[l];
+      src.layer[l] = RcPackLayer{lw.self_in_w, lw.self_out_w, lw.cross_in_w, lw.cross_out_w, lw.lin1_w, lw.lin2_w};
+    }
+    const long long total = (long long)kRcCluster * (L * kRcUnitsPerLayer + kRcUnitsHead) * 512;
+    pack_wstream_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(src, h->wstream);
+    CUDA_TRY(h, cudaGetLastError());
+    h->launches++;
+  }
   h->have_weights = true;
   return CAPDEC_OK;
 }
@@ -788,6 +821,55 @@ static int get_step_graph(capdec_handle h, int n_images, int S, int group, StepG
   return 0;
 }
 
+// ------------------------------------------------------------------ v3: whole-rollout cluster kernel
+static bool mega_applicable(capdec_handle h, int n_images, int S, int group) {
+  return h->mega && S <= 64 && group <= h->mega_rb && h->mega_rb % group == 0;
+}
+
+static int enqueue_cluster_rollout(capdec_handle h, cudaStream_t s, int n_images, int S, int group, int T) {
+  const int M = n_images * group, L = h->cfg.n_layer, RB = h->mega_rb;
+  RcParams P{};
+  for (int l = 0; l < L; ++l) {
+    const LayerParams& lp = h->layer[l];
+    RcLayer& r = P.layer[l];
+    r.b_qkv = lp.b_qkv; r.b_so = lp.b_so; r.b_cq = lp.b_cq; r.b_co = lp.b_co; r.b_1 = lp.b_1; r.b_2 = lp.b_2;
+    for (int j = 0; j < 3; ++j) { r.ln_w[j] = lp.ln_w[j]; r.ln_b[j] = lp.ln_b[j]; }
+    r.kcache = (bf16*)h->self_k + (size_t)l * h->self_layer_elems;
+    r.vcache = (bf16*)h->self_v + (size_t)l * h->self_layer_elems;
+  }
+  P.wstream = h->wstream;
+  P.emb = h->emb; P.pe = h->pe; P.fc_b = h->fc_b;
+  P.cp = h->cp; P.fin = h->fin; P.counters = h->counters; P.st = h->st; P.trace = h->trace;
+  P.n_layer = L; P.M = M; P.group = group; P.S = S; P.t_pad = h->t_pad; P.vocab = h->cfg.vocab; P.n_images = n_images;
+  const int blocks = (M + RB - 1) / RB;
+  const int ring0 = RB == 16 ? RcSmem<16>::kRing : RcSmem<32>::kRing;
+  int stages = std::min(16, (kMaxDynSmem - 1024 - ring0) / kRcUnitBytes);
+  if (h->force_stages > 0) stages = std::min(stages, h->force_stages);
+  if (stages < 2) return fail(h, CAPDEC_ERR_INVALID, "cluster rollout: no room for the weight ring (RB=%d)", RB);
+  const size_t smem = RB == 16 ? RcSmem<16>::bytes(stages) : RcSmem<32>::bytes(stages);
+  // algorithmic bytes of the chunk for the profile report: SURVEY 8d per-step terms
+  for (int n0 = 0; n0 < T; n0 += h->mega_chunk) {
+    const int n1 = std::min(T, n0 + h->mega_chunk);
+    P.step_begin = n0;
+    P.step_end = n1;
+    double bytes = 0;
+    for (int n = n0 + 1; n <= n1; ++n)
+      bytes += 22128237.0 * 2 + (double)n_images * 2 * L * S * kD * 2 + (double)M * (2.0 * L * n * kD * 2 + 2.0 * L * kD * 2) +
+               (double)M * (kD * 2 + 12);
+    set_tag(h, "rollout_cluster", bytes);
+    {
+      ProfScope ps(h, s);
+      if (RB == 16) rollout_cluster_kernel<16><<<blocks * kRcCluster, kRcThreads, smem, s>>>(h->tm_ckv, P, stages);
+      else rollout_cluster_kernel<32><<<blocks * kRcCluster, kRcThreads, smem, s>>>(h->tm_ckv, P, stages);
+      CUDA_TRY(h, cudaGetLastError());
+    }
+    rollout_check_kernel<<<1, 256, 0, s>>>(h->st, h->cp, h->counters, M, n0, n1);
+    CUDA_TRY(h, cudaGetLastError());
+    h->launches += 2;
+  }
+  return 0;
+}
+
 // ------------------------------------------------------------------ decode
 static int validate_decode(capdec_handle h, const capdec_decode_args* a) {
   if (!h->prefilled) return fail(h, CAPDEC_ERR_STATE, "capdec_decode before capdec_prefill");
@@ -828,12 +910,14 @@ extern "C" int capdec_decode(capdec_handle h, const capdec_decode_args* a, void*
   cp.n_greedy_rows = M - cp.n_sample_rows;
   // pageable source: the runtime stages it before returning, so `cp` may die with this frame
   CUDA_TRY(h, cudaMemcpyAsync(h->cp, &cp, sizeof cp, cudaMemcpyHostToDevice, s));
-  init_rollout_kernel<<<std::min((M * a->max_len + 255) / 256, 1024), 256, 0, s>>>(h->st, h->cp, h->fin, M);
+  init_rollout_kernel<<<std::min((M * a->max_len + 255) / 256, 1024), 256, 0, s>>>(h->st, h->cp, h->fin, M, h->counters);
   CUDA_TRY(h, cudaGetLastError());
   h->launches++;
 
   const int T = a->max_len - 1;
-  if (h->use_graph && !h->profiling) {
+  if (mega_applicable(h, n_images, S, group)) {
+    TRY(enqueue_cluster_rollout(h, s, n_images, S, group, T));
+  } else if (h->use_graph && !h->profiling) {
     StepGraph* g = nullptr;
     TRY(get_step_graph(h, n_images, S, group, &g));
     for (int t = 0; t < T; ++t) CUDA_TRY(h, cudaGraphLaunch(g->exec, s));

@@ -75,6 +75,14 @@ struct capdec_engine {
   CUtensorMap tm_ckv;              // whole cross cache as [rows,64], box = 64 x ca_key_rows(S)
   float* fc_wT = nullptr;          // [512][kVPad] fp32: fc_out.weight transposed + padded
 
+  // ---- v3: whole-rollout cluster kernel (rollout_cluster.cuh), used when the shape allows
+  bool mega = false;               // enabled (bf16 + tcgen05, not CAPDEC_FLAG_NO_CLUSTER_ROLLOUT)
+  unsigned char* wstream = nullptr;  // [8][L*112+8][8192] per-CTA weight units in streaming order
+  int* counters = nullptr;         // [max_len][4] per-step stop-rule counters
+  long long* trace = nullptr;      // 32 clock stamps (env CAPDEC_TRACE=1)
+  int mega_rb = 16;                // sequences per cluster
+  int mega_chunk = 8;              // decode steps per kernel launch (stop rule evaluated between chunks)
+
   // ---- host-buffer entry point staging (device side)
   float* stage_mem = nullptr;
   long long* stage_ids = nullptr;

@@ -10,7 +10,7 @@
 
 namespace capdec {
 
-__global__ void init_rollout_kernel(DecState* st, const CallParams* cp, unsigned char* fin, int M) {
+__global__ void init_rollout_kernel(DecState* st, const CallParams* cp, unsigned char* fin, int M, int* counters) {
   const CallParams p = *cp;
   const int tid = blockIdx.x * blockDim.x + threadIdx.x;
   if (tid == 0) {
@@ -25,6 +25,8 @@ __global__ void init_rollout_kernel(DecState* st, const CallParams* cp, unsigned
     if (p.logp != nullptr && i < M * (p.max_len - 1)) p.logp[i] = 0.f;
   }
   if (tid < M) fin[tid] = 0;
+  if (counters != nullptr)
+    for (int i = tid; i < p.max_len * 4; i += gridDim.x * blockDim.x) counters[i] = 0;
 }
 
 // x[m,:] = emb[tok]*sqrt(512) + pe[n,:]; separate multiply and add (no FMA contraction) so the

@@ -70,10 +70,11 @@ class CaptionDecodeEngine:
         if precision not in ("bf16", "fp32"):
             raise ValueError(f"precision must be 'bf16' or 'fp32', got {precision!r}")
         self.precision = precision
-        if step_impl not in ("v1", "v2"):
-            raise ValueError(f"step_impl must be 'v1' or 'v2', got {step_impl!r}")
+        if step_impl not in ("v1", "v2", "v3"):
+            raise ValueError(f"step_impl must be 'v1', 'v2' or 'v3', got {step_impl!r}")
         self._flags = ((0 if use_graph else _lib.FLAG_NO_GRAPH) | (0 if use_umma else _lib.FLAG_NO_UMMA)
-                       | (_lib.FLAG_V1_STEP if step_impl == "v1" else 0) | (0 if pdl else _lib.FLAG_NO_PDL))
+                       | (_lib.FLAG_V1_STEP if step_impl == "v1" else 0) | (0 if pdl else _lib.FLAG_NO_PDL)
+                       | (0 if step_impl == "v3" else _lib.FLAG_NO_CLUSTER_ROLLOUT))
         self._cap = dict(max_images=max_images, max_group=max_group, max_mem=max_mem, max_len=max_len)
         self._h = C.c_void_p()
         self._weights_sig = None

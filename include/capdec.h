@@ -76,6 +76,7 @@ typedef struct {
 #define CAPDEC_FLAG_V1_STEP 4    /* bf16 mode: the first-generation step kernels (one GEMM tile per CTA,
                                     separate LayerNorm / vocabulary / head kernels); kept for A/B runs */
 #define CAPDEC_FLAG_NO_PDL 8     /* do not chain the step's kernels with programmatic dependent launch */
+#define CAPDEC_FLAG_NO_CLUSTER_ROLLOUT 16 /* never use the whole-rollout cluster kernel (per-step kernels only) */
 
 /* fp32 DEVICE pointers, borrowed for the duration of capdec_set_weights only. */
 typedef struct {

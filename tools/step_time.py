@@ -11,12 +11,14 @@ from image_caption_b200.synthetic import random_decoder, random_memory
 
 ap = argparse.ArgumentParser()
 ap.add_argument("workload")
-ap.add_argument("--variants", default="v2,v2_nopdl,v1")
+ap.add_argument("--variants", default="v3,v2,v1")
 ap.add_argument("--bnb", default="")
 ap.add_argument("--stages", default="")
 ap.add_argument("--reps", type=int, default=5)
+ap.add_argument("--images", type=int, default=0)
 a = ap.parse_args()
 desc, n_img, S, G, ns, max_len = WORKLOADS[a.workload]
+if a.images: n_img = a.images
 dev = torch.device("cuda:0")
 dec = random_decoder(0, pe_rows=max(52, max_len)).to(dev)
 mem = random_memory(n_img, S, seed=1234).to(dev)
@@ -27,7 +29,7 @@ for var in a.variants.split(","):
             os.environ.pop("CAPDEC_BNB", None); os.environ.pop("CAPDEC_STAGES", None)
             if bnb: os.environ["CAPDEC_BNB"] = bnb
             if stg: os.environ["CAPDEC_STAGES"] = stg
-            kw = dict(step_impl="v1" if var == "v1" else "v2", pdl=(var != "v2_nopdl"), use_graph=(var != "v2_nograph"))
+            kw = dict(step_impl=var[:2], pdl=(var != "v2_nopdl"), use_graph=(var != "v2_nograph"))
             eng = CaptionDecodeEngine(dec, precision="bf16", max_images=n_img, max_group=G, max_mem=S, max_len=max_len, **kw)
             run = lambda seed: eng.decode_from_memory(mem, START, END, max_len=max_len, group=G, n_sample=ns, seed=seed, trim=False)
             for i in range(3): run(i)
