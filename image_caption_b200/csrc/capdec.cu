@@ -220,9 +220,39 @@ static int swap_stages(capdec_handle h, int bnb, int K, int ctas) {
   return stages;
 }
 
+template <int BNB, bool kLN, typename Epi, int KSPLIT>
+static int launch_swap_ks(capdec_handle h, cudaStream_t s, const CUtensorMap& tw, const CUtensorMap& tx, int M, int n_out,
+                          int K, const Epi& epi, const SwapLNParams& ln, const DecState* st) {
+  dim3 grid(n_out / kSwapBF * KSPLIT, (M + BNB - 1) / BNB);
+  int stages = swap_stages(h, BNB, K / KSPLIT, grid.x * grid.y);
+  while (stages > 2 && swap_smem_bytes(BNB, stages, KSPLIT) > kMaxDynSmem) --stages;
+  ProfScope ps(h, s);
+  cudaError_t e = launch_ex(gemm_swap_kernel<BNB, kLN, Epi, KSPLIT>, grid, dim3(kSwapThreads), swap_smem_bytes(BNB, stages, KSPLIT), s,
+                            kLN ? 4 * KSPLIT : 1, h->use_pdl, tw, tx, M, K, stages, epi, ln, st);
+  if (e != cudaSuccess) return fail(h, CAPDEC_ERR_CUDA, "gemm_swap launch failed: %s (BNB=%d n_out=%d K=%d stages=%d ksplit=%d)",
+                                    cudaGetErrorString(e), BNB, n_out, K, stages, KSPLIT);
+  h->launches_this_enqueue++;
+  return 0;
+}
+
+// LayerNorm GEMMs may divide K over the cluster (4 feature tiles x ksplit CTAs).
+static int ln_ksplit(capdec_handle h, int K, int row_tiles) {
+  // measured (B200, tools/step_time.py): 8-CTA clusters pay only while the whole grid is one small wave
+  // (cfg2: 476 -> 459 us/step); 16-CTA clusters and larger grids lose to cluster scheduling (cfg5: 764 -> 957)
+  int ks = h->force_ksplit > 0 ? h->force_ksplit : (8 * row_tiles <= 64 ? 2 : 1);
+  if (h->bnb == 128 && ks > 2) ks = 2;  // the received partial tiles must fit beside the pipeline stages
+  if (ks != 1 && ks != 2 && ks != 4) ks = 1;
+  return (K / kSwapBK) % ks == 0 ? ks : 1;
+}
+
 template <int BNB, bool kLN, typename Epi>
 static int launch_swap_bnb(capdec_handle h, cudaStream_t s, const CUtensorMap& tw, const CUtensorMap& tx, int M, int n_out,
                            int K, const Epi& epi, const SwapLNParams& ln, const DecState* st) {
+  if constexpr (kLN) {
+    const int ks = ln_ksplit(h, K, (M + BNB - 1) / BNB);
+    if (ks == 4) return launch_swap_ks<BNB, kLN, Epi, 4>(h, s, tw, tx, M, n_out, K, epi, ln, st);
+    if (ks == 2) return launch_swap_ks<BNB, kLN, Epi, 2>(h, s, tw, tx, M, n_out, K, epi, ln, st);
+  }
   dim3 grid(n_out / kSwapBF, (M + BNB - 1) / BNB);
   const int stages = swap_stages(h, BNB, K, grid.x * grid.y);
   ProfScope ps(h, s);
@@ -253,6 +283,13 @@ static cudaError_t configure_swap_epi() {
   if (e == cudaSuccess) e = cudaFuncSetAttribute(gemm_swap_kernel<128, kLN, Epi>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
   return e;
 }
+template <int BNB, int KSPLIT>
+static cudaError_t configure_swap_ln_ks() {
+  auto k = gemm_swap_kernel<BNB, true, SwapNoLN, KSPLIT>;
+  cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
+  if (e == cudaSuccess && KSPLIT * 4 > 8) e = cudaFuncSetAttribute(k, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+  return e;
+}
 static cudaError_t configure_fast_kernels() {
   cudaError_t e = configure_swap_epi<false, SwapLinear<bf16, false>>();
   if (e == cudaSuccess) e = configure_swap_epi<false, SwapLinear<bf16, true>>();
@@ -260,6 +297,12 @@ static cudaError_t configure_fast_kernels() {
   if (e == cudaSuccess) e = configure_swap_epi<false, SwapLinear<float, true>>();
   if (e == cudaSuccess) e = configure_swap_epi<false, SwapQKV<bf16>>();
   if (e == cudaSuccess) e = configure_swap_epi<true, SwapNoLN>();
+  if (e == cudaSuccess) e = configure_swap_ln_ks<32, 2>();
+  if (e == cudaSuccess) e = configure_swap_ln_ks<64, 2>();
+  if (e == cudaSuccess) e = configure_swap_ln_ks<128, 2>();
+  if (e == cudaSuccess) e = configure_swap_ln_ks<32, 4>();
+  if (e == cudaSuccess) e = configure_swap_ln_ks<64, 4>();
+  if (e == cudaSuccess) e = configure_swap_ln_ks<128, 4>();
   if (e == cudaSuccess) e = cudaFuncSetAttribute(cross_attn_tma_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(cross_attn_tma_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(cross_attn_tma_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
@@ -308,6 +351,24 @@ static void free_all(capdec_handle h) {
 extern "C" int capdec_destroy(capdec_handle h) {
   if (!h) return CAPDEC_OK;
   cudaSetDevice(h->device);
+  if (getenv("CAPDEC_TRACE_GEMM")) {  // tuning aid: stamps of the last swap-GEMM launches (gemm_swap.cuh)
+    long long* dptr = nullptr;
+    unsigned n = 0;
+    cudaMemcpyFromSymbol(&dptr, g_swap_trace, sizeof dptr);
+    cudaMemcpyFromSymbol(&n, g_swap_trace_n, sizeof n);
+    if (dptr) {
+      static long long t[256 * 8];
+      cudaMemcpy(t, dptr, sizeof t, cudaMemcpyDeviceToHost);
+      const unsigned first = n > 48 ? n - 48 : 0;
+      long long prev_exit = 0;
+      for (unsigned i = first; i < n; ++i) {
+        const long long* r = t + (i & 255u) * 8;
+        fprintf(stderr, "gemm#%u ln=%lld gap_ns=%lld  cycles: prologue %lld  pdl_wait %lld  load+mma %lld  epilogue %lld  | in-kernel ns %lld\n", i, r[7],
+                prev_exit ? r[0] - prev_exit : 0, r[2] - r[1], r[3] - r[2], r[4] - r[3], r[5] - r[4], r[6] - r[0]);
+        prev_exit = r[6];
+      }
+    }
+  }
   if (h->trace) {  // tuning aid: phase stamps of the cluster rollout kernel (cycles since the layer started)
     long long t[64];
     if (cudaMemcpy(t, h->trace, sizeof t, cudaMemcpyDeviceToHost) == cudaSuccess) {
@@ -423,8 +484,16 @@ extern "C" int capdec_create(const capdec_config* cfg, int device, capdec_handle
   h->mega = h->fast && !(cfg->flags & CAPDEC_FLAG_NO_CLUSTER_ROLLOUT) && cfg->d_ff == 2048 && h->t_pad == 64;
   if (const char* e = getenv("CAPDEC_RB")) h->mega_rb = atoi(e) == 32 ? 32 : 16;
   if (const char* e = getenv("CAPDEC_CHUNK")) h->mega_chunk = std::max(1, atoi(e));
+  if (getenv("CAPDEC_TRACE_GEMM")) {
+    long long* buf = nullptr;
+    if (cudaMalloc(&buf, 256 * 8 * sizeof(long long)) == cudaSuccess) {
+      cudaMemset(buf, 0, 256 * 8 * sizeof(long long));
+      cudaMemcpyToSymbol(g_swap_trace, &buf, sizeof buf);
+    }
+  }
   if (const char* e = getenv("CAPDEC_BNB")) h->force_bnb = atoi(e);
   if (const char* e = getenv("CAPDEC_STAGES")) h->force_stages = atoi(e);
+  if (const char* e = getenv("CAPDEC_KSPLIT")) h->force_ksplit = atoi(e);
   if (const char* e = getenv("CAPDEC_NO_PDL")) { if (atoi(e)) h->use_pdl = false; }
   int rc = create_impl(h);
   if (rc) {

@@ -22,9 +22,10 @@ constexpr int kSwapBK = 64;        // K per pipeline stage (one 128 B swizzle at
 constexpr int kSwapThreads = 192;
 
 __host__ __device__ constexpr int swap_stage_bytes(int bnb) { return (kSwapBF + bnb) * kSwapBK * 2; }
-// pipeline stages + 1 KB alignment slack + barriers/tmem slot (256 B) + LN scratch (11 * bnb floats)
-__host__ __device__ constexpr int swap_smem_bytes(int bnb, int stages) {
-  return stages * swap_stage_bytes(bnb) + 1024 + 256 + 16 * bnb * 4;
+// pipeline stages + 1 KB alignment slack + barriers/tmem slot (256 B) + LN scratch (16 * bnb floats)
+// + split-K partial tiles received from the cluster peers ((ksplit-1) x 128 x bnb floats)
+__host__ __device__ constexpr int swap_smem_bytes(int bnb, int stages, int ksplit = 1) {
+  return stages * swap_stage_bytes(bnb) + 1024 + 256 + 16 * bnb * 4 + (ksplit - 1) * kSwapBF * bnb * 4;
 }
 
 // Sum over the 32 lanes of v[j], for every j: afterwards lane l holds the total of column l.
@@ -105,8 +106,17 @@ struct SwapLNParams {
 
 struct SwapNoLN {};
 
-// grid = (n_out / 128, ceil(M / BNB)); kLN: n_out == 512 and cluster dims (4,1,1).
-template <int BNB, bool kLN, typename Epi>
+// tuning aid (env CAPDEC_TRACE_GEMM): CTA (0,0) of every launch records 8 stamps
+// {globaltimer at entry, clock at entry, after prologue, after pdl wait, accumulator ready, epilogue done, globaltimer at exit, kLN}
+__device__ long long* g_swap_trace = nullptr;
+__device__ unsigned int g_swap_trace_n = 0;
+
+// grid = (n_out / 128, ceil(M / BNB)); kLN: n_out == 512, grid.x = cluster dims x = 4 * KSPLIT.
+// KSPLIT > 1 (kLN only): cluster rank r = feature tile (r & 3) + 4 * k-slice (r >> 2).  tcgen05.mma costs
+// ~148 cycles per instruction whatever its shape (measured, tools/mma_probe.cu), so a CTA's critical path
+// is K/16 instructions; the K range is therefore divided over KSPLIT CTAs whose partial accumulators are
+// added through distributed shared memory by the k-slice-0 CTA of each feature tile.
+template <int BNB, bool kLN, typename Epi, int KSPLIT = 1>
 __global__ void __launch_bounds__(kSwapThreads, 2)
 gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CUtensorMap tm_x,
                  int M, int K, int stages, Epi epi, SwapLNParams ln, const DecState* st) {
@@ -124,10 +134,16 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * stages + 1);
   float* red = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 256);  // [2][4][BNB]; later stat[2][BNB]
   float* clu = red + 8 * BNB;                                                      // [4 ranks][2][BNB]
+  float* part = red + 16 * BNB;                                                    // [KSPLIT-1][128][BNB] partial tiles
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int f0 = blockIdx.x * kSwapBF, b0 = blockIdx.y * BNB;
-  const int num_kb = K / kSwapBK;
+  const int f0 = (kLN ? (int)(blockIdx.x & 3) : (int)blockIdx.x) * kSwapBF, b0 = blockIdx.y * BNB;
+  const int ks = kLN ? (int)(blockIdx.x >> 2) : 0;  // k-slice of this CTA
+  const int num_kb = K / kSwapBK / KSPLIT;
+  const int kb0 = ks * num_kb;
+  long long tr[8];
+  const bool tracing = g_swap_trace != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 64;
+  if (tracing) { asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tr[0])); tr[1] = clock64(); }
 
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tensormap(&tm_w);
@@ -142,9 +158,11 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   if (kLN) ptx::cluster_arrive();  // #1: every CTA of the cluster is resident before any DSMEM store
+  if (tracing) tr[2] = clock64();
 
   ptx::pdl_wait();     // outputs of the previous kernel of the step (activations, DecState) are visible
   ptx::pdl_trigger();  // let the next kernel's prologue overlap this kernel
+  if (tracing) tr[3] = clock64();
   const bool active = !(st != nullptr && st->done);
 
   if (warp == 0) {
@@ -155,12 +173,13 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
         const uint32_t ph = (kb / stages) & 1;
         ptx::mbar_wait(&empty[s], ph ^ 1);
         ptx::mbar_expect_tx(&full[s], kWBytes + kXBytes);
-        ptx::tma_load_2d_hint(smem_w + (size_t)s * kWBytes, &tm_w, &full[s], kb * kSwapBK, f0, keep);
-        ptx::tma_load_2d(smem_x + (size_t)s * kXBytes, &tm_x, &full[s], kb * kSwapBK, b0);
+        ptx::tma_load_2d_hint(smem_w + (size_t)s * kWBytes, &tm_w, &full[s], (kb0 + kb) * kSwapBK, f0, keep);
+        ptx::tma_load_2d(smem_x + (size_t)s * kXBytes, &tm_x, &full[s], (kb0 + kb) * kSwapBK, b0);
       }
     }
     __syncwarp();
     if (kLN) { ptx::cluster_wait(); ptx::cluster_arrive(); ptx::cluster_wait(); }
+    if (kLN && KSPLIT > 1) ptx::cluster_sync();
   } else if (warp == 1) {
     if (lane == 0 && active) {
       constexpr uint32_t idesc = ptx::umma_idesc_bf16(BNB);
@@ -181,6 +200,7 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
     }
     __syncwarp();
     if (kLN) { ptx::cluster_wait(); ptx::cluster_arrive(); ptx::cluster_wait(); }
+    if (kLN && KSPLIT > 1) ptx::cluster_sync();
   } else {
     const int quarter = warp & 3;  // TMEM lane quarter this warp may read
     const int f = f0 + quarter * 32 + lane;
@@ -189,6 +209,7 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
       ptx::mbar_wait(tmem_full, 0);
       ptx::tc_fence_after();
     }
+    if (tracing) tr[4] = clock64();
     if constexpr (!kLN) {
       if (active) {
 #pragma unroll 1
@@ -200,12 +221,41 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
       }
     } else {
       const int e = threadIdx.x - 64;  // 0..127
+      const int fl = quarter * 32 + lane;  // feature within the tile
       const float bias_f = __ldg(ln.bias + f);
-      if (active) {
+      const bool lead = ks == 0;           // this CTA owns the epilogue of its feature tile
+      if constexpr (KSPLIT > 1) {
+        ptx::cluster_wait();  // #1
+        if (active && !lead) {  // hand the partial accumulators of this k-slice to the k-slice-0 CTA
+          const uint32_t dst0 = ptx::map_to_cta(part + ((size_t)(ks - 1) * kSwapBF + fl) * BNB, (uint32_t)(blockIdx.x & 3));
+#pragma unroll 1
+          for (int c0 = 0; c0 < BNB; c0 += 32) {
+            float v[32];
+            ptx::tmem_ld32(taddr + (uint32_t)c0, v);
+#pragma unroll
+            for (int j = 0; j < 32; j += 4)
+              ptx::st_cluster_v4(dst0 + (uint32_t)(c0 + j) * 4, make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]));
+          }
+        }
+        ptx::cluster_arrive();  // #2: partial tiles delivered
+        ptx::cluster_wait();
+      }
+      if (active && lead) {
 #pragma unroll 1
         for (int c0 = 0; c0 < BNB; c0 += 32) {
           float v[32], a[32], q[32];
           ptx::tmem_ld32(taddr + (uint32_t)c0, v);
+          if constexpr (KSPLIT > 1) {
+#pragma unroll
+            for (int p = 0; p < KSPLIT - 1; ++p) {
+              const float4* src = reinterpret_cast<const float4*>(part + ((size_t)p * kSwapBF + fl) * BNB + c0);
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                const float4 t4 = src[j];
+                v[4 * j] += t4.x; v[4 * j + 1] += t4.y; v[4 * j + 2] += t4.z; v[4 * j + 3] += t4.w;
+              }
+            }
+          }
 #pragma unroll
           for (int j = 0; j < 32; ++j) {
             const int row = b0 + c0 + j;
@@ -221,9 +271,9 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
         }
       }
       ptx::bar_sync(1, 128);
-      ptx::cluster_wait();  // #1
-      if (active) {
-        const uint32_t my_rank = ptx::cluster_ctarank();
+      if constexpr (KSPLIT == 1) ptx::cluster_wait();  // #1
+      if (active && lead) {
+        const uint32_t my_rank = blockIdx.x & 3;  // feature tile == cluster rank of the k-slice-0 CTAs
         for (int idx = e; idx < 2 * BNB; idx += 128) {
           const int which = idx / BNB, c = idx - which * BNB;
           const float tot = (red[(which * 4 + 0) * BNB + c] + red[(which * 4 + 1) * BNB + c]) +
@@ -233,9 +283,9 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
           for (uint32_t r = 0; r < 4; ++r) ptx::st_cluster_f32(ptx::map_to_cta(slot, r), tot);
         }
       }
-      ptx::cluster_arrive();  // #2 (release: the DSMEM stores above)
+      ptx::cluster_arrive();  // #2 / #3 (release: the DSMEM stores above)
       ptx::cluster_wait();
-      if (active) {
+      if (active && lead) {
         for (int c = e; c < BNB; c += 128) {
           const float s1 = (clu[(0 * 2 + 0) * BNB + c] + clu[(1 * 2 + 0) * BNB + c]) +
                            (clu[(2 * 2 + 0) * BNB + c] + clu[(3 * 2 + 0) * BNB + c]);
@@ -248,7 +298,7 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
         }
       }
       ptx::bar_sync(1, 128);
-      if (active) {
+      if (active && lead) {
         const float g = __ldg(ln.gamma + f), be = __ldg(ln.beta + f);
 #pragma unroll 1
         for (int c0 = 0; c0 < BNB; c0 += 32) {
@@ -266,6 +316,13 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
         }
       }
     }
+  }
+  if (tracing) {
+    tr[5] = clock64();
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tr[6]));
+    tr[7] = kLN ? 1 : 0;
+    const unsigned slot = atomicAdd(&g_swap_trace_n, 1u) & 255u;
+    for (int i = 0; i < 8; ++i) g_swap_trace[slot * 8 + i] = tr[i];
   }
   ptx::tc_fence_before();
   __syncthreads();

@@ -278,6 +278,20 @@ def test_v2_step_tile_widths(dev, monkeypatch, bnb, mem_len, group, n_sample):
     eng.close()
 
 
+@pytest.mark.parametrize("ksplit", [1, 2, 4])
+def test_v2_layernorm_gemm_split_k(dev, monkeypatch, ksplit):
+    """LayerNorm GEMMs with K divided over 1/2/4 CTAs per feature tile (clusters of 4/8/16 CTAs, partial
+    accumulators added through distributed shared memory)."""
+    monkeypatch.setenv("CAPDEC_KSPLIT", str(ksplit))
+    dec = small_decoder(layers=2, end_bias=1.0)
+    w = torch_port.weights_to_numpy(dec)
+    mem = torch_port.synthetic_memory(45, 49)
+    eng = make_engine(dec.to(dev), "bf16", step_impl="v2", max_images=45, max_group=2, max_mem=49, max_len=10)
+    out = eng.decode_from_memory(mem.to(dev), START, END, max_len=10, group=2, n_sample=1, seed=4, return_logits=True)
+    check_rollout(out, w, mem.numpy(), 2, 1, TOL["bf16"], seed=4)
+    eng.close()
+
+
 def test_v2_cross_attention_many_rollouts_per_image(dev):
     """group > 16: the cross-attention CTA walks several 16-row query tiles over one staged K/V tile."""
     dec = small_decoder(layers=2)
