@@ -86,6 +86,102 @@ self_attn_kernel(const Elem* __restrict__ q, const Elem* __restrict__ kc, const 
   }
 }
 
+// bf16 engine, v2 step path.  Same work split as self_attn_kernel (one warp per (sequence, head), 8 lanes per
+// 128-byte row, 4 rows per warp-wide load) but flash-style over chunks of 32 positions: the K AND V rows of a
+// chunk are requested together (16 independent 16-byte loads per lane in flight, streaming, no L1 allocation)
+// before any arithmetic, so a warp waits for HBM once per chunk instead of twice per rollout position range.
+__device__ __forceinline__ uint4 ld_stream16(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+  return r;
+}
+__global__ void __launch_bounds__(kAttnWarps * 32)
+self_attn_stream_kernel(const bf16* __restrict__ q, const bf16* __restrict__ kc, const bf16* __restrict__ vc,
+                        bf16* __restrict__ out, int M, int t_pad, const DecState* st) {
+  asm volatile("griddepcontrol.wait;" ::: "memory");  // q and the appended K/V rows (PDL launches)
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  if (st->done) return;
+  const int gw = blockIdx.x * kAttnWarps + (threadIdx.x >> 5);
+  if (gw >= M * kH) return;
+  const int lane = threadIdx.x & 31, g = lane >> 3, c = lane & 7;
+  const int n = st->step;  // last valid position
+  const size_t row_base = (size_t)gw * t_pad * kHD + c * 8;  // gw == m*H + h
+  const bf16* kb = kc + row_base;
+  const bf16* vb = vc + row_base;
+  float qv[8];
+  {
+    const uint4 r = *reinterpret_cast<const uint4*>(q + (size_t)gw * kHD + c * 8);
+    const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { qv[2 * i] = __uint_as_float(w[i] << 16) * 0.125f; qv[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u) * 0.125f; }
+  }
+  float m_run = -INFINITY, l_run = 0.f;
+  float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  for (int p0 = 0; p0 <= n; p0 += 32) {
+    uint4 kr[8], vr[8];
+#pragma unroll
+    for (int it = 0; it < 8; ++it) {
+      const int pos = p0 + it * 4 + g;
+      if (pos <= n) {
+        kr[it] = ld_stream16(kb + (size_t)pos * kHD);
+        vr[it] = ld_stream16(vb + (size_t)pos * kHD);
+      } else {
+        kr[it] = make_uint4(0u, 0u, 0u, 0u);
+        vr[it] = make_uint4(0u, 0u, 0u, 0u);
+      }
+    }
+    float s[8];
+    float mc = -INFINITY;
+#pragma unroll
+    for (int it = 0; it < 8; ++it) {
+      const uint32_t w[4] = {kr[it].x, kr[it].y, kr[it].z, kr[it].w};
+      float d = 0.f;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        d = fmaf(qv[2 * i], __uint_as_float(w[i] << 16), d);
+        d = fmaf(qv[2 * i + 1], __uint_as_float(w[i] & 0xffff0000u), d);
+      }
+      d += __shfl_xor_sync(0xffffffffu, d, 1);
+      d += __shfl_xor_sync(0xffffffffu, d, 2);
+      d += __shfl_xor_sync(0xffffffffu, d, 4);
+      s[it] = (p0 + it * 4 + g <= n) ? d : -INFINITY;
+      mc = fmaxf(mc, s[it]);
+    }
+    mc = fmaxf(mc, __shfl_xor_sync(0xffffffffu, mc, 8));
+    mc = fmaxf(mc, __shfl_xor_sync(0xffffffffu, mc, 16));
+    const float m_new = fmaxf(m_run, mc);          // finite: position p0 <= n is in this chunk
+    const float corr = __expf(m_run - m_new);      // exp(-inf) = 0 on the first chunk
+    l_run *= corr;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i] *= corr;
+#pragma unroll
+    for (int it = 0; it < 8; ++it) {
+      const float pr = __expf(s[it] - m_new);      // 0 for masked positions
+      l_run += pr;
+      const uint32_t w[4] = {vr[it].x, vr[it].y, vr[it].z, vr[it].w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        acc[2 * i] = fmaf(pr, __uint_as_float(w[i] << 16), acc[2 * i]);
+        acc[2 * i + 1] = fmaf(pr, __uint_as_float(w[i] & 0xffff0000u), acc[2 * i + 1]);
+      }
+    }
+    m_run = m_new;
+  }
+  l_run += __shfl_xor_sync(0xffffffffu, l_run, 8);
+  l_run += __shfl_xor_sync(0xffffffffu, l_run, 16);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    acc[i] += __shfl_xor_sync(0xffffffffu, acc[i], 8);
+    acc[i] += __shfl_xor_sync(0xffffffffu, acc[i], 16);
+  }
+  if (g == 0) {
+    const float inv = 1.f / l_run;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i] *= inv;
+    store8(out + (size_t)gw * kHD + c * 8, acc);
+  }
+}
+
 // q, out: [n_images*group, 512] image-major; ck/cv: this layer's [n_images][H][S][64].
 // Work item = (image, head, query tile of GT sequences); group % GT == 0.
 template <typename Elem, int GT>

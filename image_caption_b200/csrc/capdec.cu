@@ -306,7 +306,8 @@ static cudaError_t configure_fast_kernels() {
   if (e == cudaSuccess) e = cudaFuncSetAttribute(cross_attn_tma_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(cross_attn_tma_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(cross_attn_tma_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
-  if (e == cudaSuccess) e = cudaFuncSetAttribute(vocab_head_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kVhSmemBytes);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(vocab_head_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, vh_smem_bytes(4));
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(vocab_head_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, vh_smem_bytes(16));
   return e;
 }
 
@@ -761,14 +762,6 @@ static int enqueue_step_fast(capdec_handle h, cudaStream_t s, int n_images, int 
   const DecState* st = h->st;
   const SwapLNParams no_ln{};
   cudaError_t e;
-  {
-    set_tag(h, "embed_pe", (double)M * kD * (4 + 4 + 2));
-    ProfScope ps(h, s);
-    e = launch_ex(embed_pe_kernel<bf16>, dim3((M * (kD / 4) + 255) / 256), dim3(256), 0, s, 1, h->use_pdl,
-                  (const DecState*)h->st, (const CallParams*)h->cp, (const float*)h->emb, (const float*)h->pe, h->x, (bf16*)h->xb, M);
-  }
-  CUDA_TRY(h, e);
-  h->launches_this_enqueue++;
   const double ln_extra = (double)M * kD * (4 + 4 + 2);  // residual read, x and xb written
   for (int l = 0; l < L; ++l) {
     LayerParams& lp = h->layer[l];
@@ -782,12 +775,8 @@ static int enqueue_step_fast(capdec_handle h, cudaStream_t s, int n_images, int 
       {
         const int blocks = (M * kH + kAttnWarps - 1) / kAttnWarps;
         ProfScope ps(h, s);
-        if (h->t_pad == 64)
-          e = launch_ex(self_attn_kernel<bf16, 16>, dim3(blocks), dim3(kAttnWarps * 32), 0, s, 1, h->use_pdl, (const bf16*)h->q,
-                        (const bf16*)kc, (const bf16*)vc, (bf16*)h->a, M, h->t_pad, st);
-        else
-          e = launch_ex(self_attn_kernel<bf16, 32>, dim3(blocks), dim3(kAttnWarps * 32), 0, s, 1, h->use_pdl, (const bf16*)h->q,
-                        (const bf16*)kc, (const bf16*)vc, (bf16*)h->a, M, h->t_pad, st);
+        e = launch_ex(self_attn_stream_kernel, dim3(blocks), dim3(kAttnWarps * 32), 0, s, 1, h->use_pdl, (const bf16*)h->q,
+                      (const bf16*)kc, (const bf16*)vc, (bf16*)h->a, M, h->t_pad, st);
       }
       CUDA_TRY(h, e);
       h->launches_this_enqueue++;
@@ -805,13 +794,13 @@ static int enqueue_step_fast(capdec_handle h, cudaStream_t s, int n_images, int 
         const int per_warp = (KT + 3) / 4;
         ProfScope ps(h, s);
         if (per_warp <= 1)
-          e = launch_ex(cross_attn_tma_kernel<1>, dim3(n_images * kH), dim3(kCaThreads), ca_smem_bytes(S), s, 1, h->use_pdl,
+          e = launch_ex(cross_attn_tma_kernel<1>, dim3(n_images * kH), dim3(kCaThreads), ca_smem_bytes(S, group), s, 1, h->use_pdl,
                         h->tm_ckv, (const bf16*)h->q, (bf16*)h->a, l, n_images, group, S, st);
         else if (per_warp <= 2)
-          e = launch_ex(cross_attn_tma_kernel<2>, dim3(n_images * kH), dim3(kCaThreads), ca_smem_bytes(S), s, 1, h->use_pdl,
+          e = launch_ex(cross_attn_tma_kernel<2>, dim3(n_images * kH), dim3(kCaThreads), ca_smem_bytes(S, group), s, 1, h->use_pdl,
                         h->tm_ckv, (const bf16*)h->q, (bf16*)h->a, l, n_images, group, S, st);
         else
-          e = launch_ex(cross_attn_tma_kernel<4>, dim3(n_images * kH), dim3(kCaThreads), ca_smem_bytes(S), s, 1, h->use_pdl,
+          e = launch_ex(cross_attn_tma_kernel<4>, dim3(n_images * kH), dim3(kCaThreads), ca_smem_bytes(S, group), s, 1, h->use_pdl,
                         h->tm_ckv, (const bf16*)h->q, (bf16*)h->a, l, n_images, group, S, st);
       }
       CUDA_TRY(h, e);
@@ -830,10 +819,16 @@ static int enqueue_step_fast(capdec_handle h, cudaStream_t s, int n_images, int 
     }
   }
   {
-    set_tag(h, "vocab_head", (double)kD * kVPad * 4 + (double)M * (kD * 4 + 8 + 4));
+    set_tag(h, "vocab_head", (double)kD * kVPad * 4 + (double)M * (kD * 4 + 8 + 4) + (double)M * kD * (4 + 4 + 2));
     ProfScope ps(h, s);
-    e = launch_ex(vocab_head_kernel, dim3((M + kVhRows - 1) / kVhRows), dim3(kVhThreads), kVhSmemBytes, s, 1, h->use_pdl, h->st,
-                  (const CallParams*)h->cp, (const float*)h->x, (const float*)h->fc_wT, (const float*)h->fc_b, h->fin, M, h->cfg.vocab);
+    if (M <= 1024)
+      e = launch_ex(vocab_head_kernel<4>, dim3((M + 3) / 4), dim3(128), vh_smem_bytes(4), s, 1, h->use_pdl, h->st,
+                    (const CallParams*)h->cp, h->x, (const float*)h->fc_wT, (const float*)h->fc_b, h->fin, M, h->cfg.vocab,
+                    (const float*)h->emb, (const float*)h->pe, (bf16*)h->xb);
+    else
+      e = launch_ex(vocab_head_kernel<16>, dim3((M + 15) / 16), dim3(512), vh_smem_bytes(16), s, 1, h->use_pdl, h->st,
+                    (const CallParams*)h->cp, h->x, (const float*)h->fc_wT, (const float*)h->fc_b, h->fin, M, h->cfg.vocab,
+                    (const float*)h->emb, (const float*)h->pe, (bf16*)h->xb);
   }
   CUDA_TRY(h, e);
   h->launches_this_enqueue++;
@@ -940,6 +935,7 @@ static int enqueue_cluster_rollout(capdec_handle h, cudaStream_t s, int n_images
 }
 
 // ------------------------------------------------------------------ decode
+static bool mega_applicable(capdec_handle h, int n_images, int S, int group);
 static int validate_decode(capdec_handle h, const capdec_decode_args* a) {
   if (!h->prefilled) return fail(h, CAPDEC_ERR_STATE, "capdec_decode before capdec_prefill");
   if (a->group < 1 || a->n_sample < 0 || a->n_sample > a->group) return fail(h, CAPDEC_ERR_INVALID, "bad group/n_sample (%d/%d)", a->group, a->n_sample);
@@ -984,6 +980,14 @@ extern "C" int capdec_decode(capdec_handle h, const capdec_decode_args* a, void*
   h->launches++;
 
   const int T = a->max_len - 1;
+  if (h->fast && !mega_applicable(h, n_images, S, group)) {
+    // input of step 0; later steps get theirs from the head kernel of the step before
+    set_tag(h, "embed_pe", (double)M * kD * (4 + 4 + 2));
+    ProfScope ps(h, s);
+    embed_pe_kernel<bf16><<<(M * (kD / 4) + 255) / 256, 256, 0, s>>>(h->st, h->cp, h->emb, h->pe, h->x, (bf16*)h->xb, M);
+    CUDA_TRY(h, cudaGetLastError());
+    h->launches++;
+  }
   if (mega_applicable(h, n_images, S, group)) {
     TRY(enqueue_cluster_rollout(h, s, n_images, S, group, T));
   } else if (h->use_graph && !h->profiling) {

@@ -20,8 +20,11 @@ constexpr int kCaQStride = 72;   // bf16 elements per q row in smem (144 B: conf
 constexpr int kCaOStride = 68;   // fp32 elements per partial-output row
 
 __host__ __device__ constexpr int ca_key_rows(int S) { return (S + 15) / 16 * 16; }
-__host__ __device__ constexpr int ca_smem_bytes(int S) {
-  return 1024 + 2 * ca_key_rows(S) * 128 + 16 * kCaQStride * 2 + 4 * 16 * kCaOStride * 4 + 4 * 16 * 2 * 4 + 64;
+// rows of the 16-row query tile that are real (the partial-output scratch is sized by it: greedy decoding
+// with one rollout per image needs 1 KB instead of 17 KB, so ~10 instead of 6 CTAs share an SM)
+__host__ __device__ constexpr int ca_q_rows(int group) { return group < 16 ? group : 16; }
+__host__ __device__ constexpr int ca_smem_bytes(int S, int group) {
+  return 1024 + 2 * ca_key_rows(S) * 128 + 16 * kCaQStride * 2 + 4 * ca_q_rows(group) * kCaOStride * 4 + 4 * 16 * 2 * 4 + 64;
 }
 
 namespace ptx {
@@ -53,8 +56,9 @@ cross_attn_tma_kernel(const __grid_constant__ CUtensorMap tm_kv, const bf16* __r
   uint8_t* k_s = smem;
   uint8_t* v_s = smem + (size_t)SB * 128;
   bf16* q_s = reinterpret_cast<bf16*>(v_s + (size_t)SB * 128);
-  float* o_part = reinterpret_cast<float*>(q_s + 16 * kCaQStride);  // [4][16][kCaOStride]
-  float* ml_part = o_part + 4 * 16 * kCaOStride;                    // [4][16][2]
+  const int GP = ca_q_rows(group);
+  float* o_part = reinterpret_cast<float*>(q_s + 16 * kCaQStride);  // [4][GP][kCaOStride]
+  float* ml_part = o_part + 4 * GP * kCaOStride;                    // [4][16][2]
   uint64_t* bar = reinterpret_cast<uint64_t*>(ml_part + 4 * 16 * 2);  // [2]: K landed, V landed
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -201,11 +205,11 @@ cross_attn_tma_kernel(const __grid_constant__ CUtensorMap tm_kv, const bf16* __r
     l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
 
     // ---- merge the 4 warps
-    float* op = o_part + (size_t)warp * 16 * kCaOStride;
+    float* op = o_part + (size_t)warp * GP * kCaOStride;
 #pragma unroll
     for (int d = 0; d < 8; ++d) {
-      *reinterpret_cast<float2*>(op + g * kCaOStride + d * 8 + 2 * t) = make_float2(o[d][0], o[d][1]);
-      *reinterpret_cast<float2*>(op + (g + 8) * kCaOStride + d * 8 + 2 * t) = make_float2(o[d][2], o[d][3]);
+      if (g < GP) *reinterpret_cast<float2*>(op + g * kCaOStride + d * 8 + 2 * t) = make_float2(o[d][0], o[d][1]);
+      if (g + 8 < GP) *reinterpret_cast<float2*>(op + (g + 8) * kCaOStride + d * 8 + 2 * t) = make_float2(o[d][2], o[d][3]);
     }
     if (t == 0) {
       ml_part[(warp * 16 + g) * 2 + 0] = mx0; ml_part[(warp * 16 + g) * 2 + 1] = l0;
@@ -225,8 +229,8 @@ cross_attn_tma_kernel(const __grid_constant__ CUtensorMap tm_kv, const bf16* __r
           const float mw = ml_part[(w * 16 + r) * 2];
           const float scl = mw == -INFINITY ? 0.f : __expf(mw - m);
           l += scl * ml_part[(w * 16 + r) * 2 + 1];
-          const float4 a = *reinterpret_cast<const float4*>(o_part + ((size_t)w * 16 + r) * kCaOStride + c * 8);
-          const float4 b = *reinterpret_cast<const float4*>(o_part + ((size_t)w * 16 + r) * kCaOStride + c * 8 + 4);
+          const float4 a = *reinterpret_cast<const float4*>(o_part + ((size_t)w * GP + r) * kCaOStride + c * 8);
+          const float4 b = *reinterpret_cast<const float4*>(o_part + ((size_t)w * GP + r) * kCaOStride + c * 8 + 4);
           acc[0] += scl * a.x; acc[1] += scl * a.y; acc[2] += scl * a.z; acc[3] += scl * a.w;
           acc[4] += scl * b.x; acc[5] += scl * b.y; acc[6] += scl * b.z; acc[7] += scl * b.w;
         }

@@ -193,79 +193,81 @@ head_kernel(DecState* st, const CallParams* cp, const float* __restrict__ logits
   }
 }
 
-// Fused vocabulary projection + pick (SURVEY K11+K12+K13): logits never round-trip to HBM.
+// Fused vocabulary projection + pick + next-step embedding (SURVEY K11+K12+K13+K2): logits never
+// round-trip to HBM and the step needs no separate embedding kernel.
 // wT: fc_out.weight transposed and padded, [512][kVPad] fp32; x: [M,512] fp32 residual stream.
-// CTA = 8 warps x 2 rows; the 256 KB of wT stream through shared memory in 32-row slabs
-// (double buffered); lane l accumulates vocabulary entries 4l..4l+3 of its warp's two rows.
-constexpr int kVhRows = 16, kVhThreads = 256, kVhSlab = 32;
-constexpr int kVhSmemBytes = kVhRows * kD * 4 + 2 * kVhSlab * kVPad * 4;
+// CTA = 8 warps x 2 rows; the 256 KB of wT stream through shared memory in 64-row slabs, three in
+// flight (cp.async); lane l accumulates vocabulary entries 4l..4l+3 of its warp's two rows.
+constexpr int kVhSlab = 64, kVhBufs = 3;
+__host__ __device__ constexpr int vh_smem_bytes(int rows) { return rows * kD * 4 + kVhBufs * kVhSlab * kVPad * 4; }
 
-__global__ void __launch_bounds__(kVhThreads)
-vocab_head_kernel(DecState* st, const CallParams* cp, const float* __restrict__ x, const float* __restrict__ wT,
-                  const float* __restrict__ bias, unsigned char* fin, int M, int V) {
+// R = rows per CTA = warps per CTA (one row per warp: the per-row work, 2048 FMA per lane, is the critical path
+// at small batch, so small batches use R = 4 and many CTAs, large batches R = 16 to re-stream wT less often).
+template <int R>
+__global__ void __launch_bounds__(R * 32)
+vocab_head_kernel(DecState* st, const CallParams* cp, float* __restrict__ x, const float* __restrict__ wT,
+                  const float* __restrict__ bias, unsigned char* fin, int M, int V, const float* __restrict__ emb,
+                  const float* __restrict__ pe, bf16* __restrict__ xb) {
+  constexpr int kThreads = R * 32;
   extern __shared__ __align__(16) uint8_t vh_smem[];
-  float* xs = reinterpret_cast<float*>(vh_smem);   // [16][512]
-  float* ws = xs + kVhRows * kD;                   // [2][32][128]
+  float* xs = reinterpret_cast<float*>(vh_smem);   // [R][512]
+  float* ws = xs + R * kD;                         // [3][64][128]
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  auto load_slab = [&](int slab, int buf) {  // 64 x 128 floats = 2048 float4
+    const float4* src = reinterpret_cast<const float4*>(wT + (size_t)slab * kVhSlab * kVPad);
+    float4* dst = reinterpret_cast<float4*>(ws + buf * kVhSlab * kVPad);
+#pragma unroll
+    for (int i = 0; i < 2048 / kThreads; ++i) {
+      const int idx = tid + i * kThreads;
+      const uint32_t d = static_cast<uint32_t>(__cvta_generic_to_shared(dst + idx));
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(src + idx) : "memory");
+    }
+  };
+  // the weights do not depend on the previous kernel: start streaming them before the dependency wait
+  load_slab(0, 0);
+  asm volatile("cp.async.commit_group;" ::: "memory");
+  load_slab(1, 1);
+  asm volatile("cp.async.commit_group;" ::: "memory");
   asm volatile("griddepcontrol.wait;" ::: "memory");
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-  if (st->done) return;
+  if (st->done) { asm volatile("cp.async.wait_group 0;" ::: "memory"); return; }
   const CallParams p = *cp;
   const int n = st->step;
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int r0 = blockIdx.x * kVhRows;
+  const int r0 = blockIdx.x * R;
   // x rows of this CTA -> smem (rows >= M read as zero)
-  for (int i = tid; i < kVhRows * kD / 4; i += kVhThreads) {
+  for (int i = tid; i < R * kD / 4; i += kThreads) {
     const int r = i / (kD / 4), c = i % (kD / 4);
     float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
     if (r0 + r < M) v = *reinterpret_cast<const float4*>(x + (size_t)(r0 + r) * kD + c * 4);
     reinterpret_cast<float4*>(xs)[i] = v;
   }
-  auto load_slab = [&](int slab, int buf) {  // 32 x 128 floats = 1024 float4, 4 per thread
-    const float4* src = reinterpret_cast<const float4*>(wT + (size_t)slab * kVhSlab * kVPad);
-    float4* dst = reinterpret_cast<float4*>(ws + buf * kVhSlab * kVPad);
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int idx = tid + i * kVhThreads;
-      const uint32_t d = static_cast<uint32_t>(__cvta_generic_to_shared(dst + idx));
-      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(src + idx) : "memory");
-    }
-    asm volatile("cp.async.commit_group;" ::: "memory");
-  };
-  load_slab(0, 0);
-  float acc[2][4];
-#pragma unroll
-  for (int r = 0; r < 2; ++r)
-#pragma unroll
-    for (int i = 0; i < 4; ++i) acc[r][i] = 0.f;
-  const float* xr0 = xs + (warp * 2) * kD;
-  const float* xr1 = xr0 + kD;
+  float acc[4] = {0.f, 0.f, 0.f, 0.f};
+  const float* xr = xs + warp * kD;
   constexpr int kSlabs = kD / kVhSlab;
   for (int sl = 0; sl < kSlabs; ++sl) {
-    if (sl + 1 < kSlabs) {
-      load_slab(sl + 1, (sl + 1) & 1);
-      asm volatile("cp.async.wait_group 1;" ::: "memory");
-    } else {
-      asm volatile("cp.async.wait_group 0;" ::: "memory");
-    }
+    if (sl + 2 < kSlabs) load_slab(sl + 2, (sl + 2) % kVhBufs);
+    asm volatile("cp.async.commit_group;" ::: "memory");  // possibly empty: keeps the group count uniform
+    asm volatile("cp.async.wait_group 2;" ::: "memory");
     __syncthreads();
-    const float* wb = ws + (sl & 1) * kVhSlab * kVPad + lane * 4;
+    const float* wb = ws + (sl % kVhBufs) * kVhSlab * kVPad + lane * 4;
+#pragma unroll 4
+    for (int k = 0; k < kVhSlab; k += 4) {
+      const float4 a = *reinterpret_cast<const float4*>(xr + sl * kVhSlab + k);
+      const float av[4] = {a.x, a.y, a.z, a.w};
 #pragma unroll
-    for (int k = 0; k < kVhSlab; ++k) {
-      const float4 w = *reinterpret_cast<const float4*>(wb + k * kVPad);
-      const float a = xr0[sl * kVhSlab + k], b = xr1[sl * kVhSlab + k];
-      acc[0][0] = fmaf(a, w.x, acc[0][0]); acc[0][1] = fmaf(a, w.y, acc[0][1]);
-      acc[0][2] = fmaf(a, w.z, acc[0][2]); acc[0][3] = fmaf(a, w.w, acc[0][3]);
-      acc[1][0] = fmaf(b, w.x, acc[1][0]); acc[1][1] = fmaf(b, w.y, acc[1][1]);
-      acc[1][2] = fmaf(b, w.z, acc[1][2]); acc[1][3] = fmaf(b, w.w, acc[1][3]);
+      for (int kk = 0; kk < 4; ++kk) {
+        const float4 w = *reinterpret_cast<const float4*>(wb + (k + kk) * kVPad);
+        acc[0] = fmaf(av[kk], w.x, acc[0]); acc[1] = fmaf(av[kk], w.y, acc[1]);
+        acc[2] = fmaf(av[kk], w.z, acc[2]); acc[3] = fmaf(av[kk], w.w, acc[3]);
+      }
     }
-    __syncthreads();  // slab buffer (sl & 1) is refilled two iterations later
+    __syncthreads();  // buffer (sl % 3) is refilled by the load issued at the top of iteration sl + 1
   }
   const float4 bv = __ldg(reinterpret_cast<const float4*>(bias) + lane);
-#pragma unroll
-  for (int r = 0; r < 2; ++r) {
-    const int m = r0 + warp * 2 + r;
-    if (m >= M) continue;  // warp-uniform
-    float l[4] = {acc[r][0] + bv.x, acc[r][1] + bv.y, acc[r][2] + bv.z, acc[r][3] + bv.w};
+  {
+    const int m = r0 + warp;
+    if (m < M) {  // warp-uniform
+    float l[4] = {acc[0] + bv.x, acc[1] + bv.y, acc[2] + bv.z, acc[3] + bv.w};
 #pragma unroll
     for (int i = 0; i < 4; ++i) if (lane * 4 + i >= V) l[i] = -INFINITY;
     if (p.logits_dump != nullptr) {
@@ -288,6 +290,22 @@ vocab_head_kernel(DecState* st, const CallParams* cp, const float* __restrict__ 
       } else if (ended) {
         atomicAdd(&st->cnt_end_now, 1);
       }
+    }
+    // embedding of the token just picked = input of the next step (vit:166-169); pe row n+1 exists iff a next step does
+    if (n + 1 < p.max_len - 1) {
+      const float sc = 22.627416997969522f;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int c = i * 128 + lane * 4;
+        const float4 e4 = __ldg(reinterpret_cast<const float4*>(emb + (size_t)tok * kD + c));
+        const float4 p4 = __ldg(reinterpret_cast<const float4*>(pe + (size_t)(n + 1) * kD + c));
+        float4 o;
+        o.x = __fadd_rn(__fmul_rn(e4.x, sc), p4.x); o.y = __fadd_rn(__fmul_rn(e4.y, sc), p4.y);
+        o.z = __fadd_rn(__fmul_rn(e4.z, sc), p4.z); o.w = __fadd_rn(__fmul_rn(e4.w, sc), p4.w);
+        *reinterpret_cast<float4*>(x + (size_t)m * kD + c) = o;
+        store4(xb + (size_t)m * kD + c, o.x, o.y, o.z, o.w);
+      }
+    }
     }
   }
   __syncthreads();
