@@ -247,14 +247,14 @@ static int ln_ksplit(capdec_handle h, int K, int row_tiles) {
 
 template <int BNB, bool kLN, typename Epi>
 static int launch_swap_bnb(capdec_handle h, cudaStream_t s, const CUtensorMap& tw, const CUtensorMap& tx, int M, int n_out,
-                           int K, const Epi& epi, const SwapLNParams& ln, const DecState* st) {
+                           int K, const Epi& epi, const SwapLNParams& ln, const DecState* st, int zsplit = 1) {
   if constexpr (kLN) {
     const int ks = ln_ksplit(h, K, (M + BNB - 1) / BNB);
     if (ks == 4) return launch_swap_ks<BNB, kLN, Epi, 4>(h, s, tw, tx, M, n_out, K, epi, ln, st);
     if (ks == 2) return launch_swap_ks<BNB, kLN, Epi, 2>(h, s, tw, tx, M, n_out, K, epi, ln, st);
   }
-  dim3 grid(n_out / kSwapBF, (M + BNB - 1) / BNB);
-  const int stages = swap_stages(h, BNB, K, grid.x * grid.y);
+  dim3 grid(n_out / kSwapBF, (M + BNB - 1) / BNB, zsplit);
+  const int stages = swap_stages(h, BNB, K / zsplit, grid.x * grid.y * grid.z);
   ProfScope ps(h, s);
   cudaError_t e = launch_ex(gemm_swap_kernel<BNB, kLN, Epi>, grid, dim3(kSwapThreads), swap_smem_bytes(BNB, stages), s,
                             kLN ? 4 : 1, h->use_pdl, tw, tx, M, K, stages, epi, ln, st);
@@ -266,13 +266,13 @@ static int launch_swap_bnb(capdec_handle h, cudaStream_t s, const CUtensorMap& t
 
 template <bool kLN, typename Epi>
 static int launch_swap(capdec_handle h, cudaStream_t s, const CUtensorMap& tw, const CUtensorMap& tx, int M, int n_out, int K,
-                       const Epi& epi, const SwapLNParams& ln, const DecState* st) {
+                       const Epi& epi, const SwapLNParams& ln, const DecState* st, int zsplit = 1) {
   if (K % kSwapBK != 0 || n_out % kSwapBF != 0 || (kLN && n_out != kD))
     return fail(h, CAPDEC_ERR_INVALID, "swap GEMM shape (n_out=%d K=%d ln=%d)", n_out, K, (int)kLN);
   switch (h->bnb) {
-    case 32: return launch_swap_bnb<32, kLN, Epi>(h, s, tw, tx, M, n_out, K, epi, ln, st);
-    case 64: return launch_swap_bnb<64, kLN, Epi>(h, s, tw, tx, M, n_out, K, epi, ln, st);
-    default: return launch_swap_bnb<128, kLN, Epi>(h, s, tw, tx, M, n_out, K, epi, ln, st);
+    case 32: return launch_swap_bnb<32, kLN, Epi>(h, s, tw, tx, M, n_out, K, epi, ln, st, zsplit);
+    case 64: return launch_swap_bnb<64, kLN, Epi>(h, s, tw, tx, M, n_out, K, epi, ln, st, zsplit);
+    default: return launch_swap_bnb<128, kLN, Epi>(h, s, tw, tx, M, n_out, K, epi, ln, st, zsplit);
   }
 }
 
@@ -436,6 +436,8 @@ static int create_impl(capdec_handle h) {
   if (h->use_umma) CUDA_TRY(h, configure_umma_kernels());
   if (h->fast) {
     TRY(dev_alloc(h, &h->fc_wT, (size_t)kD * kVPad));
+    h->part_rows = (int)std::min<size_t>(M, 512);
+    TRY(dev_alloc(h, &h->part, (size_t)4 * h->part_rows * kD));
     CUDA_TRY(h, configure_fast_kernels());
   }
   if (h->mega) {
@@ -495,6 +497,7 @@ extern "C" int capdec_create(const capdec_config* cfg, int device, capdec_handle
   if (const char* e = getenv("CAPDEC_BNB")) h->force_bnb = atoi(e);
   if (const char* e = getenv("CAPDEC_STAGES")) h->force_stages = atoi(e);
   if (const char* e = getenv("CAPDEC_KSPLIT")) h->force_ksplit = atoi(e);
+  if (const char* e = getenv("CAPDEC_NO_FFN2_SPLIT")) h->no_ffn2_split = atoi(e) != 0;
   if (const char* e = getenv("CAPDEC_NO_PDL")) { if (atoi(e)) h->use_pdl = false; }
   int rc = create_impl(h);
   if (rc) {
@@ -813,9 +816,23 @@ static int enqueue_step_fast(capdec_handle h, cudaStream_t s, int n_images, int 
       SwapLinear<bf16, true> e1{(bf16*)h->hbuf, lp.b_1, F};
       set_tag(h, "gemm_ffn1", gemm_bytes(M, F, kD, 2, 2, 2));
       TRY((launch_swap<false>(h, s, lp.m_1.bn[2], h->tx_xb, M, F, kD, e1, no_ln, st)));
-      SwapLNParams ln{h->x, (bf16*)h->xb, lp.b_2, lp.ln_w[2], lp.ln_b[2]};
-      set_tag(h, "gemm_ffn2_ln", gemm_bytes(M, kD, F, 2, 2, 0) + ln_extra);
-      TRY((launch_swap<true>(h, s, lp.m_2.bn[2], h->tx_h, M, kD, F, SwapNoLN{}, ln, st)));
+      const int row_tiles = (M + h->bnb - 1) / h->bnb;
+      if (M <= h->part_rows && 16 * row_tiles <= 148 && F % (4 * kSwapBK) == 0 && !h->no_ffn2_split) {
+        // small batch: K = d_ff divided over 4 CTAs per tile (fp32 partial products), closed by sum_ln
+        SwapLinear<float, false> ep{h->part, nullptr, kD, (long long)M * kD};
+        set_tag(h, "gemm_ffn2_part", gemm_bytes(M, kD, F, 2, 2, 0) + 4.0 * M * kD * 4);
+        TRY((launch_swap<false>(h, s, lp.m_2.bn[2], h->tx_h, M, kD, F, ep, no_ln, st, 4)));
+        set_tag(h, "sum_ln", (double)M * kD * (4 * 4 + 4 + 4 + 2));
+        ProfScope ps(h, s);
+        e = launch_ex(sum_ln_kernel, dim3((M + 3) / 4), dim3(128), 0, s, 1, h->use_pdl, h->x, (const float*)h->part, 4,
+                      (const float*)lp.b_2, (const float*)lp.ln_w[2], (const float*)lp.ln_b[2], (bf16*)h->xb, M, st);
+        CUDA_TRY(h, e);
+        h->launches_this_enqueue++;
+      } else {
+        SwapLNParams ln{h->x, (bf16*)h->xb, lp.b_2, lp.ln_w[2], lp.ln_b[2]};
+        set_tag(h, "gemm_ffn2_ln", gemm_bytes(M, kD, F, 2, 2, 0) + ln_extra);
+        TRY((launch_swap<true>(h, s, lp.m_2.bn[2], h->tx_h, M, kD, F, SwapNoLN{}, ln, st)));
+      }
     }
   }
   {

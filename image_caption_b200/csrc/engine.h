@@ -70,10 +70,13 @@ struct capdec_engine {
   bool fast = false;               // v2 kernels in use (off: CAPDEC_FLAG_V1_STEP)
   bool use_pdl = false;            // programmatic dependent launch between the step's kernels
   int bnb = 32;                    // sequences per GEMM CTA (UMMA N) for the current M
-  int force_bnb = 0, force_stages = 0, force_ksplit = 0;  // tuning overrides (env CAPDEC_BNB / CAPDEC_STAGES)
+  int force_bnb = 0, force_stages = 0, force_ksplit = 0;
+  bool no_ffn2_split = false;  // tuning overrides (env CAPDEC_BNB / CAPDEC_STAGES)
   CUtensorMap tx_xb, tx_a, tx_h;   // activation maps with box rows = bnb
   CUtensorMap tm_ckv;              // whole cross cache as [rows,64], box = 64 x ca_key_rows(S)
   float* fc_wT = nullptr;          // [512][kVPad] fp32: fc_out.weight transposed + padded
+  float* part = nullptr;           // [4][min(M_max,512)][512] fp32 split-K partial products (small batches)
+  int part_rows = 0;
 
   // ---- v3: whole-rollout cluster kernel (rollout_cluster.cuh), used when the shape allows
   bool mega = false;               // enabled (bf16 + tcgen05, not CAPDEC_FLAG_NO_CLUSTER_ROLLOUT)

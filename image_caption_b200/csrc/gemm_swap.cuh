@@ -54,14 +54,16 @@ struct SwapLinear {
   OutT* out;
   const float* bias;
   int ldo;
+  long long zstride = 0;  // split-K launches (gridDim.z > 1): k-slice z writes its partial product to out + z * zstride
   __device__ __forceinline__ void chunk(int f, int r0, int M, const float (&v)[32]) const {
     const float b = bias ? __ldg(bias + f) : 0.f;
+    OutT* o = out + (size_t)blockIdx.z * zstride;
 #pragma unroll
     for (int j = 0; j < 32; ++j) {
       if (r0 + j < M) {
         float r = v[j] + b;
         if (kRelu) r = fmaxf(r, 0.f);
-        out[(size_t)(r0 + j) * ldo + f] = from_f32<OutT>(r);
+        o[(size_t)(r0 + j) * ldo + f] = from_f32<OutT>(r);
       }
     }
   }
@@ -138,8 +140,8 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int f0 = (kLN ? (int)(blockIdx.x & 3) : (int)blockIdx.x) * kSwapBF, b0 = blockIdx.y * BNB;
-  const int ks = kLN ? (int)(blockIdx.x >> 2) : 0;  // k-slice of this CTA
-  const int num_kb = K / kSwapBK / KSPLIT;
+  const int ks = kLN ? (int)(blockIdx.x >> 2) : (int)blockIdx.z;  // k-slice of this CTA
+  const int num_kb = K / kSwapBK / (kLN ? KSPLIT : (int)gridDim.z);
   const int kb0 = ks * num_kb;
   long long tr[8];
   const bool tracing = g_swap_trace != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 64;

@@ -88,6 +88,50 @@ add_ln_kernel(float* __restrict__ x, const float* __restrict__ t, const float* _
   }
 }
 
+// x <- LN(x + bias + sum_z part[z]) : closes a split-K projection whose k-slices wrote fp32 partial
+// products part[z][M][512] (small batches: FFN2's K = 2048 is 128 tcgen05.mma instructions of ~148 cycles
+// in one CTA, 32 per CTA when divided over 4).  One warp per row.
+__global__ void __launch_bounds__(128)
+sum_ln_kernel(float* __restrict__ x, const float* __restrict__ part, int nz, const float* __restrict__ bias,
+              const float* __restrict__ gamma, const float* __restrict__ beta, bf16* __restrict__ xb, int M, const DecState* st) {
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  if (st->done) return;
+  const int row = blockIdx.x * 4 + (threadIdx.x >> 5);
+  if (row >= M) return;
+  const int lane = threadIdx.x & 31;
+  float v[16];
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int c = i * 128 + lane * 4;
+    float4 a = *reinterpret_cast<const float4*>(x + (size_t)row * kD + c);
+    const float4 b = __ldg(reinterpret_cast<const float4*>(bias + c));
+    a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+    for (int z = 0; z < nz; ++z) {
+      const float4 t = *reinterpret_cast<const float4*>(part + ((size_t)z * M + row) * kD + c);
+      a.x += t.x; a.y += t.y; a.z += t.z; a.w += t.w;
+    }
+    v[4 * i] = a.x; v[4 * i + 1] = a.y; v[4 * i + 2] = a.z; v[4 * i + 3] = a.w;
+    s += (a.x + a.y) + (a.z + a.w);
+  }
+  const float mean = warp_sum(s) * (1.f / kD);
+  float q = 0.f;
+#pragma unroll
+  for (int i = 0; i < 16; ++i) { v[i] -= mean; q = fmaf(v[i], v[i], q); }
+  const float rstd = rsqrtf(warp_sum(q) * (1.f / kD) + 1e-5f);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int c = i * 128 + lane * 4;
+    const float4 g = __ldg(reinterpret_cast<const float4*>(gamma + c));
+    const float4 b = __ldg(reinterpret_cast<const float4*>(beta + c));
+    const float r0 = v[4 * i] * rstd * g.x + b.x, r1 = v[4 * i + 1] * rstd * g.y + b.y;
+    const float r2 = v[4 * i + 2] * rstd * g.z + b.z, r3 = v[4 * i + 3] * rstd * g.w + b.w;
+    *reinterpret_cast<float4*>(x + (size_t)row * kD + c) = make_float4(r0, r1, r2, r3);
+    store4(xb + (size_t)row * kD + c, r0, r1, r2, r3);
+  }
+}
+
 // Warp-level argmax / categorical draw over one row of kVPad logits (entries >= V are -inf).
 // Lane l owns vocabulary entries 4l .. 4l+3.  Returns token; *logp_out = log_softmax[token].
 __device__ __forceinline__ int warp_pick(const float (&l)[4], int lane, bool sample, float u, int V, float* logp_out) {

@@ -283,6 +283,7 @@ def test_v2_layernorm_gemm_split_k(dev, monkeypatch, ksplit):
     """LayerNorm GEMMs with K divided over 1/2/4 CTAs per feature tile (clusters of 4/8/16 CTAs, partial
     accumulators added through distributed shared memory)."""
     monkeypatch.setenv("CAPDEC_KSPLIT", str(ksplit))
+    monkeypatch.setenv("CAPDEC_NO_FFN2_SPLIT", "1")  # FFN2 through the LayerNorm GEMM too (large-batch route)
     dec = small_decoder(layers=2, end_bias=1.0)
     w = torch_port.weights_to_numpy(dec)
     mem = torch_port.synthetic_memory(45, 49)
