@@ -61,11 +61,19 @@ def gather_rollout(ids_local: torch.Tensor, logp_local: Optional[torch.Tensor], 
         out[: t.size(0)] = t
         return out
 
+    # NCCL moves device memory only: results that came back through the host-buffer entry point are staged
+    # on this rank's GPU for the gather and returned on the host again
+    stage = None
+    if not ids_local.is_cuda and dist.get_backend(process_group) == "nccl":
+        stage = torch.device("cuda", torch.cuda.current_device())
+
     def gather(t: torch.Tensor) -> torch.Tensor:
-        buf = t.new_empty((world * m_max,) + tuple(t.shape[1:]))
-        dist.all_gather_into_tensor(buf, pad(t), group=process_group)
+        src = pad(t).to(stage, non_blocking=True) if stage is not None else pad(t)
+        buf = src.new_empty((world * m_max,) + tuple(t.shape[1:]))
+        dist.all_gather_into_tensor(buf, src, group=process_group)
         parts = [buf[r * m_max: r * m_max + counts[r] * group] for r in range(world)]
-        return torch.cat(parts, 0)
+        out = torch.cat(parts, 0)
+        return out.cpu() if stage is not None else out
 
     # ids travel as int32 (half the bytes; the vocabulary is tiny) and widen after the gather
     ids = gather(ids_local.to(torch.int32)).to(torch.int64)
