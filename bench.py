@@ -243,7 +243,8 @@ def run_b200_arm(args) -> None:
         "config": {"workload": f"{args.workload}: {desc}", "images_per_gpu": n_img, "mem_len": S, "group": G,
                    "n_sample": ns, "max_len": max_len, "sequences_per_gpu": M, "decode_steps": T,
                    "l2": "flushed between timed steps (512 MiB memset outside the event pairs)",
-                   "weights": "random init, torch.manual_seed(0)", "collective": "all-gather ids+logp" if world > 1 else "none"},
+                   "weights": "random init, torch.manual_seed(0)", "collective": "all-gather ids+logp" if world > 1 else "none",
+                   "engine": "v2 step kernels, one CUDA graph per decode step, programmatic dependent launch"},
         "decode_step_us": 1e3 * ms_per_step / T, "e2e": e2e, "gpu_launches": int(launches), "clocks": clk,
     }
 
@@ -271,9 +272,14 @@ def run_b200_arm(args) -> None:
                    for k, v in sorted(rep.items(), key=lambda kv: -kv[1]["ms"])}
         top = next(iter(kernels))
         tv = rep[top]
+        traffic = None
+        try:  # dram__bytes_read+write per launch of this kernel from the committed ncu --set full capture
+            traffic = json.load(open(os.path.join(ROOT, "profiles", "r01_traffic.json"))).get(args.workload, {}).get(top)
+        except OSError:
+            pass
         line["roofline"] = {"kernel": top, "bound": "hbm", "achieved": tv["bytes"] / (tv["ms"] * 1e-3) / 1e9,
                             "peak": hbm, "unit": "GB/s", "frac": tv["bytes"] / (tv["ms"] * 1e-3) / 1e9 / hbm,
-                            "traffic": None, "bytes_per_launch": tv["bytes"] / tv["launches"],
+                            "traffic": traffic, "bytes_per_launch": tv["bytes"] / tv["launches"],
                             "us_per_launch": 1e3 * tv["ms"] / tv["launches"], "share_of_step": tv["ms"] / tot,
                             "peak_source": peak_src}
         line["kernels"] = kernels
