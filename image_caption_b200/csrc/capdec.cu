@@ -100,6 +100,22 @@ static int make_map(capdec_handle h, CUtensorMap* m, const void* ptr, int rows, 
   return 0;
 }
 
+// Store view of a [rows, cols] activation matrix: box = 128 columns x box_rows, dense (unswizzled) in shared memory.
+static int make_store_map(capdec_handle h, CUtensorMap* m, const void* ptr, int rows, int cols, int box_rows, bool f32) {
+  EncodeTiledFn fn = encode_tiled_fn();
+  if (!fn) return fail(h, CAPDEC_ERR_CUDA, "cuTensorMapEncodeTiled entry point unavailable");
+  const cuuint64_t es = f32 ? 4 : 2;
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)cols * es};
+  cuuint32_t box[2] = {(cuuint32_t)kSwapBF, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(m, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims,
+                  strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                  CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(h, CAPDEC_ERR_CUDA, "cuTensorMapEncodeTiled (store view) failed (%d) rows=%d cols=%d", (int)r, rows, cols);
+  return 0;
+}
+
 static int make_weight_maps(capdec_handle h, WeightMaps* wm, const void* ptr, int n, int k) {
   const int bns[3] = {32, 64, 128};
   for (int i = 0; i < 3; ++i) {
@@ -226,8 +242,9 @@ static int launch_swap_ks(capdec_handle h, cudaStream_t s, const CUtensorMap& tw
   dim3 grid(n_out / kSwapBF * KSPLIT, (M + BNB - 1) / BNB);
   int stages = swap_stages(h, BNB, K / KSPLIT, grid.x * grid.y);
   while (stages > 2 && swap_smem_bytes(BNB, stages, KSPLIT) > kMaxDynSmem) --stages;
+  while (kLN && stages * swap_stage_bytes(BNB) < swap_ln_stage_out_bytes(BNB)) ++stages;  // the output tile is staged in the ring
   ProfScope ps(h, s);
-  cudaError_t e = launch_ex(gemm_swap_kernel<BNB, kLN, Epi, KSPLIT>, grid, dim3(kSwapThreads), swap_smem_bytes(BNB, stages, KSPLIT), s,
+  cudaError_t e = launch_ex(gemm_swap_kernel<BNB, kLN, Epi, KSPLIT>, grid, dim3(swap_threads(BNB)), swap_smem_bytes(BNB, stages, KSPLIT), s,
                             kLN ? 4 * KSPLIT : 1, h->use_pdl, tw, tx, M, K, stages, epi, ln, st);
   if (e != cudaSuccess) return fail(h, CAPDEC_ERR_CUDA, "gemm_swap launch failed: %s (BNB=%d n_out=%d K=%d stages=%d ksplit=%d)",
                                     cudaGetErrorString(e), BNB, n_out, K, stages, KSPLIT);
@@ -254,9 +271,10 @@ static int launch_swap_bnb(capdec_handle h, cudaStream_t s, const CUtensorMap& t
     if (ks == 2) return launch_swap_ks<BNB, kLN, Epi, 2>(h, s, tw, tx, M, n_out, K, epi, ln, st);
   }
   dim3 grid(n_out / kSwapBF, (M + BNB - 1) / BNB, zsplit);
-  const int stages = swap_stages(h, BNB, K / zsplit, grid.x * grid.y * grid.z);
+  int stages = swap_stages(h, BNB, K / zsplit, grid.x * grid.y * grid.z);
+  while (kLN && stages * swap_stage_bytes(BNB) < swap_ln_stage_out_bytes(BNB)) ++stages;  // the output tile is staged in the ring
   ProfScope ps(h, s);
-  cudaError_t e = launch_ex(gemm_swap_kernel<BNB, kLN, Epi>, grid, dim3(kSwapThreads), swap_smem_bytes(BNB, stages), s,
+  cudaError_t e = launch_ex(gemm_swap_kernel<BNB, kLN, Epi>, grid, dim3(swap_threads(BNB)), swap_smem_bytes(BNB, stages), s,
                             kLN ? 4 : 1, h->use_pdl, tw, tx, M, K, stages, epi, ln, st);
   if (e != cudaSuccess) return fail(h, CAPDEC_ERR_CUDA, "gemm_swap launch failed: %s (BNB=%d n_out=%d K=%d stages=%d)",
                                     cudaGetErrorString(e), BNB, n_out, K, stages);
@@ -358,14 +376,15 @@ extern "C" int capdec_destroy(capdec_handle h) {
     cudaMemcpyFromSymbol(&dptr, g_swap_trace, sizeof dptr);
     cudaMemcpyFromSymbol(&n, g_swap_trace_n, sizeof n);
     if (dptr) {
-      static long long t[256 * 8];
+      static long long t[256 * 12];
       cudaMemcpy(t, dptr, sizeof t, cudaMemcpyDeviceToHost);
       const unsigned first = n > 48 ? n - 48 : 0;
       long long prev_exit = 0;
       for (unsigned i = first; i < n; ++i) {
-        const long long* r = t + (i & 255u) * 8;
-        fprintf(stderr, "gemm#%u ln=%lld gap_ns=%lld  cycles: prologue %lld  pdl_wait %lld  load+mma %lld  epilogue %lld  | in-kernel ns %lld\n", i, r[7],
-                prev_exit ? r[0] - prev_exit : 0, r[2] - r[1], r[3] - r[2], r[4] - r[3], r[5] - r[4], r[6] - r[0]);
+        const long long* r = t + (i & 255u) * 12;
+        fprintf(stderr, "gemm#%u ln=%lld gap_ns=%lld  cycles: prologue %lld  pdl_wait %lld  load+mma %lld  epilogue %lld (pass1 %lld, exchange %lld, pass2 %lld: stage %lld, barrier %lld, store %lld)  | in-kernel ns %lld\n", i, r[7],
+                prev_exit ? r[0] - prev_exit : 0, r[2] - r[1], r[3] - r[2], r[4] - r[3], r[5] - r[4],
+                r[8] ? r[8] - r[4] : 0, r[8] ? r[9] - r[8] : 0, r[8] ? r[5] - r[9] : 0, r[8] ? r[10] - r[9] : 0, r[8] ? r[11] - r[10] : 0, r[8] ? r[5] - r[11] : 0, r[6] - r[0]);
         prev_exit = r[6];
       }
     }
@@ -489,8 +508,8 @@ extern "C" int capdec_create(const capdec_config* cfg, int device, capdec_handle
   if (const char* e = getenv("CAPDEC_CHUNK")) h->mega_chunk = std::max(1, atoi(e));
   if (getenv("CAPDEC_TRACE_GEMM")) {
     long long* buf = nullptr;
-    if (cudaMalloc(&buf, 256 * 8 * sizeof(long long)) == cudaSuccess) {
-      cudaMemset(buf, 0, 256 * 8 * sizeof(long long));
+    if (cudaMalloc(&buf, 256 * 12 * sizeof(long long)) == cudaSuccess) {
+      cudaMemset(buf, 0, 256 * 12 * sizeof(long long));
       cudaMemcpyToSymbol(g_swap_trace, &buf, sizeof buf);
     }
   }
@@ -783,7 +802,7 @@ static int enqueue_step_fast(capdec_handle h, cudaStream_t s, int n_images, int 
       }
       CUDA_TRY(h, e);
       h->launches_this_enqueue++;
-      SwapLNParams ln{h->x, (bf16*)h->xb, lp.b_so, lp.ln_w[0], lp.ln_b[0]};
+      SwapLNParams ln{h->x, (bf16*)h->xb, lp.b_so, lp.ln_w[0], lp.ln_b[0], h->ts_x, h->ts_xb};
       set_tag(h, "gemm_self_out_ln", gemm_bytes(M, kD, kD, 2, 2, 0) + ln_extra);
       TRY((launch_swap<true>(h, s, lp.m_so.bn[2], h->tx_a, M, kD, kD, SwapNoLN{}, ln, st)));
     }
@@ -808,7 +827,7 @@ static int enqueue_step_fast(capdec_handle h, cudaStream_t s, int n_images, int 
       }
       CUDA_TRY(h, e);
       h->launches_this_enqueue++;
-      SwapLNParams ln{h->x, (bf16*)h->xb, lp.b_co, lp.ln_w[1], lp.ln_b[1]};
+      SwapLNParams ln{h->x, (bf16*)h->xb, lp.b_co, lp.ln_w[1], lp.ln_b[1], h->ts_x, h->ts_xb};
       set_tag(h, "gemm_cross_out_ln", gemm_bytes(M, kD, kD, 2, 2, 0) + ln_extra);
       TRY((launch_swap<true>(h, s, lp.m_co.bn[2], h->tx_a, M, kD, kD, SwapNoLN{}, ln, st)));
     }
@@ -829,7 +848,7 @@ static int enqueue_step_fast(capdec_handle h, cudaStream_t s, int n_images, int 
         CUDA_TRY(h, e);
         h->launches_this_enqueue++;
       } else {
-        SwapLNParams ln{h->x, (bf16*)h->xb, lp.b_2, lp.ln_w[2], lp.ln_b[2]};
+        SwapLNParams ln{h->x, (bf16*)h->xb, lp.b_2, lp.ln_w[2], lp.ln_b[2], h->ts_x, h->ts_xb};
         set_tag(h, "gemm_ffn2_ln", gemm_bytes(M, kD, F, 2, 2, 0) + ln_extra);
         TRY((launch_swap<true>(h, s, lp.m_2.bn[2], h->tx_h, M, kD, F, SwapNoLN{}, ln, st)));
       }
@@ -870,6 +889,8 @@ static int ensure_activation_maps(capdec_handle h, int M) {
     TRY(make_map(h, &h->tx_xb, h->xb, M, kD, h->bnb));
     TRY(make_map(h, &h->tx_a, h->a, M, kD, h->bnb));
     TRY(make_map(h, &h->tx_h, h->hbuf, M, h->cfg.d_ff, h->bnb));
+    TRY(make_store_map(h, &h->ts_x, h->x, M, kD, h->bnb, true));
+    TRY(make_store_map(h, &h->ts_xb, h->xb, M, kD, h->bnb, false));
   }
   h->maps_for_m = M;
   return 0;

@@ -70,13 +70,8 @@ cross_attn_tma_kernel(const __grid_constant__ CUtensorMap tm_kv, const bf16* __r
     ptx::mbar_init(&bar[0], 1);
     ptx::mbar_init(&bar[1], 1);
     ptx::fence_barrier_init();
-  }
-  __syncthreads();
-  ptx::pdl_wait();
-  ptx::pdl_trigger();
-  if (st->done) return;
-
-  if (tid == 0) {
+    // the projected memory was written at prefill, long before the previous kernel of the step: request the
+    // K and V tiles before the programmatic-launch wait; only the queries have to wait for the step's chain.
     // K/V of one step are streamed once: do not let them displace the weights in L2
     const uint64_t pol = ptx::policy_evict_first();
     const int row_k = (((2 * layer + 0) * n_images + img) * kH + h) * S;
@@ -85,6 +80,13 @@ cross_attn_tma_kernel(const __grid_constant__ CUtensorMap tm_kv, const bf16* __r
     ptx::tma_load_2d_hint(k_s, &tm_kv, &bar[0], 0, row_k, pol);
     ptx::mbar_expect_tx(&bar[1], (uint32_t)SB * 128);
     ptx::tma_load_2d_hint(v_s, &tm_kv, &bar[1], 0, row_v, pol);
+  }
+  __syncthreads();
+  ptx::pdl_wait();
+  ptx::pdl_trigger();
+  if (st->done) {  // rollout over: nothing to compute, but no copy may outlive the CTA
+    if (tid == 0) { ptx::mbar_wait(&bar[0], 0); ptx::mbar_wait(&bar[1], 0); }
+    return;
   }
 
   const int g = lane >> 2, t = lane & 3;

@@ -19,11 +19,16 @@ namespace capdec {
 
 constexpr int kSwapBF = 128;       // output features per CTA (UMMA M)
 constexpr int kSwapBK = 64;        // K per pipeline stage (one 128 B swizzle atom row)
-constexpr int kSwapThreads = 192;
+// warp 0 = TMA producer, warp 1 = MMA issuer, then the epilogue warps: 4 for a 32-column tile (one per TMEM lane
+// quarter), 8 for wider tiles (two per quarter, each taking every other 32-column chunk) -- at BNB = 128 the
+// epilogue is the longest phase of the kernel (measured: 17-19k of ~27k cycles with 4 warps).
+__host__ __device__ constexpr int swap_threads(int bnb) { return bnb == 32 ? 192 : 320; }
 
 __host__ __device__ constexpr int swap_stage_bytes(int bnb) { return (kSwapBF + bnb) * kSwapBK * 2; }
 // pipeline stages + 1 KB alignment slack + barriers/tmem slot (256 B) + LN scratch (16 * bnb floats)
 // + split-K partial tiles received from the cluster peers ((ksplit-1) x 128 x bnb floats)
+// LayerNorm epilogue: the normalised tile (fp32 + bf16 copies, 128 features x bnb rows) is staged in the operand ring
+__host__ __device__ constexpr int swap_ln_stage_out_bytes(int bnb) { return bnb * kSwapBF * (4 + 2); }
 __host__ __device__ constexpr int swap_smem_bytes(int bnb, int stages, int ksplit = 1) {
   return stages * swap_stage_bytes(bnb) + 1024 + 256 + 16 * bnb * 4 + (ksplit - 1) * kSwapBF * bnb * 4;
 }
@@ -103,12 +108,17 @@ struct SwapLNParams {
   const float* bias;   // [512]
   const float* gamma;
   const float* beta;
+  // store views of x (fp32) and xb (bf16): [M, 512], box = 128 features x BNB rows, no swizzle.  The normalised
+  // tile leaves through shared memory and two bulk tensor stores: per-thread global stores ran at ~10 cycles
+  // per warp instruction and were the longest part of the LayerNorm epilogue (measured, CAPDEC_TRACE_GEMM).
+  alignas(64) CUtensorMap ts_x;
+  alignas(64) CUtensorMap ts_xb;
 };
 
 
 struct SwapNoLN {};
 
-// tuning aid (env CAPDEC_TRACE_GEMM): CTA (0,0) of every launch records 8 stamps
+// tuning aid (env CAPDEC_TRACE_GEMM): CTA (0,0) of every launch records 12 stamps
 // {globaltimer at entry, clock at entry, after prologue, after pdl wait, accumulator ready, epilogue done, globaltimer at exit, kLN}
 __device__ long long* g_swap_trace = nullptr;
 __device__ unsigned int g_swap_trace_n = 0;
@@ -119,9 +129,9 @@ __device__ unsigned int g_swap_trace_n = 0;
 // is K/16 instructions; the K range is therefore divided over KSPLIT CTAs whose partial accumulators are
 // added through distributed shared memory by the k-slice-0 CTA of each feature tile.
 template <int BNB, bool kLN, typename Epi, int KSPLIT = 1>
-__global__ void __launch_bounds__(kSwapThreads, 2)
+__global__ void __launch_bounds__(swap_threads(BNB), (kLN && BNB > 32) ? 1 : 2)
 gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CUtensorMap tm_x,
-                 int M, int K, int stages, Epi epi, SwapLNParams ln, const DecState* st) {
+                 int M, int K, int stages, Epi epi, const __grid_constant__ SwapLNParams ln, const DecState* st) {
   static_assert(BNB == 32 || BNB == 64 || BNB == 128, "BNB");
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -143,16 +153,30 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
   const int ks = kLN ? (int)(blockIdx.x >> 2) : (int)blockIdx.z;  // k-slice of this CTA
   const int num_kb = K / kSwapBK / (kLN ? KSPLIT : (int)gridDim.z);
   const int kb0 = ks * num_kb;
-  long long tr[8];
+  const int n_pre = num_kb < stages ? num_kb : stages;  // k-blocks whose weight tiles are requested in the prologue
+  long long tr[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
   const bool tracing = g_swap_trace != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 64;
   if (tracing) { asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tr[0])); tr[1] = clock64(); }
 
-  if (warp == 0 && lane == 0) {
-    ptx::prefetch_tensormap(&tm_w);
-    ptx::prefetch_tensormap(&tm_x);
-    for (int s = 0; s < stages; ++s) { ptx::mbar_init(&full[s], 1); ptx::mbar_init(&empty[s], 1); }
-    ptx::mbar_init(tmem_full, 1);
-    ptx::fence_barrier_init();
+  // TMA and tcgen05 instructions take warp-uniform operands.  Issued under `if (lane == 0)` the compiler cannot prove
+  // uniformity and wraps each one in an elect/broadcast/branch loop (measured: ~150 cycles per MMA, ~150-220 per bulk
+  // copy); issued by the converged warp under elect.sync they cost ~40-75 cycles (tools/mma_probe2.cu).
+  if (warp == 0) {
+    if (ptx::elect_one()) {
+      ptx::prefetch_tensormap(&tm_w);
+      ptx::prefetch_tensormap(&tm_x);
+      for (int s = 0; s < stages; ++s) { ptx::mbar_init(&full[s], 1); ptx::mbar_init(&empty[s], 1); }
+      ptx::mbar_init(tmem_full, 1);
+      ptx::fence_barrier_init();
+      // the weights do not depend on the previous kernel of the step: request the first ring of weight tiles now,
+      // so that only the activation tiles are still to come once the programmatic-launch wait returns
+      const uint64_t keep = ptx::policy_evict_last();  // weights are re-read every step: keep them in L2
+      for (int kb = 0; kb < n_pre; ++kb) {
+        ptx::mbar_expect_tx(&full[kb], kWBytes + kXBytes);
+        ptx::tma_load_2d_hint(smem_w + (size_t)kb * kWBytes, &tm_w, &full[kb], (kb0 + kb) * kSwapBK, f0, keep);
+      }
+    }
+    __syncwarp();
   }
   if (warp == 1) ptx::tmem_alloc(tmem_slot, BNB);
   ptx::tc_fence_before();
@@ -168,45 +192,74 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
   const bool active = !(st != nullptr && st->done);
 
   if (warp == 0) {
-    if (lane == 0 && active) {
-      const uint64_t keep = ptx::policy_evict_last();  // weights are re-read every step: keep them in L2
-      for (int kb = 0; kb < num_kb; ++kb) {
+    if (ptx::elect_one()) {
+      for (int kb = 0; kb < n_pre; ++kb)  // also when the rollout is over: the prologue's barriers must complete
+        ptx::tma_load_2d(smem_x + (size_t)kb * kXBytes, &tm_x, &full[kb], (kb0 + kb) * kSwapBK, b0);
+    }
+    __syncwarp();
+    if (active) {
+      const uint64_t keep = ptx::policy_evict_last();
+      for (int kb = n_pre; kb < num_kb; ++kb) {
         const int s = kb % stages;
         const uint32_t ph = (kb / stages) & 1;
         ptx::mbar_wait(&empty[s], ph ^ 1);
-        ptx::mbar_expect_tx(&full[s], kWBytes + kXBytes);
-        ptx::tma_load_2d_hint(smem_w + (size_t)s * kWBytes, &tm_w, &full[s], (kb0 + kb) * kSwapBK, f0, keep);
-        ptx::tma_load_2d(smem_x + (size_t)s * kXBytes, &tm_x, &full[s], (kb0 + kb) * kSwapBK, b0);
+        if (ptx::elect_one()) {
+          ptx::mbar_expect_tx(&full[s], kWBytes + kXBytes);
+          ptx::tma_load_2d_hint(smem_w + (size_t)s * kWBytes, &tm_w, &full[s], (kb0 + kb) * kSwapBK, f0, keep);
+          ptx::tma_load_2d(smem_x + (size_t)s * kXBytes, &tm_x, &full[s], (kb0 + kb) * kSwapBK, b0);
+        }
+        __syncwarp();
       }
+    } else {
+      for (int kb = 0; kb < n_pre; ++kb) ptx::mbar_wait(&full[kb], 0);  // no copy may outlive the CTA
     }
     __syncwarp();
     if (kLN) { ptx::cluster_wait(); ptx::cluster_arrive(); ptx::cluster_wait(); }
     if (kLN && KSPLIT > 1) ptx::cluster_sync();
   } else if (warp == 1) {
-    if (lane == 0 && active) {
+    if (active) {
       constexpr uint32_t idesc = ptx::umma_idesc_bf16(BNB);
       for (int kb = 0; kb < num_kb; ++kb) {
         const int s = kb % stages;
         const uint32_t ph = (kb / stages) & 1;
         ptx::mbar_wait(&full[s], ph);
         ptx::tc_fence_after();
-        const uint32_t w_addr = ptx::smem_u32(smem_w + (size_t)s * kWBytes);
-        const uint32_t x_addr = ptx::smem_u32(smem_x + (size_t)s * kXBytes);
+        if (ptx::elect_one()) {
+          const uint32_t w_addr = ptx::smem_u32(smem_w + (size_t)s * kWBytes);
+          const uint32_t x_addr = ptx::smem_u32(smem_x + (size_t)s * kXBytes);
 #pragma unroll
-        for (int k = 0; k < kSwapBK / 16; ++k)
-          ptx::umma_f16(tmem_base, ptx::umma_desc_sw128(w_addr + k * 32), ptx::umma_desc_sw128(x_addr + k * 32),
-                        idesc, (kb | k) != 0 ? 1u : 0u);
-        ptx::umma_commit(&empty[s]);
+          for (int k = 0; k < kSwapBK / 16; ++k)
+            ptx::umma_f16(tmem_base, ptx::umma_desc_sw128(w_addr + k * 32), ptx::umma_desc_sw128(x_addr + k * 32),
+                          idesc, (kb | k) != 0 ? 1u : 0u);
+          ptx::umma_commit(&empty[s]);
+          if (kb == num_kb - 1) ptx::umma_commit(tmem_full);  // same thread as the MMAs it tracks
+        }
+        __syncwarp();
       }
-      ptx::umma_commit(tmem_full);
     }
     __syncwarp();
     if (kLN) { ptx::cluster_wait(); ptx::cluster_arrive(); ptx::cluster_wait(); }
     if (kLN && KSPLIT > 1) ptx::cluster_sync();
   } else {
-    const int quarter = warp & 3;  // TMEM lane quarter this warp may read
+    constexpr int kEpi = swap_threads(BNB) - 64;  // epilogue threads
+    constexpr int kCStep = kEpi / 4;               // columns covered by one round of the epilogue warps (32 or 64)
+    const int quarter = warp & 3;                  // TMEM lane quarter this warp may read
+    const int cbeg = ((warp - 2) >> 2) * 32;       // first column chunk of this warp
     const int f = f0 + quarter * 32 + lane;
     const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16);
+    constexpr int kChunks = BNB / kCStep;  // 32-column chunks per epilogue warp (1 or 2)
+    float xres[kLN ? kChunks : 1][kLN ? 32 : 1];  // kLN: residual rows of this thread's feature, fetched while the MMAs run
+    if constexpr (kLN) {
+      if (active && ks == 0) {
+#pragma unroll
+        for (int ch = 0; ch < kChunks; ++ch)
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const int row = b0 + cbeg + ch * kCStep + j;
+            xres[ch][j] = row < M ? ln.x[(size_t)row * kD + f] : 0.f;
+          }
+      }
+    }
     if (active) {
       ptx::mbar_wait(tmem_full, 0);
       ptx::tc_fence_after();
@@ -215,14 +268,14 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
     if constexpr (!kLN) {
       if (active) {
 #pragma unroll 1
-        for (int c0 = 0; c0 < BNB; c0 += 32) {
+        for (int c0 = cbeg; c0 < BNB; c0 += kCStep) {
           float v[32];
           ptx::tmem_ld32(taddr + (uint32_t)c0, v);
           epi.chunk(f, b0 + c0, M, v);
         }
       }
     } else {
-      const int e = threadIdx.x - 64;  // 0..127
+      const int e = threadIdx.x - 64;  // 0..kEpi-1
       const int fl = quarter * 32 + lane;  // feature within the tile
       const float bias_f = __ldg(ln.bias + f);
       const bool lead = ks == 0;           // this CTA owns the epilogue of its feature tile
@@ -231,7 +284,7 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
         if (active && !lead) {  // hand the partial accumulators of this k-slice to the k-slice-0 CTA
           const uint32_t dst0 = ptx::map_to_cta(part + ((size_t)(ks - 1) * kSwapBF + fl) * BNB, (uint32_t)(blockIdx.x & 3));
 #pragma unroll 1
-          for (int c0 = 0; c0 < BNB; c0 += 32) {
+          for (int c0 = cbeg; c0 < BNB; c0 += kCStep) {
             float v[32];
             ptx::tmem_ld32(taddr + (uint32_t)c0, v);
 #pragma unroll
@@ -243,8 +296,9 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
         ptx::cluster_wait();
       }
       if (active && lead) {
-#pragma unroll 1
-        for (int c0 = 0; c0 < BNB; c0 += 32) {
+#pragma unroll
+        for (int ch = 0; ch < kChunks; ++ch) {
+          const int c0 = cbeg + ch * kCStep;
           float v[32], a[32], q[32];
           ptx::tmem_ld32(taddr + (uint32_t)c0, v);
           if constexpr (KSPLIT > 1) {
@@ -260,8 +314,7 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
           }
 #pragma unroll
           for (int j = 0; j < 32; ++j) {
-            const int row = b0 + c0 + j;
-            v[j] += bias_f + (row < M ? ln.x[(size_t)row * kD + f] : 0.f);
+            v[j] += bias_f + xres[ch][j];
             a[j] = v[j];
             q[j] = v[j] * v[j];
           }
@@ -272,11 +325,12 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
           red[(1 * 4 + quarter) * BNB + c0 + lane] = s2;
         }
       }
-      ptx::bar_sync(1, 128);
+      if (tracing) tr[8] = clock64();
+      ptx::bar_sync(1, kEpi);
       if constexpr (KSPLIT == 1) ptx::cluster_wait();  // #1
       if (active && lead) {
         const uint32_t my_rank = blockIdx.x & 3;  // feature tile == cluster rank of the k-slice-0 CTAs
-        for (int idx = e; idx < 2 * BNB; idx += 128) {
+        for (int idx = e; idx < 2 * BNB; idx += kEpi) {
           const int which = idx / BNB, c = idx - which * BNB;
           const float tot = (red[(which * 4 + 0) * BNB + c] + red[(which * 4 + 1) * BNB + c]) +
                             (red[(which * 4 + 2) * BNB + c] + red[(which * 4 + 3) * BNB + c]);
@@ -288,7 +342,7 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
       ptx::cluster_arrive();  // #2 / #3 (release: the DSMEM stores above)
       ptx::cluster_wait();
       if (active && lead) {
-        for (int c = e; c < BNB; c += 128) {
+        for (int c = e; c < BNB; c += kEpi) {
           const float s1 = (clu[(0 * 2 + 0) * BNB + c] + clu[(1 * 2 + 0) * BNB + c]) +
                            (clu[(2 * 2 + 0) * BNB + c] + clu[(3 * 2 + 0) * BNB + c]);
           const float s2 = (clu[(0 * 2 + 1) * BNB + c] + clu[(1 * 2 + 1) * BNB + c]) +
@@ -299,23 +353,34 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
           red[BNB + c] = rsqrtf(var + 1e-5f);
         }
       }
-      ptx::bar_sync(1, 128);
+      ptx::bar_sync(1, kEpi);
+      if (tracing) tr[9] = clock64();
       if (active && lead) {
+        // every MMA has completed (tmem_full), so the operand ring is free: stage the output tile there
+        float* x_stage = reinterpret_cast<float*>(smem);                        // [BNB][128] fp32
+        bf16* xb_stage = reinterpret_cast<bf16*>(smem + (size_t)BNB * kSwapBF * 4);  // [BNB][128] bf16
         const float g = __ldg(ln.gamma + f), be = __ldg(ln.beta + f);
 #pragma unroll 1
-        for (int c0 = 0; c0 < BNB; c0 += 32) {
+        for (int c0 = cbeg; c0 < BNB; c0 += kCStep) {
           float v[32];
           ptx::tmem_ld32(taddr + (uint32_t)c0, v);
 #pragma unroll
           for (int j = 0; j < 32; ++j) {
-            const int row = b0 + c0 + j;
-            if (row < M) {
-              const float y = (v[j] - red[c0 + j]) * red[BNB + c0 + j] * g + be;
-              ln.x[(size_t)row * kD + f] = y;
-              ln.xb[(size_t)row * kD + f] = __float2bfloat16_rn(y);
-            }
+            const float y = (v[j] - red[c0 + j]) * red[BNB + c0 + j] * g + be;
+            x_stage[(c0 + j) * kSwapBF + fl] = y;
+            xb_stage[(c0 + j) * kSwapBF + fl] = __float2bfloat16_rn(y);
           }
         }
+        ptx::fence_proxy_async();
+      }
+      if (tracing) tr[10] = clock64();
+      ptx::bar_sync(1, kEpi);
+      if (tracing) tr[11] = clock64();
+      if (active && lead && e == 0) {  // rows >= M are clipped by the maps
+        ptx::tma_store_2d(&ln.ts_x, smem, f0, b0);
+        ptx::tma_store_2d(&ln.ts_xb, smem + (size_t)BNB * kSwapBF * 4, f0, b0);
+        ptx::bulk_commit();
+        ptx::bulk_wait_read0();
       }
     }
   }
@@ -324,7 +389,7 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tr[6]));
     tr[7] = kLN ? 1 : 0;
     const unsigned slot = atomicAdd(&g_swap_trace_n, 1u) & 255u;
-    for (int i = 0; i < 8; ++i) g_swap_trace[slot * 8 + i] = tr[i];
+    for (int i = 0; i < 12; ++i) g_swap_trace[slot * 12 + i] = tr[i];
   }
   ptx::tc_fence_before();
   __syncthreads();
