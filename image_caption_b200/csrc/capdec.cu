@@ -244,7 +244,7 @@ static int launch_swap_ks(capdec_handle h, cudaStream_t s, const CUtensorMap& tw
   while (stages > 2 && swap_smem_bytes(BNB, stages, KSPLIT) > kMaxDynSmem) --stages;
   while (kLN && stages * swap_stage_bytes(BNB) < swap_ln_stage_out_bytes(BNB)) ++stages;  // the output tile is staged in the ring
   ProfScope ps(h, s);
-  cudaError_t e = launch_ex(gemm_swap_kernel<BNB, kLN, Epi, KSPLIT>, grid, dim3(swap_threads(BNB)), swap_smem_bytes(BNB, stages, KSPLIT), s,
+  cudaError_t e = launch_ex(gemm_swap_kernel<BNB, kLN, Epi, KSPLIT>, grid, dim3(swap_threads(BNB, kLN)), swap_smem_bytes(BNB, stages, KSPLIT), s,
                             kLN ? 4 * KSPLIT : 1, h->use_pdl, tw, tx, M, K, stages, epi, ln, st);
   if (e != cudaSuccess) return fail(h, CAPDEC_ERR_CUDA, "gemm_swap launch failed: %s (BNB=%d n_out=%d K=%d stages=%d ksplit=%d)",
                                     cudaGetErrorString(e), BNB, n_out, K, stages, KSPLIT);
@@ -254,9 +254,12 @@ static int launch_swap_ks(capdec_handle h, cudaStream_t s, const CUtensorMap& tw
 
 // LayerNorm GEMMs may divide K over the cluster (4 feature tiles x ksplit CTAs).
 static int ln_ksplit(capdec_handle h, int K, int row_tiles) {
-  // measured (B200, tools/step_time.py): 8-CTA clusters pay only while the whole grid is one small wave
-  // (cfg2: 476 -> 459 us/step); 16-CTA clusters and larger grids lose to cluster scheduling (cfg5: 764 -> 957)
-  int ks = h->force_ksplit > 0 ? h->force_ksplit : (8 * row_tiles <= 64 ? 2 : 1);
+  // History (B200, tools/step_time.py): while every MMA cost ~150 cycles to issue (per-lane issue, see gemm_swap.cuh)
+  // 8-CTA clusters paid for one small wave (cfg2: 476 -> 459 us/step).  With elect.sync issue the K = 512 chain is
+  // ~2.4k cycles and the DSMEM hand-over costs more than it saves (cfg2: 368.6 with 2 slices, 361.2 with 1), so the
+  // default is no split; CAPDEC_KSPLIT keeps the path testable.
+  (void)row_tiles;
+  int ks = h->force_ksplit > 0 ? h->force_ksplit : 1;
   if (h->bnb == 128 && ks > 2) ks = 2;  // the received partial tiles must fit beside the pipeline stages
   if (ks != 1 && ks != 2 && ks != 4) ks = 1;
   return (K / kSwapBK) % ks == 0 ? ks : 1;
@@ -274,7 +277,7 @@ static int launch_swap_bnb(capdec_handle h, cudaStream_t s, const CUtensorMap& t
   int stages = swap_stages(h, BNB, K / zsplit, grid.x * grid.y * grid.z);
   while (kLN && stages * swap_stage_bytes(BNB) < swap_ln_stage_out_bytes(BNB)) ++stages;  // the output tile is staged in the ring
   ProfScope ps(h, s);
-  cudaError_t e = launch_ex(gemm_swap_kernel<BNB, kLN, Epi>, grid, dim3(swap_threads(BNB)), swap_smem_bytes(BNB, stages), s,
+  cudaError_t e = launch_ex(gemm_swap_kernel<BNB, kLN, Epi>, grid, dim3(swap_threads(BNB, kLN)), swap_smem_bytes(BNB, stages), s,
                             kLN ? 4 : 1, h->use_pdl, tw, tx, M, K, stages, epi, ln, st);
   if (e != cudaSuccess) return fail(h, CAPDEC_ERR_CUDA, "gemm_swap launch failed: %s (BNB=%d n_out=%d K=%d stages=%d)",
                                     cudaGetErrorString(e), BNB, n_out, K, stages);
@@ -384,7 +387,10 @@ extern "C" int capdec_destroy(capdec_handle h) {
         const long long* r = t + (i & 255u) * 12;
         fprintf(stderr, "gemm#%u ln=%lld gap_ns=%lld  cycles: prologue %lld  pdl_wait %lld  load+mma %lld  epilogue %lld (pass1 %lld, exchange %lld, pass2 %lld: stage %lld, barrier %lld, store %lld)  | in-kernel ns %lld\n", i, r[7],
                 prev_exit ? r[0] - prev_exit : 0, r[2] - r[1], r[3] - r[2], r[4] - r[3], r[5] - r[4],
-                r[8] ? r[8] - r[4] : 0, r[8] ? r[9] - r[8] : 0, r[8] ? r[5] - r[9] : 0, r[8] ? r[10] - r[9] : 0, r[8] ? r[11] - r[10] : 0, r[8] ? r[5] - r[11] : 0, r[6] - r[0]);
+                r[7] ? r[8] - r[4] : 0, r[7] ? r[9] - r[8] : 0, r[7] ? r[5] - r[9] : 0, r[7] ? r[10] - r[9] : 0, r[7] ? r[11] - r[10] : 0, r[7] ? r[5] - r[11] : 0, r[6] - r[0]);
+        if (!r[7] && r[8])
+          fprintf(stderr, "          mainloop, cycles since the pdl wait returned: activation tiles requested %lld, first tile landed %lld, all mma issued %lld, accumulator seen %lld\n",
+                  r[8] - r[3], r[9] - r[3], r[10] - r[3], r[4] - r[3]);
         prev_exit = r[6];
       }
     }
@@ -513,6 +519,7 @@ extern "C" int capdec_create(const capdec_config* cfg, int device, capdec_handle
       cudaMemcpyToSymbol(g_swap_trace, &buf, sizeof buf);
     }
   }
+  if (const char* e = getenv("CAPDEC_LN_TMA_STORE")) h->force_ln_tma_store = atoi(e) != 0 ? 1 : 0;
   if (const char* e = getenv("CAPDEC_BNB")) h->force_bnb = atoi(e);
   if (const char* e = getenv("CAPDEC_STAGES")) h->force_stages = atoi(e);
   if (const char* e = getenv("CAPDEC_KSPLIT")) h->force_ksplit = atoi(e);
@@ -802,7 +809,7 @@ static int enqueue_step_fast(capdec_handle h, cudaStream_t s, int n_images, int 
       }
       CUDA_TRY(h, e);
       h->launches_this_enqueue++;
-      SwapLNParams ln{h->x, (bf16*)h->xb, lp.b_so, lp.ln_w[0], lp.ln_b[0], h->ts_x, h->ts_xb};
+      SwapLNParams ln{h->x, (bf16*)h->xb, lp.b_so, lp.ln_w[0], lp.ln_b[0], h->ts_x, h->ts_xb, h->ln_tma_store};
       set_tag(h, "gemm_self_out_ln", gemm_bytes(M, kD, kD, 2, 2, 0) + ln_extra);
       TRY((launch_swap<true>(h, s, lp.m_so.bn[2], h->tx_a, M, kD, kD, SwapNoLN{}, ln, st)));
     }
@@ -827,7 +834,7 @@ static int enqueue_step_fast(capdec_handle h, cudaStream_t s, int n_images, int 
       }
       CUDA_TRY(h, e);
       h->launches_this_enqueue++;
-      SwapLNParams ln{h->x, (bf16*)h->xb, lp.b_co, lp.ln_w[1], lp.ln_b[1], h->ts_x, h->ts_xb};
+      SwapLNParams ln{h->x, (bf16*)h->xb, lp.b_co, lp.ln_w[1], lp.ln_b[1], h->ts_x, h->ts_xb, h->ln_tma_store};
       set_tag(h, "gemm_cross_out_ln", gemm_bytes(M, kD, kD, 2, 2, 0) + ln_extra);
       TRY((launch_swap<true>(h, s, lp.m_co.bn[2], h->tx_a, M, kD, kD, SwapNoLN{}, ln, st)));
     }
@@ -848,7 +855,7 @@ static int enqueue_step_fast(capdec_handle h, cudaStream_t s, int n_images, int 
         CUDA_TRY(h, e);
         h->launches_this_enqueue++;
       } else {
-        SwapLNParams ln{h->x, (bf16*)h->xb, lp.b_2, lp.ln_w[2], lp.ln_b[2], h->ts_x, h->ts_xb};
+        SwapLNParams ln{h->x, (bf16*)h->xb, lp.b_2, lp.ln_w[2], lp.ln_b[2], h->ts_x, h->ts_xb, h->ln_tma_store};
         set_tag(h, "gemm_ffn2_ln", gemm_bytes(M, kD, F, 2, 2, 0) + ln_extra);
         TRY((launch_swap<true>(h, s, lp.m_2.bn[2], h->tx_h, M, kD, F, SwapNoLN{}, ln, st)));
       }
@@ -889,6 +896,9 @@ static int ensure_activation_maps(capdec_handle h, int M) {
     TRY(make_map(h, &h->tx_xb, h->xb, M, kD, h->bnb));
     TRY(make_map(h, &h->tx_a, h->a, M, kD, h->bnb));
     TRY(make_map(h, &h->tx_h, h->hbuf, M, h->cfg.d_ff, h->bnb));
+    // measured (B200): staging + bulk stores win for 32-row tiles (cfg2 372.6 -> 368.6 us/step), per-thread stores
+    // for wider ones (cfg3 974 -> 958, cfg5 627 -> 620): the 96 KB tile takes ~3.3k cycles to drain
+    h->ln_tma_store = h->force_ln_tma_store >= 0 ? h->force_ln_tma_store : (h->bnb == 32 ? 1 : 0);
     TRY(make_store_map(h, &h->ts_x, h->x, M, kD, h->bnb, true));
     TRY(make_store_map(h, &h->ts_xb, h->xb, M, kD, h->bnb, false));
   }

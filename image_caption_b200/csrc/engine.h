@@ -74,6 +74,8 @@ struct capdec_engine {
   bool no_ffn2_split = false;  // tuning overrides (env CAPDEC_BNB / CAPDEC_STAGES)
   CUtensorMap tx_xb, tx_a, tx_h;   // activation maps with box rows = bnb
   CUtensorMap ts_x, ts_xb;         // store views of the residual stream (fp32 / bf16), box = 128 x bnb
+  int ln_tma_store = 1;            // LayerNorm epilogue leaves through bulk tensor stores
+  int force_ln_tma_store = -1;     // env CAPDEC_LN_TMA_STORE
   CUtensorMap tm_ckv;              // whole cross cache as [rows,64], box = 64 x ca_key_rows(S)
   float* fc_wT = nullptr;          // [512][kVPad] fp32: fc_out.weight transposed + padded
   float* part = nullptr;           // [4][min(M_max,512)][512] fp32 split-K partial products (small batches)

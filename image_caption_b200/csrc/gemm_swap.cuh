@@ -22,7 +22,17 @@ constexpr int kSwapBK = 64;        // K per pipeline stage (one 128 B swizzle at
 // warp 0 = TMA producer, warp 1 = MMA issuer, then the epilogue warps: 4 for a 32-column tile (one per TMEM lane
 // quarter), 8 for wider tiles (two per quarter, each taking every other 32-column chunk) -- at BNB = 128 the
 // epilogue is the longest phase of the kernel (measured: 17-19k of ~27k cycles with 4 warps).
-__host__ __device__ constexpr int swap_threads(int bnb) { return bnb == 32 ? 192 : 320; }
+// The last warp is a second MMA issuer: one warp sustains ~75-130 cycles per tcgen05.mma of this size, the tensor
+// pipe ~40 (tools/mma_probe2.cu), so even and odd k-blocks are issued by two warps into two accumulators that the
+// epilogue adds.
+// (Wide tiles without LayerNorm keep one issuer: they run two CTAs per SM, whose register budget the second
+// accumulator's epilogue would exceed, and their MMA issue already overlaps the other CTA's epilogue.)
+__host__ __device__ constexpr int swap_epi_threads(int bnb) { return bnb == 32 ? 128 : 256; }
+#ifndef CAPDEC_SWAP_ISSUERS32
+#define CAPDEC_SWAP_ISSUERS32 2
+#endif
+__host__ __device__ constexpr int swap_issuers(int bnb, bool ln) { return bnb == 32 ? CAPDEC_SWAP_ISSUERS32 : (ln ? 2 : 1); }
+__host__ __device__ constexpr int swap_threads(int bnb, bool ln) { return 64 + swap_epi_threads(bnb) + 32 * (swap_issuers(bnb, ln) - 1); }
 
 __host__ __device__ constexpr int swap_stage_bytes(int bnb) { return (kSwapBF + bnb) * kSwapBK * 2; }
 // pipeline stages + 1 KB alignment slack + barriers/tmem slot (256 B) + LN scratch (16 * bnb floats)
@@ -113,6 +123,7 @@ struct SwapLNParams {
   // per warp instruction and were the longest part of the LayerNorm epilogue (measured, CAPDEC_TRACE_GEMM).
   alignas(64) CUtensorMap ts_x;
   alignas(64) CUtensorMap ts_xb;
+  int tma_store;  // 1: output tile staged in shared memory and written by two bulk tensor stores; 0: per-thread stores
 };
 
 
@@ -129,7 +140,7 @@ __device__ unsigned int g_swap_trace_n = 0;
 // is K/16 instructions; the K range is therefore divided over KSPLIT CTAs whose partial accumulators are
 // added through distributed shared memory by the k-slice-0 CTA of each feature tile.
 template <int BNB, bool kLN, typename Epi, int KSPLIT = 1>
-__global__ void __launch_bounds__(swap_threads(BNB), (kLN && BNB > 32) ? 1 : 2)
+__global__ void __launch_bounds__(swap_threads(BNB, kLN), (kLN && BNB > 32) ? 1 : 2)
 gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CUtensorMap tm_x,
                  int M, int K, int stages, Epi epi, const __grid_constant__ SwapLNParams ln, const DecState* st) {
   static_assert(BNB == 32 || BNB == 64 || BNB == 128, "BNB");
@@ -149,13 +160,17 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
   float* part = red + 16 * BNB;                                                    // [KSPLIT-1][128][BNB] partial tiles
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  constexpr int kIssuers = swap_issuers(BNB, kLN);
+  constexpr int kIssuer2 = 2 + swap_epi_threads(BNB) / 32;  // first of the kIssuers - 1 extra issuer warps (the last warps)
   const int f0 = (kLN ? (int)(blockIdx.x & 3) : (int)blockIdx.x) * kSwapBF, b0 = blockIdx.y * BNB;
   const int ks = kLN ? (int)(blockIdx.x >> 2) : (int)blockIdx.z;  // k-slice of this CTA
   const int num_kb = K / kSwapBK / (kLN ? KSPLIT : (int)gridDim.z);
   const int kb0 = ks * num_kb;
+  const int n_acc = num_kb < kIssuers ? num_kb : kIssuers;  // issuers (= accumulators) that have k-blocks at all
   const int n_pre = num_kb < stages ? num_kb : stages;  // k-blocks whose weight tiles are requested in the prologue
   long long tr[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
-  const bool tracing = g_swap_trace != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 64;
+  const bool trace_cta = g_swap_trace != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0;
+  const bool tracing = trace_cta && threadIdx.x == 64;
   if (tracing) { asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tr[0])); tr[1] = clock64(); }
 
   // TMA and tcgen05 instructions take warp-uniform operands.  Issued under `if (lane == 0)` the compiler cannot prove
@@ -166,7 +181,7 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
       ptx::prefetch_tensormap(&tm_w);
       ptx::prefetch_tensormap(&tm_x);
       for (int s = 0; s < stages; ++s) { ptx::mbar_init(&full[s], 1); ptx::mbar_init(&empty[s], 1); }
-      ptx::mbar_init(tmem_full, 1);
+      ptx::mbar_init(tmem_full, n_acc);  // one arrival per MMA issuer
       ptx::fence_barrier_init();
       // the weights do not depend on the previous kernel of the step: request the first ring of weight tiles now,
       // so that only the activation tiles are still to come once the programmatic-launch wait returns
@@ -178,7 +193,7 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
     }
     __syncwarp();
   }
-  if (warp == 1) ptx::tmem_alloc(tmem_slot, BNB);
+  if (warp == 1) ptx::tmem_alloc(tmem_slot, kIssuers * BNB);  // one accumulator per issuer (even / odd k-blocks)
   ptx::tc_fence_before();
   __syncthreads();
   ptx::tc_fence_after();
@@ -195,6 +210,7 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
     if (ptx::elect_one()) {
       for (int kb = 0; kb < n_pre; ++kb)  // also when the rollout is over: the prologue's barriers must complete
         ptx::tma_load_2d(smem_x + (size_t)kb * kXBytes, &tm_x, &full[kb], (kb0 + kb) * kSwapBK, b0);
+      if (!kLN && trace_cta) reinterpret_cast<long long*>(red)[0] = clock64();  // activation tiles requested
     }
     __syncwarp();
     if (active) {
@@ -216,23 +232,27 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
     __syncwarp();
     if (kLN) { ptx::cluster_wait(); ptx::cluster_arrive(); ptx::cluster_wait(); }
     if (kLN && KSPLIT > 1) ptx::cluster_sync();
-  } else if (warp == 1) {
+  } else if (warp == 1 || warp >= kIssuer2) {
     if (active) {
       constexpr uint32_t idesc = ptx::umma_idesc_bf16(BNB);
-      for (int kb = 0; kb < num_kb; ++kb) {
+      const int first = warp == 1 ? 0 : warp - kIssuer2 + 1;  // this issuer's k-blocks: first, first + kIssuers, ...
+      const uint32_t acc = tmem_base + (uint32_t)(first * BNB);
+      for (int kb = first; kb < num_kb; kb += kIssuers) {
         const int s = kb % stages;
         const uint32_t ph = (kb / stages) & 1;
         ptx::mbar_wait(&full[s], ph);
         ptx::tc_fence_after();
         if (ptx::elect_one()) {
+          if (!kLN && trace_cta && kb == 0) reinterpret_cast<long long*>(red)[1] = clock64();  // first tile landed
           const uint32_t w_addr = ptx::smem_u32(smem_w + (size_t)s * kWBytes);
           const uint32_t x_addr = ptx::smem_u32(smem_x + (size_t)s * kXBytes);
 #pragma unroll
           for (int k = 0; k < kSwapBK / 16; ++k)
-            ptx::umma_f16(tmem_base, ptx::umma_desc_sw128(w_addr + k * 32), ptx::umma_desc_sw128(x_addr + k * 32),
-                          idesc, (kb | k) != 0 ? 1u : 0u);
+            ptx::umma_f16(acc, ptx::umma_desc_sw128(w_addr + k * 32), ptx::umma_desc_sw128(x_addr + k * 32),
+                          idesc, (kb != first || k != 0) ? 1u : 0u);
           ptx::umma_commit(&empty[s]);
-          if (kb == num_kb - 1) ptx::umma_commit(tmem_full);  // same thread as the MMAs it tracks
+          if (kb + kIssuers >= num_kb) ptx::umma_commit(tmem_full);  // same thread as the MMAs it tracks
+          if (!kLN && trace_cta && kb == num_kb - 1) reinterpret_cast<long long*>(red)[2] = clock64();  // all issued
         }
         __syncwarp();
       }
@@ -241,7 +261,7 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
     if (kLN) { ptx::cluster_wait(); ptx::cluster_arrive(); ptx::cluster_wait(); }
     if (kLN && KSPLIT > 1) ptx::cluster_sync();
   } else {
-    constexpr int kEpi = swap_threads(BNB) - 64;  // epilogue threads
+    constexpr int kEpi = swap_epi_threads(BNB);    // epilogue threads
     constexpr int kCStep = kEpi / 4;               // columns covered by one round of the epilogue warps (32 or 64)
     const int quarter = warp & 3;                  // TMEM lane quarter this warp may read
     const int cbeg = ((warp - 2) >> 2) * 32;       // first column chunk of this warp
@@ -264,13 +284,29 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
       ptx::mbar_wait(tmem_full, 0);
       ptx::tc_fence_after();
     }
+    auto load_acc = [n_acc](uint32_t addr, float (&v)[32]) {  // sum of the issuers' accumulators
+      ptx::tmem_ld32(addr, v);
+#pragma unroll
+      for (int i = 1; i < kIssuers; ++i) {
+        if (i >= n_acc) break;
+        float w[32];
+        ptx::tmem_ld32(addr + (uint32_t)(i * BNB), w);
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] += w[j];
+      }
+    };
     if (tracing) tr[4] = clock64();
+    if (!kLN && tracing) {  // mainloop stamps left in shared memory by the producer and MMA warps
+      tr[8] = reinterpret_cast<long long*>(red)[0];
+      tr[9] = reinterpret_cast<long long*>(red)[1];
+      tr[10] = reinterpret_cast<long long*>(red)[2];
+    }
     if constexpr (!kLN) {
       if (active) {
 #pragma unroll 1
         for (int c0 = cbeg; c0 < BNB; c0 += kCStep) {
           float v[32];
-          ptx::tmem_ld32(taddr + (uint32_t)c0, v);
+          load_acc(taddr + (uint32_t)c0, v);
           epi.chunk(f, b0 + c0, M, v);
         }
       }
@@ -286,7 +322,7 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
 #pragma unroll 1
           for (int c0 = cbeg; c0 < BNB; c0 += kCStep) {
             float v[32];
-            ptx::tmem_ld32(taddr + (uint32_t)c0, v);
+            load_acc(taddr + (uint32_t)c0, v);
 #pragma unroll
             for (int j = 0; j < 32; j += 4)
               ptx::st_cluster_v4(dst0 + (uint32_t)(c0 + j) * 4, make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]));
@@ -300,7 +336,7 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
         for (int ch = 0; ch < kChunks; ++ch) {
           const int c0 = cbeg + ch * kCStep;
           float v[32], a[32], q[32];
-          ptx::tmem_ld32(taddr + (uint32_t)c0, v);
+          load_acc(taddr + (uint32_t)c0, v);
           if constexpr (KSPLIT > 1) {
 #pragma unroll
             for (int p = 0; p < KSPLIT - 1; ++p) {
@@ -349,38 +385,64 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
                            (clu[(2 * 2 + 1) * BNB + c] + clu[(3 * 2 + 1) * BNB + c]);
           const float mean = s1 * (1.f / kD);
           const float var = fmaxf(s2 * (1.f / kD) - mean * mean, 0.f);
-          red[c] = mean;
-          red[BNB + c] = rsqrtf(var + 1e-5f);
+          const float rstd = rsqrtf(var + 1e-5f);
+          reinterpret_cast<float2*>(red)[c] = make_float2(rstd, -mean * rstd);  // normalised = v * rstd - mean * rstd
         }
       }
       ptx::bar_sync(1, kEpi);
       if (tracing) tr[9] = clock64();
+      const bool staged = ln.tma_store != 0;
       if (active && lead) {
-        // every MMA has completed (tmem_full), so the operand ring is free: stage the output tile there
-        float* x_stage = reinterpret_cast<float*>(smem);                        // [BNB][128] fp32
+        // staged: every MMA has completed (tmem_full), so the operand ring is free to hold the output tile
+        float* x_stage = reinterpret_cast<float*>(smem);                             // [BNB][128] fp32
         bf16* xb_stage = reinterpret_cast<bf16*>(smem + (size_t)BNB * kSwapBF * 4);  // [BNB][128] bf16
         const float g = __ldg(ln.gamma + f), be = __ldg(ln.beta + f);
 #pragma unroll 1
         for (int c0 = cbeg; c0 < BNB; c0 += kCStep) {
+          // the row statistics first, as 16 vector loads: read one by one between the stores below they would be
+          // serialised behind them (the compiler must assume the stores alias the statistics)
+          float4 rs[16];
+          const float4* sp = reinterpret_cast<const float4*>(red) + (c0 >> 1);
+#pragma unroll
+          for (int i = 0; i < 16; ++i) rs[i] = sp[i];
           float v[32];
           ptx::tmem_ld32(taddr + (uint32_t)c0, v);
 #pragma unroll
           for (int j = 0; j < 32; ++j) {
-            const float y = (v[j] - red[c0 + j]) * red[BNB + c0 + j] * g + be;
-            x_stage[(c0 + j) * kSwapBF + fl] = y;
-            xb_stage[(c0 + j) * kSwapBF + fl] = __float2bfloat16_rn(y);
+            const float sc = (j & 1) ? rs[j >> 1].z : rs[j >> 1].x, sh = (j & 1) ? rs[j >> 1].w : rs[j >> 1].y;
+            v[j] = fmaf(fmaf(v[j], sc, sh), g, be);
+          }
+          if (staged) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              x_stage[(c0 + j) * kSwapBF + fl] = v[j];
+              xb_stage[(c0 + j) * kSwapBF + fl] = __float2bfloat16_rn(v[j]);
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              const int row = b0 + c0 + j;
+              if (row < M) {
+                ln.x[(size_t)row * kD + f] = v[j];
+                ln.xb[(size_t)row * kD + f] = __float2bfloat16_rn(v[j]);
+              }
+            }
           }
         }
-        ptx::fence_proxy_async();
+        if (staged) ptx::fence_proxy_async();
       }
       if (tracing) tr[10] = clock64();
-      ptx::bar_sync(1, kEpi);
-      if (tracing) tr[11] = clock64();
-      if (active && lead && e == 0) {  // rows >= M are clipped by the maps
-        ptx::tma_store_2d(&ln.ts_x, smem, f0, b0);
-        ptx::tma_store_2d(&ln.ts_xb, smem + (size_t)BNB * kSwapBF * 4, f0, b0);
-        ptx::bulk_commit();
-        ptx::bulk_wait_read0();
+      if (staged) {
+        ptx::bar_sync(1, kEpi);
+        if (tracing) tr[11] = clock64();
+        if (active && lead && e == 0) {  // rows >= M are clipped by the maps
+          ptx::tma_store_2d(&ln.ts_x, smem, f0, b0);
+          ptx::tma_store_2d(&ln.ts_xb, smem + (size_t)BNB * kSwapBF * 4, f0, b0);
+          ptx::bulk_commit();
+          ptx::bulk_wait_read0();
+        }
+      } else if (tracing) {
+        tr[11] = tr[10];
       }
     }
   }
@@ -393,7 +455,7 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
   }
   ptx::tc_fence_before();
   __syncthreads();
-  if (warp == 1) ptx::tmem_dealloc(tmem_base, BNB);
+  if (warp == 1) ptx::tmem_dealloc(tmem_base, kIssuers * BNB);
 }
 
 }  // namespace capdec

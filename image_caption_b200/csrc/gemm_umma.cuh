@@ -46,12 +46,17 @@ gemm_umma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
   const int m0 = blockIdx.y * kUmmaBM, n0 = blockIdx.x * BLOCK_N;
   const int num_kb = K / kUmmaBK;
 
-  if (warp == 0 && lane == 0) {
-    ptx::prefetch_tensormap(&tm_a);
-    ptx::prefetch_tensormap(&tm_w);
-    for (int s = 0; s < stages; ++s) { ptx::mbar_init(&full[s], 1); ptx::mbar_init(&empty[s], 1); }
-    ptx::mbar_init(tmem_full, 1);
-    ptx::fence_barrier_init();
+  // TMA / tcgen05 instructions are issued by the converged warp under elect.sync (see gemm_swap.cuh: under
+  // `if (lane == 0)` every instruction is wrapped in a uniformity loop and costs ~150 cycles)
+  if (warp == 0) {
+    if (ptx::elect_one()) {
+      ptx::prefetch_tensormap(&tm_a);
+      ptx::prefetch_tensormap(&tm_w);
+      for (int s = 0; s < stages; ++s) { ptx::mbar_init(&full[s], 1); ptx::mbar_init(&empty[s], 1); }
+      ptx::mbar_init(tmem_full, 1);
+      ptx::fence_barrier_init();
+    }
+    __syncwarp();
   }
   if (warp == 1) ptx::tmem_alloc(tmem_slot, BLOCK_N);
   ptx::tc_fence_before();
@@ -60,24 +65,25 @@ gemm_umma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    if (lane == 0) {
-      for (int kb = 0; kb < num_kb; ++kb) {
-        const int s = kb % stages;
-        const uint32_t ph = (kb / stages) & 1;
-        ptx::mbar_wait(&empty[s], ph ^ 1);
+    for (int kb = 0; kb < num_kb; ++kb) {
+      const int s = kb % stages;
+      const uint32_t ph = (kb / stages) & 1;
+      ptx::mbar_wait(&empty[s], ph ^ 1);
+      if (ptx::elect_one()) {
         ptx::mbar_expect_tx(&full[s], kABytes + kBBytes);
         ptx::tma_load_2d(smem_a + (size_t)s * kABytes, &tm_a, &full[s], kb * kUmmaBK, m0);
         ptx::tma_load_2d(smem_b + (size_t)s * kBBytes, &tm_w, &full[s], kb * kUmmaBK, n0);
       }
+      __syncwarp();
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      constexpr uint32_t idesc = ptx::umma_idesc_bf16(BLOCK_N);
-      for (int kb = 0; kb < num_kb; ++kb) {
-        const int s = kb % stages;
-        const uint32_t ph = (kb / stages) & 1;
-        ptx::mbar_wait(&full[s], ph);
-        ptx::tc_fence_after();
+    constexpr uint32_t idesc = ptx::umma_idesc_bf16(BLOCK_N);
+    for (int kb = 0; kb < num_kb; ++kb) {
+      const int s = kb % stages;
+      const uint32_t ph = (kb / stages) & 1;
+      ptx::mbar_wait(&full[s], ph);
+      ptx::tc_fence_after();
+      if (ptx::elect_one()) {
         const uint32_t a_addr = ptx::smem_u32(smem_a + (size_t)s * kABytes);
         const uint32_t b_addr = ptx::smem_u32(smem_b + (size_t)s * kBBytes);
 #pragma unroll
@@ -86,11 +92,11 @@ gemm_umma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
           ptx::umma_f16(tmem_base, ptx::umma_desc_sw128(a_addr + k * kUmmaK * 2),
                         ptx::umma_desc_sw128(b_addr + k * kUmmaK * 2), idesc, (kb | k) != 0 ? 1u : 0u);
         }
-        ptx::umma_commit(&empty[s]);  // smem slot reusable once these MMAs retire
+        ptx::umma_commit(&empty[s]);                        // smem slot reusable once these MMAs retire
+        if (kb == num_kb - 1) ptx::umma_commit(tmem_full);  // accumulator complete (same thread as its MMAs)
       }
-      ptx::umma_commit(tmem_full);    // accumulator complete
+      __syncwarp();
     }
-    __syncwarp();
   } else {
     // epilogue warps 2..5: TMEM lane quarter = warp % 4
     const int quarter = warp & 3;
