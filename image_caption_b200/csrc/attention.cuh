@@ -182,6 +182,120 @@ self_attn_stream_kernel(const bf16* __restrict__ q, const bf16* __restrict__ kc,
   }
 }
 
+// bf16 engine, v2 step path, one sequence per image (greedy decoding: cfg2, cfg5).  One warp per (image, head), the
+// same lane layout and online softmax as self_attn_stream_kernel, over the projected memory
+// ckv = [L][2][n_images][H][S][64].  The memory was projected at prefill, so the first chunk's K and V rows are
+// requested (and the second chunk's lines pulled into L2) BEFORE the programmatic-launch wait: only the query
+// depends on the previous kernel of the step.  With one query per (image, head) the tensor-core kernel
+// (cross_attn_tma.cuh) spends its time on CTA scheduling -- 126 registers x 128 threads allow 4 CTAs per SM,
+// so 2048 CTAs run in 3.5 waves -- while here every (image, head) is resident at once.
+__global__ void __launch_bounds__(kAttnWarps * 32)
+cross_attn_stream_kernel(const bf16* __restrict__ q, const bf16* __restrict__ ckv, bf16* __restrict__ out, int layer,
+                         int n_images, int S, const DecState* st) {
+  const int gw = blockIdx.x * kAttnWarps + (threadIdx.x >> 5);  // image * H + head
+  const bool live = gw < n_images * kH;
+  const int lane = threadIdx.x & 31, g = lane >> 3, c = lane & 7;
+  const size_t plane = (size_t)n_images * kH * S * kHD;  // one of K / V of one layer
+  const bf16* kb = ckv + (size_t)(2 * layer) * plane + (size_t)(live ? gw : 0) * S * kHD + c * 8;
+  const bf16* vb = kb + plane;
+  uint4 kr[8], vr[8];
+#pragma unroll
+  for (int it = 0; it < 8; ++it) {
+    const int pos = it * 4 + g;
+    if (live && pos < S) {
+      kr[it] = ld_stream16(kb + (size_t)pos * kHD);
+      vr[it] = ld_stream16(vb + (size_t)pos * kHD);
+    } else {
+      kr[it] = make_uint4(0u, 0u, 0u, 0u);
+      vr[it] = make_uint4(0u, 0u, 0u, 0u);
+    }
+  }
+  if (live && 32 + lane < S) {  // one 128-byte row per lane
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(kb - c * 8 + (size_t)(32 + lane) * kHD));
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(vb - c * 8 + (size_t)(32 + lane) * kHD));
+  }
+  asm volatile("griddepcontrol.wait;" ::: "memory");  // the query projection of this step
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  if (st->done || !live) return;
+  float qv[8];
+  {
+    const uint4 r = *reinterpret_cast<const uint4*>(q + (size_t)gw * kHD + c * 8);  // group == 1: row == image
+    const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { qv[2 * i] = __uint_as_float(w[i] << 16) * 0.125f; qv[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u) * 0.125f; }
+  }
+  float m_run = -INFINITY, l_run = 0.f;
+  float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  for (int p0 = 0; p0 < S; p0 += 32) {
+    if (p0 > 0) {
+#pragma unroll
+      for (int it = 0; it < 8; ++it) {
+        const int pos = p0 + it * 4 + g;
+        if (pos < S) {
+          kr[it] = ld_stream16(kb + (size_t)pos * kHD);
+          vr[it] = ld_stream16(vb + (size_t)pos * kHD);
+        } else {
+          kr[it] = make_uint4(0u, 0u, 0u, 0u);
+          vr[it] = make_uint4(0u, 0u, 0u, 0u);
+        }
+      }
+      if (p0 + 32 + lane < S) {
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(kb - c * 8 + (size_t)(p0 + 32 + lane) * kHD));
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(vb - c * 8 + (size_t)(p0 + 32 + lane) * kHD));
+      }
+    }
+    float s[8];
+    float mc = -INFINITY;
+#pragma unroll
+    for (int it = 0; it < 8; ++it) {
+      const uint32_t w[4] = {kr[it].x, kr[it].y, kr[it].z, kr[it].w};
+      float d = 0.f;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        d = fmaf(qv[2 * i], __uint_as_float(w[i] << 16), d);
+        d = fmaf(qv[2 * i + 1], __uint_as_float(w[i] & 0xffff0000u), d);
+      }
+      d += __shfl_xor_sync(0xffffffffu, d, 1);
+      d += __shfl_xor_sync(0xffffffffu, d, 2);
+      d += __shfl_xor_sync(0xffffffffu, d, 4);
+      s[it] = (p0 + it * 4 + g < S) ? d : -INFINITY;
+      mc = fmaxf(mc, s[it]);
+    }
+    mc = fmaxf(mc, __shfl_xor_sync(0xffffffffu, mc, 8));
+    mc = fmaxf(mc, __shfl_xor_sync(0xffffffffu, mc, 16));
+    const float m_new = fmaxf(m_run, mc);      // finite: position p0 < S is in this chunk
+    const float corr = __expf(m_run - m_new);  // exp(-inf) = 0 on the first chunk
+    l_run *= corr;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i] *= corr;
+#pragma unroll
+    for (int it = 0; it < 8; ++it) {
+      const float pr = __expf(s[it] - m_new);  // 0 for masked positions
+      l_run += pr;
+      const uint32_t w[4] = {vr[it].x, vr[it].y, vr[it].z, vr[it].w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        acc[2 * i] = fmaf(pr, __uint_as_float(w[i] << 16), acc[2 * i]);
+        acc[2 * i + 1] = fmaf(pr, __uint_as_float(w[i] & 0xffff0000u), acc[2 * i + 1]);
+      }
+    }
+    m_run = m_new;
+  }
+  l_run += __shfl_xor_sync(0xffffffffu, l_run, 8);
+  l_run += __shfl_xor_sync(0xffffffffu, l_run, 16);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    acc[i] += __shfl_xor_sync(0xffffffffu, acc[i], 8);
+    acc[i] += __shfl_xor_sync(0xffffffffu, acc[i], 16);
+  }
+  if (g == 0) {
+    const float inv = 1.f / l_run;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i] *= inv;
+    store8(out + (size_t)gw * kHD + c * 8, acc);
+  }
+}
+
 // q, out: [n_images*group, 512] image-major; ck/cv: this layer's [n_images][H][S][64].
 // Work item = (image, head, query tile of GT sequences); group % GT == 0.
 template <typename Elem, int GT>

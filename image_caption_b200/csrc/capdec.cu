@@ -520,6 +520,7 @@ extern "C" int capdec_create(const capdec_config* cfg, int device, capdec_handle
     }
   }
   if (const char* e = getenv("CAPDEC_LN_TMA_STORE")) h->force_ln_tma_store = atoi(e) != 0 ? 1 : 0;
+  if (const char* e = getenv("CAPDEC_NO_CROSS_STREAM")) h->no_cross_stream = atoi(e) != 0;
   if (const char* e = getenv("CAPDEC_BNB")) h->force_bnb = atoi(e);
   if (const char* e = getenv("CAPDEC_STAGES")) h->force_stages = atoi(e);
   if (const char* e = getenv("CAPDEC_KSPLIT")) h->force_ksplit = atoi(e);
@@ -822,7 +823,12 @@ static int enqueue_step_fast(capdec_handle h, cudaStream_t s, int n_images, int 
         const int KT = ca_key_rows(S) / 16;
         const int per_warp = (KT + 3) / 4;
         ProfScope ps(h, s);
-        if (per_warp <= 1)
+        // one query per (image, head) and a short memory: streaming warps, all resident at once (B200: cfg2 335 -> 321
+        // us/step, cfg5 592 -> 532; at S = 196 the tensor-core kernel is level, 561 vs 565)
+        if (group == 1 && S <= 128 && !h->no_cross_stream)
+          e = launch_ex(cross_attn_stream_kernel, dim3((n_images * kH + kAttnWarps - 1) / kAttnWarps), dim3(kAttnWarps * 32), 0,
+                        s, 1, h->use_pdl, (const bf16*)h->q, (const bf16*)h->cross_kv, (bf16*)h->a, l, n_images, S, st);
+        else if (per_warp <= 1)
           e = launch_ex(cross_attn_tma_kernel<1>, dim3(n_images * kH), dim3(kCaThreads), ca_smem_bytes(S, group), s, 1, h->use_pdl,
                         h->tm_ckv, (const bf16*)h->q, (bf16*)h->a, l, n_images, group, S, st);
         else if (per_warp <= 2)

@@ -76,6 +76,7 @@ struct capdec_engine {
   CUtensorMap ts_x, ts_xb;         // store views of the residual stream (fp32 / bf16), box = 128 x bnb
   int ln_tma_store = 1;            // LayerNorm epilogue leaves through bulk tensor stores
   int force_ln_tma_store = -1;     // env CAPDEC_LN_TMA_STORE
+  bool no_cross_stream = false;    // env CAPDEC_NO_CROSS_STREAM: keep the tensor-core cross-attention for group == 1
   CUtensorMap tm_ckv;              // whole cross cache as [rows,64], box = 64 x ca_key_rows(S)
   float* fc_wT = nullptr;          // [512][kVPad] fp32: fc_out.weight transposed + padded
   float* part = nullptr;           // [4][min(M_max,512)][512] fp32 split-K partial products (small batches)
