@@ -116,12 +116,31 @@ static int make_store_map(capdec_handle h, CUtensorMap* m, const void* ptr, int 
   return 0;
 }
 
+// bf16 [rows, cols] row-major matrix seen as [64, rows, cols/64]: one copy brings box_kb k-blocks of box_rows rows,
+// laid out in shared memory as box_kb consecutive 128B-swizzled tiles (exactly the per-stage tiles of make_map).
+// The TMA unit keeps about two bulk copies in flight per SM and each takes an L2 round trip (~650 cycles), so its
+// throughput is ~2 x copy size / 650 cycles: few large copies instead of one small box per k-block.
+static int make_map3(capdec_handle h, CUtensorMap* m, const void* ptr, int rows, int cols, int box_rows, int box_kb) {
+  EncodeTiledFn fn = encode_tiled_fn();
+  if (!fn) return fail(h, CAPDEC_ERR_CUDA, "cuTensorMapEncodeTiled entry point unavailable");
+  cuuint64_t dims[3] = {(cuuint64_t)kUmmaBK, (cuuint64_t)rows, (cuuint64_t)(cols / kUmmaBK)};
+  cuuint64_t strides[2] = {(cuuint64_t)cols * 2, (cuuint64_t)kUmmaBK * 2};
+  cuuint32_t box[3] = {(cuuint32_t)kUmmaBK, (cuuint32_t)box_rows, (cuuint32_t)box_kb};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(ptr), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(h, CAPDEC_ERR_CUDA, "cuTensorMapEncodeTiled (3-D view) failed (%d) rows=%d cols=%d", (int)r, rows, cols);
+  return 0;
+}
+
 static int make_weight_maps(capdec_handle h, WeightMaps* wm, const void* ptr, int n, int k) {
   const int bns[3] = {32, 64, 128};
   for (int i = 0; i < 3; ++i) {
     int rc = make_map(h, &wm->bn[i], ptr, n, k, bns[i]);
     if (rc) return rc;
   }
+  if (n % kSwapBF == 0 && (k / kUmmaBK) % kSwapWholeKB == 0) return make_map3(h, &wm->w3, ptr, n, k, kSwapBF, kSwapWholeKB / 2);
   return 0;
 }
 
@@ -236,8 +255,14 @@ static int swap_stages(capdec_handle h, int bnb, int K, int ctas) {
   return stages;
 }
 
+// All of a CTA's K range in three copies (two weight halves + the activations) when it is exactly 8 k-blocks and the
+// ring holds them all (env CAPDEC_NO_WHOLE_K=1 keeps one copy per k-block and operand).
+static int swap_whole_k(capdec_handle h, int bnb, int num_kb, int stages) {
+  return (!h->no_whole_k && num_kb == kSwapWholeKB && stages >= kSwapWholeKB && bnb <= 64) ? 1 : 0;
+}
+
 template <int BNB, bool kLN, typename Epi, int KSPLIT>
-static int launch_swap_ks(capdec_handle h, cudaStream_t s, const CUtensorMap& tw, const CUtensorMap& tx, int M, int n_out,
+static int launch_swap_ks(capdec_handle h, cudaStream_t s, const WeightMaps& tw, const ActMaps& tx, int M, int n_out,
                           int K, const Epi& epi, const SwapLNParams& ln, const DecState* st) {
   dim3 grid(n_out / kSwapBF * KSPLIT, (M + BNB - 1) / BNB);
   int stages = swap_stages(h, BNB, K / KSPLIT, grid.x * grid.y);
@@ -245,7 +270,8 @@ static int launch_swap_ks(capdec_handle h, cudaStream_t s, const CUtensorMap& tw
   while (kLN && stages * swap_stage_bytes(BNB) < swap_ln_stage_out_bytes(BNB)) ++stages;  // the output tile is staged in the ring
   ProfScope ps(h, s);
   cudaError_t e = launch_ex(gemm_swap_kernel<BNB, kLN, Epi, KSPLIT>, grid, dim3(swap_threads(BNB, kLN)), swap_smem_bytes(BNB, stages, KSPLIT), s,
-                            kLN ? 4 * KSPLIT : 1, h->use_pdl, tw, tx, M, K, stages, epi, ln, st);
+                            kLN ? 4 * KSPLIT : 1, h->use_pdl, tw.bn[2], tx.tile, tw.w3, tx.whole,
+                            swap_whole_k(h, BNB, K / kSwapBK / KSPLIT, stages), M, K, stages, epi, ln, st);
   if (e != cudaSuccess) return fail(h, CAPDEC_ERR_CUDA, "gemm_swap launch failed: %s (BNB=%d n_out=%d K=%d stages=%d ksplit=%d)",
                                     cudaGetErrorString(e), BNB, n_out, K, stages, KSPLIT);
   h->launches_this_enqueue++;
@@ -266,7 +292,7 @@ static int ln_ksplit(capdec_handle h, int K, int row_tiles) {
 }
 
 template <int BNB, bool kLN, typename Epi>
-static int launch_swap_bnb(capdec_handle h, cudaStream_t s, const CUtensorMap& tw, const CUtensorMap& tx, int M, int n_out,
+static int launch_swap_bnb(capdec_handle h, cudaStream_t s, const WeightMaps& tw, const ActMaps& tx, int M, int n_out,
                            int K, const Epi& epi, const SwapLNParams& ln, const DecState* st, int zsplit = 1) {
   if constexpr (kLN) {
     const int ks = ln_ksplit(h, K, (M + BNB - 1) / BNB);
@@ -278,7 +304,8 @@ static int launch_swap_bnb(capdec_handle h, cudaStream_t s, const CUtensorMap& t
   while (kLN && stages * swap_stage_bytes(BNB) < swap_ln_stage_out_bytes(BNB)) ++stages;  // the output tile is staged in the ring
   ProfScope ps(h, s);
   cudaError_t e = launch_ex(gemm_swap_kernel<BNB, kLN, Epi>, grid, dim3(swap_threads(BNB, kLN)), swap_smem_bytes(BNB, stages), s,
-                            kLN ? 4 : 1, h->use_pdl, tw, tx, M, K, stages, epi, ln, st);
+                            kLN ? 4 : 1, h->use_pdl, tw.bn[2], tx.tile, tw.w3, tx.whole,
+                            swap_whole_k(h, BNB, K / kSwapBK / zsplit, stages), M, K, stages, epi, ln, st);
   if (e != cudaSuccess) return fail(h, CAPDEC_ERR_CUDA, "gemm_swap launch failed: %s (BNB=%d n_out=%d K=%d stages=%d)",
                                     cudaGetErrorString(e), BNB, n_out, K, stages);
   h->launches_this_enqueue++;
@@ -286,7 +313,7 @@ static int launch_swap_bnb(capdec_handle h, cudaStream_t s, const CUtensorMap& t
 }
 
 template <bool kLN, typename Epi>
-static int launch_swap(capdec_handle h, cudaStream_t s, const CUtensorMap& tw, const CUtensorMap& tx, int M, int n_out, int K,
+static int launch_swap(capdec_handle h, cudaStream_t s, const WeightMaps& tw, const ActMaps& tx, int M, int n_out, int K,
                        const Epi& epi, const SwapLNParams& ln, const DecState* st, int zsplit = 1) {
   if (K % kSwapBK != 0 || n_out % kSwapBF != 0 || (kLN && n_out != kD))
     return fail(h, CAPDEC_ERR_INVALID, "swap GEMM shape (n_out=%d K=%d ln=%d)", n_out, K, (int)kLN);
@@ -521,6 +548,7 @@ extern "C" int capdec_create(const capdec_config* cfg, int device, capdec_handle
   }
   if (const char* e = getenv("CAPDEC_LN_TMA_STORE")) h->force_ln_tma_store = atoi(e) != 0 ? 1 : 0;
   if (const char* e = getenv("CAPDEC_NO_CROSS_STREAM")) h->no_cross_stream = atoi(e) != 0;
+  if (const char* e = getenv("CAPDEC_NO_WHOLE_K")) h->no_whole_k = atoi(e) != 0;
   if (const char* e = getenv("CAPDEC_BNB")) h->force_bnb = atoi(e);
   if (const char* e = getenv("CAPDEC_STAGES")) h->force_stages = atoi(e);
   if (const char* e = getenv("CAPDEC_KSPLIT")) h->force_ksplit = atoi(e);
@@ -800,7 +828,7 @@ static int enqueue_step_fast(capdec_handle h, cudaStream_t s, int n_images, int 
     {  // self-attention block
       SwapQKV<bf16> eq{(bf16*)h->q, kc, vc, lp.b_qkv, st, h->t_pad};
       set_tag(h, "gemm_qkv", gemm_bytes(M, 3 * kD, kD, 2, 2, 2));
-      TRY((launch_swap<false>(h, s, lp.m_qkv.bn[2], h->tx_xb, M, 3 * kD, kD, eq, no_ln, st)));
+      TRY((launch_swap<false>(h, s, lp.m_qkv, h->tx_xb, M, 3 * kD, kD, eq, no_ln, st)));
       set_tag(h, "self_attn", (double)M * kD * 2 * 2 + (double)M * 2 * kD * 2 * h->prof_step_n);
       {
         const int blocks = (M * kH + kAttnWarps - 1) / kAttnWarps;
@@ -812,12 +840,12 @@ static int enqueue_step_fast(capdec_handle h, cudaStream_t s, int n_images, int 
       h->launches_this_enqueue++;
       SwapLNParams ln{h->x, (bf16*)h->xb, lp.b_so, lp.ln_w[0], lp.ln_b[0], h->ts_x, h->ts_xb, h->ln_tma_store};
       set_tag(h, "gemm_self_out_ln", gemm_bytes(M, kD, kD, 2, 2, 0) + ln_extra);
-      TRY((launch_swap<true>(h, s, lp.m_so.bn[2], h->tx_a, M, kD, kD, SwapNoLN{}, ln, st)));
+      TRY((launch_swap<true>(h, s, lp.m_so, h->tx_a, M, kD, kD, SwapNoLN{}, ln, st)));
     }
     {  // cross-attention block
       SwapLinear<bf16, false> eq{(bf16*)h->q, lp.b_cq, kD};
       set_tag(h, "gemm_cross_q", gemm_bytes(M, kD, kD, 2, 2, 2));
-      TRY((launch_swap<false>(h, s, lp.m_cq.bn[2], h->tx_xb, M, kD, kD, eq, no_ln, st)));
+      TRY((launch_swap<false>(h, s, lp.m_cq, h->tx_xb, M, kD, kD, eq, no_ln, st)));
       set_tag(h, "cross_attn", (double)n_images * S * 2 * kD * 2 + (double)M * kD * 2 * 2);
       {
         const int KT = ca_key_rows(S) / 16;
@@ -842,18 +870,18 @@ static int enqueue_step_fast(capdec_handle h, cudaStream_t s, int n_images, int 
       h->launches_this_enqueue++;
       SwapLNParams ln{h->x, (bf16*)h->xb, lp.b_co, lp.ln_w[1], lp.ln_b[1], h->ts_x, h->ts_xb, h->ln_tma_store};
       set_tag(h, "gemm_cross_out_ln", gemm_bytes(M, kD, kD, 2, 2, 0) + ln_extra);
-      TRY((launch_swap<true>(h, s, lp.m_co.bn[2], h->tx_a, M, kD, kD, SwapNoLN{}, ln, st)));
+      TRY((launch_swap<true>(h, s, lp.m_co, h->tx_a, M, kD, kD, SwapNoLN{}, ln, st)));
     }
     {  // feed-forward block
       SwapLinear<bf16, true> e1{(bf16*)h->hbuf, lp.b_1, F};
       set_tag(h, "gemm_ffn1", gemm_bytes(M, F, kD, 2, 2, 2));
-      TRY((launch_swap<false>(h, s, lp.m_1.bn[2], h->tx_xb, M, F, kD, e1, no_ln, st)));
+      TRY((launch_swap<false>(h, s, lp.m_1, h->tx_xb, M, F, kD, e1, no_ln, st)));
       const int row_tiles = (M + h->bnb - 1) / h->bnb;
       if (M <= h->part_rows && 16 * row_tiles <= 148 && F % (4 * kSwapBK) == 0 && !h->no_ffn2_split) {
         // small batch: K = d_ff divided over 4 CTAs per tile (fp32 partial products), closed by sum_ln
         SwapLinear<float, false> ep{h->part, nullptr, kD, (long long)M * kD};
         set_tag(h, "gemm_ffn2_part", gemm_bytes(M, kD, F, 2, 2, 0) + 4.0 * M * kD * 4);
-        TRY((launch_swap<false>(h, s, lp.m_2.bn[2], h->tx_h, M, kD, F, ep, no_ln, st, 4)));
+        TRY((launch_swap<false>(h, s, lp.m_2, h->tx_h, M, kD, F, ep, no_ln, st, 4)));
         set_tag(h, "sum_ln", (double)M * kD * (4 * 4 + 4 + 4 + 2));
         ProfScope ps(h, s);
         e = launch_ex(sum_ln_kernel, dim3((M + 3) / 4), dim3(128), 0, s, 1, h->use_pdl, h->x, (const float*)h->part, 4,
@@ -863,7 +891,7 @@ static int enqueue_step_fast(capdec_handle h, cudaStream_t s, int n_images, int 
       } else {
         SwapLNParams ln{h->x, (bf16*)h->xb, lp.b_2, lp.ln_w[2], lp.ln_b[2], h->ts_x, h->ts_xb, h->ln_tma_store};
         set_tag(h, "gemm_ffn2_ln", gemm_bytes(M, kD, F, 2, 2, 0) + ln_extra);
-        TRY((launch_swap<true>(h, s, lp.m_2.bn[2], h->tx_h, M, kD, F, SwapNoLN{}, ln, st)));
+        TRY((launch_swap<true>(h, s, lp.m_2, h->tx_h, M, kD, F, SwapNoLN{}, ln, st)));
       }
     }
   }
@@ -899,9 +927,12 @@ static int ensure_activation_maps(capdec_handle h, int M) {
     // sequences per GEMM CTA: small enough that (n_out/128) x (M/bnb) CTAs cover the SMs
     h->bnb = h->force_bnb ? h->force_bnb : (M <= 768 ? 32 : (M <= 2048 ? 64 : 128));
     if (h->bnb != 32 && h->bnb != 64 && h->bnb != 128) return fail(h, CAPDEC_ERR_INVALID, "CAPDEC_BNB must be 32, 64 or 128");
-    TRY(make_map(h, &h->tx_xb, h->xb, M, kD, h->bnb));
-    TRY(make_map(h, &h->tx_a, h->a, M, kD, h->bnb));
-    TRY(make_map(h, &h->tx_h, h->hbuf, M, h->cfg.d_ff, h->bnb));
+    TRY(make_map(h, &h->tx_xb.tile, h->xb, M, kD, h->bnb));
+    TRY(make_map(h, &h->tx_a.tile, h->a, M, kD, h->bnb));
+    TRY(make_map(h, &h->tx_h.tile, h->hbuf, M, h->cfg.d_ff, h->bnb));
+    TRY(make_map3(h, &h->tx_xb.whole, h->xb, M, kD, h->bnb, kSwapWholeKB));
+    TRY(make_map3(h, &h->tx_a.whole, h->a, M, kD, h->bnb, kSwapWholeKB));
+    TRY(make_map3(h, &h->tx_h.whole, h->hbuf, M, h->cfg.d_ff, h->bnb, kSwapWholeKB));
     // measured (B200): staging + bulk stores win for 32-row tiles (cfg2 372.6 -> 368.6 us/step), per-thread stores
     // for wider ones (cfg3 974 -> 958, cfg5 627 -> 620): the 96 KB tile takes ~3.3k cycles to drain
     h->ln_tma_store = h->force_ln_tma_store >= 0 ? h->force_ln_tma_store : (h->bnb == 32 ? 1 : 0);

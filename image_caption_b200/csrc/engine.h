@@ -15,6 +15,12 @@ namespace capdec {
 // W operand tensor maps for the three N-tile widths the tcgen05 GEMM is instantiated for.
 struct WeightMaps {
   CUtensorMap bn[3];  // 32, 64, 128
+  CUtensorMap w3;     // [64, rows, K/64] view, box = 64 x 128 rows x 4 k-blocks: half of a K = 512 weight slice per copy
+};
+// TMA views of one activation matrix for the v2 GEMMs
+struct ActMaps {
+  CUtensorMap tile;   // box = 64 columns x bnb rows (one k-block)
+  CUtensorMap whole;  // [64, rows, K/64] view, box = 64 x bnb rows x 8 k-blocks: all of K = 512 in one copy
 };
 
 struct LayerParams {
@@ -72,10 +78,11 @@ struct capdec_engine {
   int bnb = 32;                    // sequences per GEMM CTA (UMMA N) for the current M
   int force_bnb = 0, force_stages = 0, force_ksplit = 0;
   bool no_ffn2_split = false;  // tuning overrides (env CAPDEC_BNB / CAPDEC_STAGES)
-  CUtensorMap tx_xb, tx_a, tx_h;   // activation maps with box rows = bnb
+  capdec::ActMaps tx_xb, tx_a, tx_h;  // activation maps with box rows = bnb
   CUtensorMap ts_x, ts_xb;         // store views of the residual stream (fp32 / bf16), box = 128 x bnb
   int ln_tma_store = 1;            // LayerNorm epilogue leaves through bulk tensor stores
   int force_ln_tma_store = -1;     // env CAPDEC_LN_TMA_STORE
+  bool no_whole_k = false;         // env CAPDEC_NO_WHOLE_K: one TMA copy per k-block instead of whole-K copies
   bool no_cross_stream = false;    // env CAPDEC_NO_CROSS_STREAM: keep the tensor-core cross-attention for group == 1
   CUtensorMap tm_ckv;              // whole cross cache as [rows,64], box = 64 x ca_key_rows(S)
   float* fc_wT = nullptr;          // [512][kVPad] fp32: fc_out.weight transposed + padded

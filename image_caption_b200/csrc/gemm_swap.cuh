@@ -34,6 +34,7 @@ __host__ __device__ constexpr int swap_epi_threads(int bnb) { return bnb == 32 ?
 __host__ __device__ constexpr int swap_issuers(int bnb, bool ln) { return bnb == 32 ? CAPDEC_SWAP_ISSUERS32 : (ln ? 2 : 1); }
 __host__ __device__ constexpr int swap_threads(int bnb, bool ln) { return 64 + swap_epi_threads(bnb) + 32 * (swap_issuers(bnb, ln) - 1); }
 
+constexpr int kSwapWholeKB = 8;  // k-blocks of a "whole K" launch: K = 512 per CTA
 __host__ __device__ constexpr int swap_stage_bytes(int bnb) { return (kSwapBF + bnb) * kSwapBK * 2; }
 // pipeline stages + 1 KB alignment slack + barriers/tmem slot (256 B) + LN scratch (16 * bnb floats)
 // + split-K partial tiles received from the cluster peers ((ksplit-1) x 128 x bnb floats)
@@ -142,6 +143,7 @@ __device__ unsigned int g_swap_trace_n = 0;
 template <int BNB, bool kLN, typename Epi, int KSPLIT = 1>
 __global__ void __launch_bounds__(swap_threads(BNB, kLN), (kLN && BNB > 32) ? 1 : 2)
 gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CUtensorMap tm_x,
+                 const __grid_constant__ CUtensorMap tm_w3, const __grid_constant__ CUtensorMap tm_x3, int whole_k,
                  int M, int K, int stages, Epi epi, const __grid_constant__ SwapLNParams ln, const DecState* st) {
   static_assert(BNB == 32 || BNB == 64 || BNB == 128, "BNB");
   extern __shared__ uint8_t smem_raw[];
@@ -186,9 +188,23 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
       // the weights do not depend on the previous kernel of the step: request the first ring of weight tiles now,
       // so that only the activation tiles are still to come once the programmatic-launch wait returns
       const uint64_t keep = ptx::policy_evict_last();  // weights are re-read every step: keep them in L2
-      for (int kb = 0; kb < n_pre; ++kb) {
-        ptx::mbar_expect_tx(&full[kb], kWBytes + kXBytes);
-        ptx::tma_load_2d_hint(smem_w + (size_t)kb * kWBytes, &tm_w, &full[kb], (kb0 + kb) * kSwapBK, f0, keep);
+      if (whole_k) {
+        // whole K in three copies: full[0] / full[1] = the two halves of the weight slice, full[2] = the activations.
+        // (The TMA unit keeps ~2 copies in flight, ~650 cycles each whatever their size: one box per k-block and
+        // operand delivered a pair of k-blocks every ~650 cycles and was the longest part of the kernel.)
+        ptx::prefetch_tensormap(&tm_w3);
+        ptx::prefetch_tensormap(&tm_x3);
+#pragma unroll
+        for (int hf = 0; hf < 2; ++hf) {
+          ptx::mbar_expect_tx(&full[hf], (kSwapWholeKB / 2) * kWBytes);
+          ptx::tma_load_3d_hint(smem_w + (size_t)hf * (kSwapWholeKB / 2) * kWBytes, &tm_w3, &full[hf], 0, f0,
+                                kb0 + hf * (kSwapWholeKB / 2), keep);
+        }
+      } else {
+        for (int kb = 0; kb < n_pre; ++kb) {
+          ptx::mbar_expect_tx(&full[kb], kWBytes + kXBytes);
+          ptx::tma_load_2d_hint(smem_w + (size_t)kb * kWBytes, &tm_w, &full[kb], (kb0 + kb) * kSwapBK, f0, keep);
+        }
       }
     }
     __syncwarp();
@@ -202,18 +218,27 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
   if (tracing) tr[2] = clock64();
 
   ptx::pdl_wait();     // outputs of the previous kernel of the step (activations, DecState) are visible
-  ptx::pdl_trigger();  // let the next kernel's prologue overlap this kernel
   if (tracing) tr[3] = clock64();
-  const bool active = !(st != nullptr && st->done);
-
-  if (warp == 0) {
-    if (ptx::elect_one()) {
-      for (int kb = 0; kb < n_pre; ++kb)  // also when the rollout is over: the prologue's barriers must complete
-        ptx::tma_load_2d(smem_x + (size_t)kb * kXBytes, &tm_x, &full[kb], (kb0 + kb) * kSwapBK, b0);
+  if (warp == 0) {       // the activation tiles are on the critical path: request them before anything else
+    if (ptx::elect_one()) {  // (also when the rollout is over: the prologue's barriers must complete)
+      if (whole_k) {
+        ptx::mbar_expect_tx(&full[2], kSwapWholeKB * kXBytes);
+        ptx::tma_load_3d(smem_x, &tm_x3, &full[2], 0, b0, kb0);
+      } else {
+        for (int kb = 0; kb < n_pre; ++kb)
+          ptx::tma_load_2d(smem_x + (size_t)kb * kXBytes, &tm_x, &full[kb], (kb0 + kb) * kSwapBK, b0);
+      }
       if (!kLN && trace_cta) reinterpret_cast<long long*>(red)[0] = clock64();  // activation tiles requested
     }
     __syncwarp();
-    if (active) {
+  }
+  ptx::pdl_trigger();  // let the next kernel's prologue overlap this kernel
+  const bool active = !(st != nullptr && st->done);
+
+  if (warp == 0) {
+    if (whole_k) {
+      if (!active) { ptx::mbar_wait(&full[0], 0); ptx::mbar_wait(&full[1], 0); ptx::mbar_wait(&full[2], 0); }  // no copy may outlive the CTA
+    } else if (active) {
       const uint64_t keep = ptx::policy_evict_last();
       for (int kb = n_pre; kb < num_kb; ++kb) {
         const int s = kb % stages;
@@ -237,20 +262,21 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
       constexpr uint32_t idesc = ptx::umma_idesc_bf16(BNB);
       const int first = warp == 1 ? 0 : warp - kIssuer2 + 1;  // this issuer's k-blocks: first, first + kIssuers, ...
       const uint32_t acc = tmem_base + (uint32_t)(first * BNB);
+      const uint32_t w_lo0 = ptx::umma_desc_lo(ptx::smem_u32(smem_w)), x_lo0 = ptx::umma_desc_lo(ptx::smem_u32(smem_x));
+      if (whole_k) ptx::mbar_wait(&full[2], 0);  // the activations
       for (int kb = first; kb < num_kb; kb += kIssuers) {
-        const int s = kb % stages;
-        const uint32_t ph = (kb / stages) & 1;
-        ptx::mbar_wait(&full[s], ph);
+        const int s = whole_k ? kb : kb % stages;
+        const uint32_t ph = whole_k ? 0u : (uint32_t)((kb / stages) & 1);
+        ptx::mbar_wait(&full[whole_k ? kb / (kSwapWholeKB / 2) : s], ph);
         ptx::tc_fence_after();
         if (ptx::elect_one()) {
           if (!kLN && trace_cta && kb == 0) reinterpret_cast<long long*>(red)[1] = clock64();  // first tile landed
-          const uint32_t w_addr = ptx::smem_u32(smem_w + (size_t)s * kWBytes);
-          const uint32_t x_addr = ptx::smem_u32(smem_x + (size_t)s * kXBytes);
+          const uint32_t w_lo = w_lo0 + (uint32_t)s * (kWBytes >> 4);  // descriptor low words: address >> 4
+          const uint32_t x_lo = x_lo0 + (uint32_t)s * (kXBytes >> 4);
 #pragma unroll
-          for (int k = 0; k < kSwapBK / 16; ++k)
-            ptx::umma_f16(acc, ptx::umma_desc_sw128(w_addr + k * 32), ptx::umma_desc_sw128(x_addr + k * 32),
-                          idesc, (kb != first || k != 0) ? 1u : 0u);
-          ptx::umma_commit(&empty[s]);
+          for (int k = 0; k < kSwapBK / 16; ++k)  // 16 bf16 = 32 bytes along K inside the swizzle atom
+            ptx::umma_f16_lohi(acc, w_lo + k * 2, x_lo + k * 2, idesc, (kb != first || k != 0) ? 1u : 0u);
+          if (!whole_k) ptx::umma_commit(&empty[s]);  // (no ring reuse in a whole-K launch)
           if (kb + kIssuers >= num_kb) ptx::umma_commit(tmem_full);  // same thread as the MMAs it tracks
           if (!kLN && trace_cta && kb == num_kb - 1) reinterpret_cast<long long*>(red)[2] = clock64();  // all issued
         }

@@ -17,7 +17,8 @@ __global__ void __launch_bounds__(160, 2) probe(int m, int n, int iters, int nis
   uint32_t* slot = (uint32_t*)(sm + 64);
   uint8_t* a = sm + 1024;          // 128 rows x 128 B
   uint8_t* b = sm + 1024 + 16384;  // 128 rows x 128 B
-  for (int i = threadIdx.x; i < (16384 + 16384) / 4; i += blockDim.x) ((uint32_t*)a)[i] = 0;
+  for (int i = threadIdx.x; i < (16384 + 16384 + 8 * 20480) / 4; i += blockDim.x)
+    ((uint32_t*)a)[i] = (flags & 32) ? (0x3c003c00u | ((uint32_t)(i * 2654435761u) >> 24) | (((uint32_t)(i * 40503u) & 0x7fu) << 16)) : 0u;  // bf16 pairs near 0.0078
   const int warp = threadIdx.x >> 5;
   if (threadIdx.x == 0) { for (int i = 0; i < 4; ++i) ptx::mbar_init(&done[i], 1); ptx::fence_barrier_init(); }
   if (warp == alloc_warp) ptx::tmem_alloc(slot, ncols);
@@ -32,8 +33,9 @@ __global__ void __launch_bounds__(160, 2) probe(int m, int n, int iters, int nis
       if (flags & 2) ptx::tc_fence_after();
       if (ptx::elect_one()) {
 #pragma unroll
+        const uint32_t off = (flags & 16) ? (uint32_t)(((i >> 2) & 7) * 20480) : 0u;
         for (int k = 0; k < 4; ++k)
-          ptx::umma_f16(tm + (uint32_t)(w * n), ptx::umma_desc_sw128(aa + k * 32), ptx::umma_desc_sw128(bb + k * 32), id, (uint32_t)((i | k) != 0));
+          ptx::umma_f16(tm + (uint32_t)(w * n), ptx::umma_desc_sw128(aa + off + k * 32), ptx::umma_desc_sw128(bb + off + k * 32), id, (uint32_t)((i | k) != 0));
         if (flags & 1) ptx::umma_commit(&done[3]);
       }
       __syncwarp();
@@ -66,7 +68,7 @@ __global__ void __launch_bounds__(160, 2) probe(int m, int n, int iters, int nis
 
 int main() {
   long long* d; cudaMalloc(&d, 8 * 4 * 296);
-  size_t smem = 2048 + 32768;
+  size_t smem = 2048 + 32768 + 8 * 20480;
   cudaFuncSetAttribute(probe, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   int occ = 0;
   cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, probe, 160, smem);
@@ -74,9 +76,8 @@ int main() {
   const int iters = 2048;
   static long long h[4 * 296];
   struct V { int n, nissue, grid, alloc_warp, ncols, nacc, flags; };
-  const V vs[] = {{32, 1, 1, 1, 32, 0, 0}, {32, 1, 1, 1, 32, 0, 3}, {32, 1, 1, 1, 32, 0, 8}, {32, 1, 1, 1, 32, 0, 11}, {32, 1, 1, 1, 32, 0, 15},
-                  {64, 1, 1, 1, 64, 0, 11}, {128, 1, 1, 1, 128, 0, 8}, {128, 1, 1, 1, 128, 0, 11}, {128, 1, 1, 1, 128, 0, 15},
-                  {32, 2, 1, 0, 256, 0, 11}, {32, 2, 148, 0, 64, 0, 11}, {32, 2, 296, 0, 64, 0, 11}};
+  const V vs[] = {{32, 1, 1, 1, 32, 0, 27}, {32, 1, 1, 1, 32, 0, 59}, {32, 2, 1, 0, 64, 0, 27}, {32, 2, 1, 0, 64, 0, 59}, {32, 4, 1, 0, 128, 0, 59},
+                  {128, 1, 1, 1, 128, 0, 59}, {128, 2, 1, 0, 256, 0, 59}};
   for (const V& v : vs) {
     for (int rep = 0; rep < 2; ++rep) { cudaMemset(d, 0, sizeof h); probe<<<v.grid, 32 * (1 + v.nissue), smem>>>(128, v.n, iters, v.nissue, d, v.alloc_warp, v.ncols, v.nacc, v.flags); cudaMemcpy(h, d, sizeof h, cudaMemcpyDeviceToHost); }
     cudaError_t e = cudaGetLastError();
