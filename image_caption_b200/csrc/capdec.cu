@@ -549,6 +549,7 @@ extern "C" int capdec_create(const capdec_config* cfg, int device, capdec_handle
   if (const char* e = getenv("CAPDEC_LN_TMA_STORE")) h->force_ln_tma_store = atoi(e) != 0 ? 1 : 0;
   if (const char* e = getenv("CAPDEC_NO_CROSS_STREAM")) h->no_cross_stream = atoi(e) != 0;
   if (const char* e = getenv("CAPDEC_NO_WHOLE_K")) h->no_whole_k = atoi(e) != 0;
+  if (const char* e = getenv("CAPDEC_GRAPH_STEPS")) h->graph_steps = std::max(1, atoi(e));
   if (const char* e = getenv("CAPDEC_BNB")) h->force_bnb = atoi(e);
   if (const char* e = getenv("CAPDEC_STAGES")) h->force_stages = atoi(e);
   if (const char* e = getenv("CAPDEC_KSPLIT")) h->force_ksplit = atoi(e);
@@ -944,8 +945,10 @@ static int ensure_activation_maps(capdec_handle h, int M) {
 }
 
 // Capture one step into a graph (on a private stream: the caller's may be the legacy stream).
-static int get_step_graph(capdec_handle h, int n_images, int S, int group, StepGraph** out) {
-  auto key = std::make_tuple(n_images, S, group);
+// `nsteps` consecutive steps in one graph: the kernels read the step index from DecState, so a step's launches are
+// the same at every position, and the programmatic-launch edges continue across the step boundary.
+static int get_step_graph(capdec_handle h, int n_images, int S, int group, int nsteps, StepGraph** out) {
+  auto key = std::make_tuple(n_images, S, group, nsteps);
   auto it = h->graphs.find(key);
   if (it != h->graphs.end()) { *out = &it->second; return 0; }
   cudaStream_t cs;
@@ -954,7 +957,12 @@ static int get_step_graph(capdec_handle h, int n_images, int S, int group, StepG
   cudaError_t e = cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal);
   int rc = 0;
   if (e == cudaSuccess) {
-    rc = enqueue_step(h, cs, n_images, S, group);
+    int kernels = 0;
+    for (int i = 0; i < nsteps && rc == 0; ++i) {
+      rc = enqueue_step(h, cs, n_images, S, group);
+      kernels += h->launches_this_enqueue;
+    }
+    h->launches_this_enqueue = kernels;
     e = cudaStreamEndCapture(cs, &g.graph);
   }
   if (rc == 0 && e == cudaSuccess) e = cudaGraphInstantiate(&g.exec, g.graph, 0);
@@ -1077,9 +1085,17 @@ extern "C" int capdec_decode(capdec_handle h, const capdec_decode_args* a, void*
     TRY(enqueue_cluster_rollout(h, s, n_images, S, group, T));
   } else if (h->use_graph && !h->profiling) {
     StepGraph* g = nullptr;
-    TRY(get_step_graph(h, n_images, S, group, &g));
-    for (int t = 0; t < T; ++t) CUDA_TRY(h, cudaGraphLaunch(g->exec, s));
-    h->launches += (long long)g->kernels * T;
+    const int per = std::max(1, std::min(h->graph_steps, T));
+    if (T / per > 0) {
+      TRY(get_step_graph(h, n_images, S, group, per, &g));
+      for (int t = 0; t + per <= T; t += per) CUDA_TRY(h, cudaGraphLaunch(g->exec, s));
+      h->launches += (long long)g->kernels * (T / per);
+    }
+    if (T % per) {
+      TRY(get_step_graph(h, n_images, S, group, T % per, &g));
+      CUDA_TRY(h, cudaGraphLaunch(g->exec, s));
+      h->launches += g->kernels;
+    }
   } else {
     for (int t = 0; t < T; ++t) {
       h->prof_step_n = t + 1;
