@@ -244,7 +244,7 @@ def run_b200_arm(args) -> None:
                    "n_sample": ns, "max_len": max_len, "sequences_per_gpu": M, "decode_steps": T,
                    "l2": "flushed between timed steps (512 MiB memset outside the event pairs)",
                    "weights": "random init, torch.manual_seed(0)", "collective": "all-gather ids+logp" if world > 1 else "none",
-                   "engine": "v2 step kernels, one CUDA graph per decode step, programmatic dependent launch"},
+                   "engine": "v2 step kernels, 7 decode steps per CUDA graph, programmatic dependent launch"},
         "decode_step_us": 1e3 * ms_per_step / T, "e2e": e2e, "gpu_launches": int(launches), "clocks": clk,
     }
 

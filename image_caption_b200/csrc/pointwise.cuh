@@ -240,9 +240,10 @@ head_kernel(DecState* st, const CallParams* cp, const float* __restrict__ logits
 // Fused vocabulary projection + pick + next-step embedding (SURVEY K11+K12+K13+K2): logits never
 // round-trip to HBM and the step needs no separate embedding kernel.
 // wT: fc_out.weight transposed and padded, [512][kVPad] fp32; x: [M,512] fp32 residual stream.
-// CTA = 8 warps x 2 rows; the 256 KB of wT stream through shared memory in 64-row slabs, three in
-// flight (cp.async); lane l accumulates vocabulary entries 4l..4l+3 of its warp's two rows.
-constexpr int kVhSlab = 64, kVhBufs = 3;
+// The 256 KB of wT stream through shared memory in 64-row slabs (cp.async); six of the eight slabs are requested
+// before the dependency wait (the weights do not depend on the step), so that after the wait a warp only waits
+// for its x row.  Lane l accumulates vocabulary entries 4l..4l+3 of its warp's row.
+constexpr int kVhSlab = 64, kVhBufs = 6;
 __host__ __device__ constexpr int vh_smem_bytes(int rows) { return rows * kD * 4 + kVhBufs * kVhSlab * kVPad * 4; }
 
 // R = rows per CTA = warps per CTA (one row per warp: the per-row work, 2048 FMA per lane, is the critical path
@@ -268,10 +269,11 @@ vocab_head_kernel(DecState* st, const CallParams* cp, float* __restrict__ x, con
     }
   };
   // the weights do not depend on the previous kernel: start streaming them before the dependency wait
-  load_slab(0, 0);
-  asm volatile("cp.async.commit_group;" ::: "memory");
-  load_slab(1, 1);
-  asm volatile("cp.async.commit_group;" ::: "memory");
+#pragma unroll
+  for (int b = 0; b < kVhBufs; ++b) {
+    load_slab(b, b);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  }
   asm volatile("griddepcontrol.wait;" ::: "memory");
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   if (st->done) { asm volatile("cp.async.wait_group 0;" ::: "memory"); return; }
@@ -288,10 +290,10 @@ vocab_head_kernel(DecState* st, const CallParams* cp, float* __restrict__ x, con
   float acc[4] = {0.f, 0.f, 0.f, 0.f};
   const float* xr = xs + warp * kD;
   constexpr int kSlabs = kD / kVhSlab;
+  static_assert(kVhBufs == 6, "the wait_group immediate below is kVhBufs - 1");
   for (int sl = 0; sl < kSlabs; ++sl) {
-    if (sl + 2 < kSlabs) load_slab(sl + 2, (sl + 2) % kVhBufs);
-    asm volatile("cp.async.commit_group;" ::: "memory");  // possibly empty: keeps the group count uniform
-    asm volatile("cp.async.wait_group 2;" ::: "memory");
+    // groups committed so far: kVhBufs + sl (one per iteration, possibly empty); slabs 0..sl are needed
+    asm volatile("cp.async.wait_group 5;" ::: "memory");
     __syncthreads();
     const float* wb = ws + (sl % kVhBufs) * kVhSlab * kVPad + lane * 4;
 #pragma unroll 4
@@ -305,7 +307,9 @@ vocab_head_kernel(DecState* st, const CallParams* cp, float* __restrict__ x, con
         acc[2] = fmaf(av[kk], w.z, acc[2]); acc[3] = fmaf(av[kk], w.w, acc[3]);
       }
     }
-    __syncthreads();  // buffer (sl % 3) is refilled by the load issued at the top of iteration sl + 1
+    __syncthreads();  // every warp is done with buffer (sl % kVhBufs): refill it
+    if (sl + kVhBufs < kSlabs) load_slab(sl + kVhBufs, sl % kVhBufs);
+    asm volatile("cp.async.commit_group;" ::: "memory");
   }
   const float4 bv = __ldg(reinterpret_cast<const float4*>(bias) + lane);
   {
