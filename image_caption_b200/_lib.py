@@ -13,11 +13,13 @@ MAX_LAYERS = 12
 PREC_FP32, PREC_BF16 = 0, 1
 FLAG_NO_GRAPH, FLAG_NO_UMMA, FLAG_V1_STEP, FLAG_NO_PDL, FLAG_NO_CLUSTER_ROLLOUT = 1, 2, 4, 8, 16
 DECODE_NO_EARLY_STOP = 1
+BEAM_STOP_GRID = 1
 
 EXPORTS = (
     "capdec_abi_version", "capdec_last_error", "capdec_create", "capdec_destroy", "capdec_set_weights",
     "capdec_prefill", "capdec_decode", "capdec_generate_host", "capdec_sample_logits", "capdec_launch_count",
     "capdec_debug_gemm", "capdec_debug_cross_kv", "capdec_profile_enable", "capdec_profile_report",
+    "capdec_beam_search",
 )
 
 
@@ -55,6 +57,12 @@ class DecodeArgs(C.Structure):
                 ("logits_out", _fp), ("steps_out", C.POINTER(C.c_int32))]
 
 
+class BeamArgs(C.Structure):
+    _fields_ = [("beam_size", C.c_int32), ("flags", C.c_int32), ("start_token", C.c_int32), ("end_token", C.c_int32),
+                ("pad_token", C.c_int32), ("max_len", C.c_int32), ("ids_out", _fp), ("len_out", _fp),
+                ("score_out", _fp), ("steps_out", C.POINTER(C.c_int32))]
+
+
 _lib = None
 
 
@@ -83,6 +91,7 @@ def load() -> C.CDLL:
     lib.capdec_generate_host.argtypes = [H, C.c_void_p, C.c_int32, C.c_int32, C.POINTER(DecodeArgs), C.c_void_p]
     lib.capdec_sample_logits.argtypes = [H, C.c_void_p, C.c_int32, C.c_int32, C.c_uint64, C.c_uint64, C.c_int32,
                                          C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.capdec_beam_search.argtypes = [H, C.POINTER(BeamArgs), C.c_void_p]
     lib.capdec_launch_count.restype = C.c_int64
     lib.capdec_launch_count.argtypes = [H]
     lib.capdec_debug_gemm.argtypes = [H, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32,

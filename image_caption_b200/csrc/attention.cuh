@@ -13,10 +13,12 @@ namespace capdec {
 constexpr int kAttnWarps = 4;
 
 // q, out: [M, 512]; kc/vc: this layer's cache [M][H][t_pad][64]; positions 0..st->step valid.
+// anc (beam search, beam.cuh; else null): [2][M][t_pad], buffer (step & 1): the cache row that holds position j of
+// the hypothesis in row m -- re-ranked hypotheses read their ancestors' rows instead of copying them.
 template <typename Elem, int NIT>
 __global__ void __launch_bounds__(kAttnWarps * 32)
 self_attn_kernel(const Elem* __restrict__ q, const Elem* __restrict__ kc, const Elem* __restrict__ vc,
-                 Elem* __restrict__ out, int M, int t_pad, const DecState* st) {
+                 Elem* __restrict__ out, int M, int t_pad, const DecState* st, const int* __restrict__ anc) {
   asm volatile("griddepcontrol.wait;" ::: "memory");  // q and the appended K/V rows (PDL launches)
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   if (st->done) return;
@@ -27,6 +29,11 @@ self_attn_kernel(const Elem* __restrict__ q, const Elem* __restrict__ kc, const 
   const size_t row_base = (size_t)gw * t_pad * kHD;  // gw == m*H + h
   const Elem* kb = kc + row_base + c * 8;
   const Elem* vb = vc + row_base + c * 8;
+  const int* arow = anc != nullptr ? anc + ((size_t)(n & 1) * M + gw / kH) * t_pad : nullptr;
+  // offset of position j's row relative to kb / vb: 0 without ancestry
+  auto row_shift = [&](int j) -> long long {
+    return arow != nullptr ? ((long long)arow[j] - gw / kH) * (long long)kH * t_pad * kHD : 0ll;
+  };
 
   float qv[8];
   load8(q + (size_t)gw * kHD + c * 8, qv);  // (m*512 + h*64) == gw*64
@@ -41,7 +48,7 @@ self_attn_kernel(const Elem* __restrict__ q, const Elem* __restrict__ kc, const 
     if (it * 4 <= n) {  // warp-uniform
       if (j <= n) {
         float kv[8];
-        load8(kb + (size_t)j * kHD, kv);
+        load8(kb + row_shift(j) + (size_t)j * kHD, kv);
 #pragma unroll
         for (int i = 0; i < 8; ++i) d = fmaf(qv[i], kv[i], d);
       }
@@ -66,7 +73,7 @@ self_attn_kernel(const Elem* __restrict__ q, const Elem* __restrict__ kc, const 
       const float p = expf(s[it] - mx);
       sum += p;
       float vv[8];
-      load8(vb + (size_t)j * kHD, vv);
+      load8(vb + row_shift(j) + (size_t)j * kHD, vv);
 #pragma unroll
       for (int i = 0; i < 8; ++i) acc[i] = fmaf(p, vv[i], acc[i]);
     }

@@ -13,6 +13,7 @@
 #include "gemm_simt.cuh"
 #include "gemm_umma.cuh"
 #include "gemm_swap.cuh"
+#include "beam.cuh"
 #include "cross_attn_tma.cuh"
 #include "attention.cuh"
 #include "pointwise.cuh"
@@ -701,9 +702,9 @@ static int launch_self_attn(capdec_handle h, cudaStream_t s, int l, int M) {
   const int blocks = (M * kH + kAttnWarps - 1) / kAttnWarps;
   ProfScope ps(h, s);
   if (h->t_pad == 64)
-    self_attn_kernel<Elem, 16><<<blocks, kAttnWarps * 32, 0, s>>>((const Elem*)h->q, kc, vc, (Elem*)h->a, M, h->t_pad, h->st);
+    self_attn_kernel<Elem, 16><<<blocks, kAttnWarps * 32, 0, s>>>((const Elem*)h->q, kc, vc, (Elem*)h->a, M, h->t_pad, h->st, h->beam_mode ? h->beam.anc : nullptr);
   else
-    self_attn_kernel<Elem, 32><<<blocks, kAttnWarps * 32, 0, s>>>((const Elem*)h->q, kc, vc, (Elem*)h->a, M, h->t_pad, h->st);
+    self_attn_kernel<Elem, 32><<<blocks, kAttnWarps * 32, 0, s>>>((const Elem*)h->q, kc, vc, (Elem*)h->a, M, h->t_pad, h->st, h->beam_mode ? h->beam.anc : nullptr);
   CUDA_TRY(h, cudaGetLastError());
   h->launches_this_enqueue++;
   return 0;
@@ -805,7 +806,11 @@ static int enqueue_step_t(capdec_handle h, cudaStream_t s, int n_images, int S, 
   EpiLinear<float, false> ev{h->logits, h->fc_b, kVPad};
   set_tag(h, "gemm_vocab", gemm_bytes(M, kVPad, kD, 4, 4, 4));
   TRY((launch_simt<float, float, EpiLinear<float, false>>(h, s, h->x, kD, h->fc_w, kD, M, kVPad, kD, ev, st)));
-  {
+  if (h->beam_mode) {
+    set_tag(h, "beam_head", (double)M * (kVPad * 4 + 8 + 4 + 2 * h->t_pad * 4));
+    ProfScope ps(h, s);
+    beam_head_kernel<<<n_images, group * 32, 0, s>>>(h->st, h->cp, h->beam, h->logits, n_images, group, h->cfg.vocab, h->t_pad, h->beam_grid_rule);
+  } else {
     set_tag(h, "head", (double)M * (kVPad * 4 + 8 + 4));
     ProfScope ps(h, s);
     head_kernel<<<(M + 3) / 4, 128, 0, s>>>(h->st, h->cp, h->logits, h->fin, M, h->cfg.vocab);
@@ -915,7 +920,7 @@ static int enqueue_step_fast(capdec_handle h, cudaStream_t s, int n_images, int 
 
 static int enqueue_step(capdec_handle h, cudaStream_t s, int n_images, int S, int group) {
   h->launches_this_enqueue = 0;
-  if (h->fast) return enqueue_step_fast(h, s, n_images, S, group);
+  if (h->fast && !h->beam_mode) return enqueue_step_fast(h, s, n_images, S, group);  // beam search runs the v1 kernels
   return h->bf16 ? enqueue_step_t<bf16>(h, s, n_images, S, group) : enqueue_step_t<float>(h, s, n_images, S, group);
 }
 
@@ -948,7 +953,8 @@ static int ensure_activation_maps(capdec_handle h, int M) {
 // `nsteps` consecutive steps in one graph: the kernels read the step index from DecState, so a step's launches are
 // the same at every position, and the programmatic-launch edges continue across the step boundary.
 static int get_step_graph(capdec_handle h, int n_images, int S, int group, int nsteps, StepGraph** out) {
-  auto key = std::make_tuple(n_images, S, group, nsteps);
+  // beam steps are different kernels (and the stop rule is a launch argument)
+  auto key = std::make_tuple(n_images, S, h->beam_mode ? -(group + 100 * h->beam_grid_rule) : group, nsteps);
   auto it = h->graphs.find(key);
   if (it != h->graphs.end()) { *out = &it->second; return 0; }
   cudaStream_t cs;
@@ -1103,6 +1109,93 @@ extern "C" int capdec_decode(capdec_handle h, const capdec_decode_args* a, void*
       h->launches += h->launches_this_enqueue;
     }
   }
+  if (a->steps_out) {
+    int steps = 0;
+    CUDA_TRY(h, cudaMemcpyAsync(&steps, &h->st->steps_executed, sizeof(int), cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(h, cudaStreamSynchronize(s));
+    *a->steps_out = steps;
+  }
+  return CAPDEC_OK;
+}
+
+// ------------------------------------------------------------------ beam search (beam.cuh)
+static int ensure_beam_buffers(capdec_handle h) {
+  if (h->beam.score) return 0;
+  const size_t Mmax = (size_t)h->cfg.max_images * h->cfg.max_group;
+  TRY(dev_alloc(h, &h->beam.score, Mmax));
+  TRY(dev_alloc(h, &h->beam.comp_score, Mmax));
+  TRY(dev_alloc_bytes(h, (void**)&h->beam.live, Mmax * sizeof(int)));
+  TRY(dev_alloc_bytes(h, (void**)&h->beam.k, (size_t)h->cfg.max_images * sizeof(int)));
+  TRY(dev_alloc_bytes(h, (void**)&h->beam.anc, 2 * Mmax * h->t_pad * sizeof(int)));
+  TRY(dev_alloc_bytes(h, (void**)&h->beam.par, Mmax * h->cfg.max_len * sizeof(int)));
+  TRY(dev_alloc_bytes(h, (void**)&h->beam.comp_slot, Mmax * sizeof(int)));
+  TRY(dev_alloc_bytes(h, (void**)&h->beam.comp_pos, Mmax * sizeof(int)));
+  TRY(dev_alloc_bytes(h, (void**)&h->beam.comp_n, (size_t)h->cfg.max_images * sizeof(int)));
+  TRY(dev_alloc_bytes(h, (void**)&h->beam.images_done, sizeof(int)));
+  TRY(dev_alloc(h, &h->beam_tok, Mmax * h->cfg.max_len));
+  return 0;
+}
+
+extern "C" int capdec_beam_search(capdec_handle h, const capdec_beam_args* a, void* stream) {
+  if (!h || !a) return fail(h, CAPDEC_ERR_INVALID, "null argument");
+  if (!h->prefilled) return fail(h, CAPDEC_ERR_STATE, "capdec_beam_search before capdec_prefill");
+  const int V = h->cfg.vocab;
+  if (a->beam_size < 1 || a->beam_size > kBeamMax || a->beam_size > h->cfg.max_group || a->beam_size > V)
+    return fail(h, CAPDEC_ERR_CAPACITY, "beam_size %d outside 1..min(%d, max_group %d)", a->beam_size, kBeamMax, h->cfg.max_group);
+  if (a->max_len < 2 || a->max_len > h->cfg.max_len) return fail(h, CAPDEC_ERR_CAPACITY, "max_len %d outside 2..%d", a->max_len, h->cfg.max_len);
+  if (a->start_token < 0 || a->start_token >= V || a->end_token < 0 || a->end_token >= V || a->pad_token < 0 || a->pad_token >= V)
+    return fail(h, CAPDEC_ERR_INVALID, "start/end/pad token outside the vocabulary");
+  if (!a->ids_out || !a->len_out) return fail(h, CAPDEC_ERR_INVALID, "ids_out / len_out is null");
+  cudaStream_t s = (cudaStream_t)stream;
+  CUDA_TRY(h, cudaSetDevice(h->device));
+  TRY(ensure_beam_buffers(h));
+  const int n_images = h->n_images, S = h->mem_len, beam = a->beam_size, M = n_images * beam;
+  TRY(ensure_activation_maps(h, M));
+
+  CallParams cp{};
+  cp.ids = h->beam_tok;
+  cp.max_len = a->max_len;
+  cp.group = beam;
+  cp.start_token = a->start_token;
+  cp.end_token = a->end_token;
+  cp.pad_token = a->pad_token;
+  cp.n_greedy_rows = M;
+  CUDA_TRY(h, cudaMemcpyAsync(h->cp, &cp, sizeof cp, cudaMemcpyHostToDevice, s));
+  init_rollout_kernel<<<std::min((M * a->max_len + 255) / 256, 1024), 256, 0, s>>>(h->st, h->cp, h->fin, M, h->counters);
+  beam_init_kernel<<<std::min((2 * M * h->t_pad + 255) / 256, 1024), 256, 0, s>>>(h->beam, h->cp, n_images, beam, h->t_pad);
+  CUDA_TRY(h, cudaGetLastError());
+  h->launches += 2;
+
+  struct ModeGuard {  // the step enqueue / graph cache read the mode from the handle
+    capdec_handle h;
+    ~ModeGuard() { h->beam_mode = false; }
+  } guard{h};
+  h->beam_mode = true;
+  h->beam_grid_rule = (a->flags & CAPDEC_BEAM_STOP_GRID) ? 1 : 0;
+  const int T = a->max_len - 1;
+  if (h->use_graph && !h->profiling) {
+    StepGraph* g = nullptr;
+    const int per = std::max(1, std::min(h->graph_steps, T));
+    if (T / per > 0) {
+      TRY(get_step_graph(h, n_images, S, beam, per, &g));
+      for (int t = 0; t + per <= T; t += per) CUDA_TRY(h, cudaGraphLaunch(g->exec, s));
+      h->launches += (long long)g->kernels * (T / per);
+    }
+    if (T % per) {
+      TRY(get_step_graph(h, n_images, S, beam, T % per, &g));
+      CUDA_TRY(h, cudaGraphLaunch(g->exec, s));
+      h->launches += g->kernels;
+    }
+  } else {
+    for (int t = 0; t < T; ++t) {
+      h->prof_step_n = t + 1;
+      TRY(enqueue_step(h, s, n_images, S, beam));
+      h->launches += h->launches_this_enqueue;
+    }
+  }
+  beam_finalize_kernel<<<(n_images + 3) / 4, 128, 0, s>>>(h->st, h->cp, h->beam, n_images, beam, (long long*)a->ids_out, a->len_out, a->score_out);
+  CUDA_TRY(h, cudaGetLastError());
+  h->launches++;
   if (a->steps_out) {
     int steps = 0;
     CUDA_TRY(h, cudaMemcpyAsync(&steps, &h->st->steps_executed, sizeof(int), cudaMemcpyDeviceToHost, s));

@@ -42,6 +42,20 @@ struct CallParams {
   int no_early_stop;
 };
 
+// Beam-search state (beam.cuh), device resident; pointers are engine-owned buffers sized for the handle's capacity.
+struct BeamState {
+  float* score;      // [M] running score of the hypothesis in each slot
+  int* live;         // [M] 1 = alive
+  int* k;            // [n_images] hypotheses to select at the next step (vit:381 `beam_size`)
+  int* anc;          // [2][M][t_pad] cache row holding position q of the hypothesis in slot m (double-buffered by step parity)
+  int* par;          // [M][max_len] slot at position q-1 that the hypothesis in slot m at position q extended
+  float* comp_score; // [M] completed hypotheses of an image, in completion order
+  int* comp_slot;    // [M]
+  int* comp_pos;     // [M] position of their <end>
+  int* comp_n;       // [n_images]
+  int* images_done;  // [1] images whose beam is empty
+};
+
 // ---------------------------------------------------------------- element helpers
 __device__ __forceinline__ float to_f32(float v) { return v; }
 __device__ __forceinline__ float to_f32(bf16 v) { return __bfloat162float(v); }

@@ -107,6 +107,11 @@ struct capdec_engine {
   bool prefilled = false;
   bool prefilled_once = false;
   std::map<std::tuple<int, int, int, int>, capdec::StepGraph> graphs;  // (n_images, mem_len, group, steps in the graph)
+  // ---- beam search: runs the v1 step kernels with an ancestry table and a per-image head
+  bool beam_mode = false;          // set for the duration of capdec_beam_search
+  int beam_grid_rule = 0;          // stop rule of the Grid model (grid:308) instead of the ViT model's (vit:402)
+  capdec::BeamState beam{};        // buffers allocated on first use
+  long long* beam_tok = nullptr;   // [M_max][max_len] token of each slot at each position
   int graph_steps = 7;  // decode steps captured per graph (env CAPDEC_GRAPH_STEPS); B200 cfg2: 317.3 us/step with 1, 313.4 with 7, 312.6 with 49
   long long launches = 0;
   int launches_this_enqueue = 0;

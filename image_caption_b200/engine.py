@@ -212,24 +212,63 @@ class CaptionDecodeEngine:
             logits = logits[:, :n] if logits is not None else None
         return Rollout(ids=ids, logp=logp, steps=n, logits=logits)
 
+    def beam_search_from_memory(self, memory: torch.Tensor, start_token: int, end_token: int, max_len: int = 50,
+                                beam_size: int = 5, pad_token: int = 0, stop_rule: str = "vit"):
+        """Batched beam search (C ABI ``capdec_beam_search``) over ``memory`` (B, S, 512) CUDA float32.
+        ``stop_rule``: ``"vit"`` = an image stops when every hypothesis of a step ended
+        (models/vit_transformer_model.py:402), ``"grid"`` = when the completed list is at least as long as
+        the beam is wide (models/grid_transformer_model.py:308).  Returns ``(ids, lengths, scores)``:
+        ids (B, max_len) int64 padded with ``pad_token``, lengths (B,) int32, scores (B,) float32."""
+        if memory.dim() != 3 or memory.shape[2] != self.d_model:
+            raise ValueError(f"memory must be (B, S, {self.d_model}), got {tuple(memory.shape)}")
+        if not memory.is_cuda:
+            raise ValueError("beam search needs a CUDA memory tensor")
+        if stop_rule not in ("vit", "grid"):
+            raise ValueError("stop_rule must be 'vit' or 'grid'")
+        if not 1 <= beam_size <= 8:
+            raise ValueError("beam_size must be in 1..8")
+        self._check_lengths(max_len)
+        n_images, mem_len = memory.shape[0], memory.shape[1]
+        self._ensure_capacity(n_images, beam_size, mem_len, max_len)
+        self.sync_weights()
+        memory = memory.detach().to(torch.float32).contiguous()
+        ids = torch.empty((n_images, max_len), dtype=torch.int64, device=self.device)
+        lens = torch.empty((n_images,), dtype=torch.int32, device=self.device)
+        scores = torch.empty((n_images,), dtype=torch.float32, device=self.device)
+        steps = C.c_int32(0)
+        args = _lib.BeamArgs(beam_size=beam_size, flags=_lib.BEAM_STOP_GRID if stop_rule == "grid" else 0,
+                             start_token=start_token, end_token=end_token, pad_token=pad_token, max_len=max_len,
+                             ids_out=ids.data_ptr(), len_out=lens.data_ptr(), score_out=scores.data_ptr(),
+                             steps_out=C.pointer(steps))
+        stream = _stream_ptr(self.device)
+        _lib.check(self._h, self._lib.capdec_prefill(self._h, memory.data_ptr(), n_images, mem_len, stream))
+        _lib.check(self._h, self._lib.capdec_beam_search(self._h, C.byref(args), stream))
+        return ids, lens, scores
+
     # ------------------------------------------------------------------ reference-facing entry points
     @torch.no_grad()
     def generate(self, model: torch.nn.Module, images: torch.Tensor, start_token: int, end_token: int,
                  max_len: int = 50, method: str = "greedy", beam_size: int = 5) -> torch.Tensor:
-        """Drop-in for ``model.generate`` (vit:276-294 / grid:222-228).  Greedy runs on the engine;
-        ``beam_search`` is delegated to the reference's own implementation."""
+        """Drop-in for ``model.generate`` (vit:276-294 / grid:222-228); both methods run on the engine.
+
+        ``beam_search``: the reference decodes one image per call and concatenates the results, which only
+        works when all captions have the same length (``torch.cat`` at vit:341 / grid:263); here the batch is
+        decoded at once and returned as (B, longest) padded with 0 -- identical for one image or equal lengths.
+        The ViT model always uses a beam of 5 (vit:291); the Grid model's extra stop rule (grid:308) is selected
+        by the class name."""
         if method == "greedy":
             model.eval()  # vit:298 - a side effect the reference never undoes
             memory = model.encoder(images)
             return self.decode_from_memory(memory, start_token, end_token, max_len).ids
         if method == "beam_search":
-            ref = getattr(model, "_capdec_reference_generate", None)
-            if ref is None:
-                raise NotImplementedError("beam_search is served by the reference implementation; install() keeps it")
-            try:
-                return ref(images, start_token, end_token, max_len, method="beam_search", beam_size=beam_size)
-            except TypeError:  # ViT signature has no beam_size (vit:276)
-                return ref(images, start_token, end_token, max_len, method="beam_search")
+            model.eval()  # vit:329
+            is_grid = "grid" in type(model).__name__.lower()
+            if not is_grid:
+                beam_size = 5
+            memory = model.encoder(images)
+            ids, lens, _ = self.beam_search_from_memory(memory, start_token, end_token, max_len, beam_size=beam_size,
+                                                        stop_rule="grid" if is_grid else "vit")
+            return ids[:, :int(lens.max().item())]
         raise ValueError(f"Unknown generation method: {method}")
 
     def sample_with_log_probs(self, model: torch.nn.Module, images: torch.Tensor, start_token: int,

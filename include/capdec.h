@@ -147,6 +147,29 @@ int capdec_decode(capdec_handle h, const capdec_decode_args* args, void* cuda_st
 int capdec_generate_host(capdec_handle h, const float* memory_host, int32_t n_images, int32_t mem_len,
                          const capdec_decode_args* args_host, void* cuda_stream);
 
+/* Batched beam search over the images of the last prefill: the third `generate` method of the reference,
+ * `_beam_search` (models/vit_transformer_model.py:327-420, models/grid_transformer_model.py:253-322), which the
+ * reference runs one image at a time and without a KV cache.  Same rules: scores are sums of log-softmax values
+ * (no length normalisation), step 0 expands one hypothesis, the beam shrinks as hypotheses emit <end>, an image
+ * stops when all of a step's hypotheses ended (ViT model, vit:402; the Grid model's rule is CAPDEC_BEAM_STOP_GRID)
+ * or after max_len-1 steps, the result is the first completed
+ * hypothesis with the highest score, else the best live one.  beam_size <= min(8, max_group of the handle).
+ * ids_out DEVICE int64 [n_images, max_len]: row i holds its sequence (with <start>, and <end> if it completed)
+ * followed by pad_token; len_out DEVICE int32 [n_images]; score_out DEVICE fp32 [n_images] or NULL.
+ * steps_out as in capdec_decode. */
+#define CAPDEC_BEAM_STOP_GRID 1 /* Grid model's stop rule (grid:308): stop once len(completed) >= current beam width */
+typedef struct capdec_beam_args {
+  int32_t beam_size;
+  int32_t flags;
+  int32_t start_token, end_token, pad_token;
+  int32_t max_len;
+  int64_t* ids_out;
+  int32_t* len_out;
+  float* score_out;
+  int32_t* steps_out;
+} capdec_beam_args;
+int capdec_beam_search(capdec_handle h, const capdec_beam_args* args, void* cuda_stream);
+
 /* Sampler alone: logits DEVICE fp32 [n_rows, vocab]; row r uses sequence id seq_id_base + r.
  * mode 0 = argmax, 1 = sample.  ids_out DEVICE int64 [n_rows], logp_out DEVICE fp32 [n_rows] or NULL. */
 int capdec_sample_logits(capdec_handle h, const float* logits, int32_t n_rows, int32_t mode, uint64_t seed,

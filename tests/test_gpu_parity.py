@@ -404,3 +404,153 @@ def test_capacity_grows_and_limits_raise(dev):
     with pytest.raises(ValueError):
         eng.decode_from_memory(mem[:, :, :100], START, END)
     eng.close()
+
+
+# ---------------------------------------------------------------- batched beam search
+from conftest import load_golden  # noqa: E402
+from oracle import beam as oracle_beam  # noqa: E402
+
+
+def _beam_decoder(z, end_bias):
+    dec = torch_port.build_decoder(0, VOCAB, 512, 8, int(z["n_layers"]), 2048, int(z["pe_rows"]), perturb=float(z["perturb"]))
+    with torch.no_grad():
+        dec.fc_out.bias[END] += float(end_bias)
+    return dec.eval(), torch_port.synthetic_memory(int(z["n_images"]), int(z["mem_len"]))
+
+
+def _sequence_scores(dec, mem, ids, lens):
+    """Sum of the oracle's log-softmax values along each returned sequence (teacher-forced)."""
+    logp = torch.log_softmax(torch_port.teacher_forced_logits(dec, ids, mem), -1)
+    out = []
+    for i, n in enumerate(lens.tolist()):
+        out.append(float(logp[i, torch.arange(n - 1), ids[i, 1:n]].sum()))
+    return np.array(out)
+
+
+def _check_beam_shape(ids, lens, max_len):
+    assert ids.shape[1] == max_len and (ids[:, 0] == START).all()
+    for i, n in enumerate(lens.tolist()):
+        assert 2 <= n <= max_len
+        assert (ids[i, n:] == PAD).all()
+        assert (ids[i, 1:n - 1] != END).all()          # <end> can only be the last token
+        assert n == max_len or ids[i, n - 1] == END    # shorter than max_len only by ending
+
+
+@pytest.mark.parametrize("name,rule", [("beam_vit_L6", "vit"), ("beam_grid_L3", "grid")])
+def test_beam_search_golden_fp32(dev, name, rule):
+    """fp32 engine against sequences produced by the reference's own _beam_search (tests/golden/beam_*.npz).
+    Identical ids wherever the oracle's tightest selection gap exceeds 10x the fp32 logit tolerance; the score of
+    the returned sequence must always be the oracle's score of that sequence."""
+    z = load_golden(name)
+    for r, (beam, max_len, end_bias) in enumerate(z["runs"]):
+        beam, max_len = int(beam), int(max_len)
+        dec, mem = _beam_decoder(z, end_bias)
+        _, _, o_scores, gaps = oracle_beam.beam_search(dec, mem, START, END, max_len, beam, rule)
+        eng = make_engine(dec.to(dev), "fp32", max_images=8, max_group=8, max_mem=int(z["mem_len"]), max_len=max_len)
+        ids, lens, scores = eng.beam_search_from_memory(mem.to(dev), START, END, max_len, beam_size=beam, stop_rule=rule)
+        ids, lens, scores = ids.cpu(), lens.cpu(), scores.cpu().numpy()
+        dec.cpu()
+        _check_beam_shape(ids, lens, max_len)
+        sure = gaps.numpy() > 10 * TOL["fp32"]
+        assert sure.sum() >= len(sure) - 2, "fixture has too many near-ties to be a test"
+        np.testing.assert_array_equal(ids.numpy()[sure], z[f"ids_{r}"][sure])
+        np.testing.assert_array_equal(lens.numpy()[sure], z[f"len_{r}"][sure])
+        assert np.abs(scores[sure] - o_scores.numpy()[sure]).max() < 1e-3
+        assert np.abs(scores - _sequence_scores(dec, mem, ids, lens)).max() < 1e-3
+        eng.close()
+
+
+@pytest.mark.parametrize("beam,rule,mem_len", [(5, "vit", 49), (3, "grid", 196), (8, "vit", 49), (1, "grid", 33)])
+def test_beam_search_bf16_is_self_consistent(dev, beam, rule, mem_len):
+    """bf16 mode cannot promise the oracle's ranking at near-ties; it must return well-formed sequences whose
+    score is the oracle's score of that very sequence within the bf16 tolerance per step, and on images whose
+    tightest gap is wide the oracle's sequence itself."""
+    dec = small_decoder(seed=5, layers=2, pe_rows=24, end_bias=3.0)
+    mem = torch_port.synthetic_memory(11, mem_len, seed=77)
+    max_len = 14
+    o_ids, o_lens, o_scores, gaps = oracle_beam.beam_search(dec, mem, START, END, max_len, beam, rule)
+    eng = make_engine(dec.to(dev), "bf16", max_images=11, max_group=8, max_mem=mem_len, max_len=max_len)
+    ids, lens, scores = eng.beam_search_from_memory(mem.to(dev), START, END, max_len, beam_size=beam, stop_rule=rule)
+    ids, lens, scores = ids.cpu(), lens.cpu(), scores.cpu().numpy()
+    dec.cpu()
+    _check_beam_shape(ids, lens, max_len)
+    mine = _sequence_scores(dec, mem, ids, lens)
+    assert (np.abs(scores - mine) <= TOL["bf16"] * np.maximum(lens.numpy() - 1, 1)).all()
+    wide = gaps.numpy() > 4 * TOL["bf16"]
+    np.testing.assert_array_equal(ids.numpy()[wide], o_ids.numpy()[wide])
+    eng.close()
+
+
+def test_beam_search_batch_composition_and_graph(dev):
+    """An image's result does not depend on which other images share the batch, nor on graph vs direct launch."""
+    dec = small_decoder(seed=9, layers=2, pe_rows=24, end_bias=3.0)
+    mem = torch_port.synthetic_memory(6, 49, seed=5).to(dev)
+    eng = make_engine(dec.to(dev), "fp32", max_images=6, max_group=5, max_mem=49, max_len=12)
+    ids, lens, scores = eng.beam_search_from_memory(mem, START, END, 12, beam_size=5)
+    for i in (0, 3, 5):
+        i1, l1, s1 = eng.beam_search_from_memory(mem[i:i + 1], START, END, 12, beam_size=5)
+        assert torch.equal(i1[0], ids[i]) and int(l1[0]) == int(lens[i]) and abs(float(s1[0]) - float(scores[i])) < 1e-4
+    eng2 = make_engine(dec, "fp32", max_images=6, max_group=5, max_mem=49, max_len=12, use_graph=False)
+    i2, l2, _ = eng2.beam_search_from_memory(mem, START, END, 12, beam_size=5)
+    assert torch.equal(i2, ids) and torch.equal(l2, lens)
+    # a greedy rollout on the same handle afterwards is unaffected by the beam state
+    g = eng.decode_from_memory(mem, START, END, max_len=12)
+    g2 = eng2.decode_from_memory(mem, START, END, max_len=12)
+    assert torch.equal(g.ids, g2.ids)
+    eng.close(); eng2.close()
+
+
+def test_beam_width_one_is_greedy(dev):
+    """beam_size = 1 follows the argmax path until its first <end> (vit:381 with k = 1)."""
+    dec = small_decoder(seed=3, layers=2, pe_rows=24, end_bias=2.5)
+    mem = torch_port.synthetic_memory(7, 49, seed=6).to(dev)
+    eng = make_engine(dec.to(dev), "fp32", max_images=7, max_group=2, max_mem=49, max_len=16)
+    ids, lens, _ = eng.beam_search_from_memory(mem, START, END, 16, beam_size=1)
+    g = eng.decode_from_memory(mem, START, END, max_len=16, early_stop=False, trim=False).ids
+    for i, n in enumerate(lens.tolist()):
+        assert torch.equal(ids[i, :n], g[i, :n])
+    eng.close()
+
+
+def test_generate_beam_search_through_the_installed_model(dev):
+    """model.generate(..., method='beam_search') reaches the engine (vit:290-291: the ViT model fixes beam 5)."""
+    from image_caption_b200 import patch
+
+    class StandInViT(torch.nn.Module):
+        def __init__(self, decoder):
+            super().__init__()
+            self.encoder = torch.nn.Identity()
+            self.decoder = decoder
+            self.vocab_size = VOCAB
+
+        def generate(self, images, start_token, end_token, max_len=50, method="greedy"):
+            raise AssertionError("the reference path must not run")
+
+    dec = small_decoder(seed=4, layers=2, pe_rows=24, end_bias=3.0)
+    model = StandInViT(dec).to(dev)
+    mem = torch_port.synthetic_memory(3, 49, seed=8).to(dev)
+    patch.install(model, precision="fp32", max_images=3, max_group=5, max_mem=49, max_len=12)
+    out = model.generate(mem, START, END, max_len=12, method="beam_search")
+    o_ids, o_lens, _, gaps = oracle_beam.beam_search(dec.cpu(), mem.cpu(), START, END, 12, 5, "vit")
+    assert out.shape == (3, int(o_lens.max())) or (gaps < 10 * TOL["fp32"]).any()
+    for i in range(3):
+        if gaps[i] > 10 * TOL["fp32"]:
+            assert torch.equal(out[i, :int(o_lens[i])].cpu(), o_ids[i, :int(o_lens[i])])
+    with pytest.raises(ValueError):
+        model.generate(mem, START, END, max_len=12, method="nucleus")
+    patch.uninstall(model)
+
+
+def test_beam_search_rejects_bad_arguments(dev):
+    dec = small_decoder(seed=2, layers=1, pe_rows=24)
+    eng = make_engine(dec.to(dev), "fp32", max_images=2, max_group=4, max_mem=49, max_len=12)
+    mem = torch_port.synthetic_memory(2, 49).to(dev)
+    with pytest.raises(ValueError):
+        eng.beam_search_from_memory(mem, START, END, 12, beam_size=9)
+    with pytest.raises(ValueError):
+        eng.beam_search_from_memory(mem, START, END, 12, beam_size=3, stop_rule="length")
+    with pytest.raises(ValueError):
+        eng.beam_search_from_memory(mem.cpu(), START, END, 12, beam_size=3)
+    ids, lens, _ = eng.beam_search_from_memory(mem, START, END, 12, beam_size=6)  # capacity grows on demand
+    assert ids.shape == (2, 12)
+    eng.close()

@@ -97,3 +97,41 @@ def test_prefix_longer_than_table_raises():
     w = torch_port.weights_to_numpy(dec)
     with pytest.raises(ValueError):
         decoder_np.decoder_forward(w, np.zeros((1, 5), np.int64), np.zeros((1, 3, 512), np.float32))
+
+
+# ---------------------------------------------------------------- beam search
+import pytest  # noqa: E402
+
+from conftest import VOCAB, load_golden  # noqa: E402
+from oracle import beam as oracle_beam  # noqa: E402
+
+
+def beam_case_decoder(z, end_bias):
+    dec = torch_port.build_decoder(0, VOCAB, 512, 8, int(z["n_layers"]), 2048, int(z["pe_rows"]),
+                                   perturb=float(z["perturb"]))
+    with torch.no_grad():
+        dec.fc_out.bias[END] += float(end_bias)
+    return dec.eval(), torch_port.synthetic_memory(int(z["n_images"]), int(z["mem_len"]))
+
+
+@pytest.mark.parametrize("name,rule", [("beam_vit_L6", "vit"), ("beam_grid_L3", "grid")])
+def test_beam_search_restatement_matches_reference(name, rule):
+    """oracle/beam.py against sequences produced by the reference's own _beam_search (vit:327-420, grid:253-322)."""
+    z = load_golden(name)
+    for r, (beam, max_len, end_bias) in enumerate(z["runs"]):
+        dec, mem = beam_case_decoder(z, end_bias)
+        ids, lens, scores, _ = oracle_beam.beam_search(dec, mem, START, END, int(max_len), int(beam), rule)
+        np.testing.assert_array_equal(lens.numpy(), z[f"len_{r}"])
+        np.testing.assert_array_equal(ids.numpy(), z[f"ids_{r}"])
+        assert torch.isfinite(scores).all()
+
+
+def test_beam_stop_rules_differ_where_the_reference_models_differ():
+    """grid:308 stops once len(completed) >= current beam width; vit:402 only when a whole step ended."""
+    z = load_golden("beam_grid_L3")
+    beam, max_len, end_bias = z["runs"][0]
+    dec, mem = beam_case_decoder(z, end_bias)
+    g = oracle_beam.beam_search(dec, mem, START, END, int(max_len), int(beam), "grid")
+    v = oracle_beam.beam_search(dec, mem, START, END, int(max_len), int(beam), "vit")
+    # the ViT rule searches longer, so its winner can only score at least as well
+    assert (v[2] >= g[2] - 1e-5).all()
