@@ -104,7 +104,7 @@ __device__ __forceinline__ uint4 ld_stream16(const void* p) {
 }
 __global__ void __launch_bounds__(kAttnWarps * 32)
 self_attn_stream_kernel(const bf16* __restrict__ q, const bf16* __restrict__ kc, const bf16* __restrict__ vc,
-                        bf16* __restrict__ out, int M, int t_pad, const DecState* st) {
+                        bf16* __restrict__ out, int M, int t_pad, const DecState* st, const int* __restrict__ anc) {
   asm volatile("griddepcontrol.wait;" ::: "memory");  // q and the appended K/V rows (PDL launches)
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   if (st->done) return;
@@ -115,6 +115,11 @@ self_attn_stream_kernel(const bf16* __restrict__ q, const bf16* __restrict__ kc,
   const size_t row_base = (size_t)gw * t_pad * kHD + c * 8;  // gw == m*H + h
   const bf16* kb = kc + row_base;
   const bf16* vb = vc + row_base;
+  // beam search (beam.cuh): position j of the hypothesis in row m lives in cache row anc[step & 1][m][j]
+  const int* arow = anc != nullptr ? anc + ((size_t)(n & 1) * M + gw / kH) * t_pad : nullptr;
+  auto row_shift = [&](int pos) -> long long {
+    return arow != nullptr ? ((long long)arow[pos] - gw / kH) * (long long)kH * t_pad * kHD : 0ll;
+  };
   float qv[8];
   {
     const uint4 r = *reinterpret_cast<const uint4*>(q + (size_t)gw * kHD + c * 8);
@@ -130,8 +135,9 @@ self_attn_stream_kernel(const bf16* __restrict__ q, const bf16* __restrict__ kc,
     for (int it = 0; it < 8; ++it) {
       const int pos = p0 + it * 4 + g;
       if (pos <= n) {
-        kr[it] = ld_stream16(kb + (size_t)pos * kHD);
-        vr[it] = ld_stream16(vb + (size_t)pos * kHD);
+        const long long sh = row_shift(pos);
+        kr[it] = ld_stream16(kb + sh + (size_t)pos * kHD);
+        vr[it] = ld_stream16(vb + sh + (size_t)pos * kHD);
       } else {
         kr[it] = make_uint4(0u, 0u, 0u, 0u);
         vr[it] = make_uint4(0u, 0u, 0u, 0u);

@@ -550,6 +550,7 @@ extern "C" int capdec_create(const capdec_config* cfg, int device, capdec_handle
   if (const char* e = getenv("CAPDEC_LN_TMA_STORE")) h->force_ln_tma_store = atoi(e) != 0 ? 1 : 0;
   if (const char* e = getenv("CAPDEC_NO_CROSS_STREAM")) h->no_cross_stream = atoi(e) != 0;
   if (const char* e = getenv("CAPDEC_NO_WHOLE_K")) h->no_whole_k = atoi(e) != 0;
+  if (const char* e = getenv("CAPDEC_BEAM_V1")) h->beam_v1 = atoi(e) != 0;
   if (const char* e = getenv("CAPDEC_GRAPH_STEPS")) h->graph_steps = std::max(1, atoi(e));
   if (const char* e = getenv("CAPDEC_BNB")) h->force_bnb = atoi(e);
   if (const char* e = getenv("CAPDEC_STAGES")) h->force_stages = atoi(e);
@@ -840,7 +841,8 @@ static int enqueue_step_fast(capdec_handle h, cudaStream_t s, int n_images, int 
         const int blocks = (M * kH + kAttnWarps - 1) / kAttnWarps;
         ProfScope ps(h, s);
         e = launch_ex(self_attn_stream_kernel, dim3(blocks), dim3(kAttnWarps * 32), 0, s, 1, h->use_pdl, (const bf16*)h->q,
-                      (const bf16*)kc, (const bf16*)vc, (bf16*)h->a, M, h->t_pad, st);
+                      (const bf16*)kc, (const bf16*)vc, (bf16*)h->a, M, h->t_pad, st,
+                      (const int*)(h->beam_mode ? h->beam.anc : nullptr));
       }
       CUDA_TRY(h, e);
       h->launches_this_enqueue++;
@@ -901,6 +903,27 @@ static int enqueue_step_fast(capdec_handle h, cudaStream_t s, int n_images, int 
       }
     }
   }
+  if (h->beam_mode) {
+    // beam search: logits to memory (fp32, as in the v1 step), per-image top-k head, then the next step's embedding
+    EpiLinear<float, false> ev{h->logits, h->fc_b, kVPad};
+    set_tag(h, "gemm_vocab", gemm_bytes(M, kVPad, kD, 4, 4, 4));
+    TRY((launch_simt<float, float, EpiLinear<float, false>>(h, s, h->x, kD, h->fc_w, kD, M, kVPad, kD, ev, st)));
+    {
+      set_tag(h, "beam_head", (double)M * (kVPad * 4 + 8 + 4 + 2 * h->t_pad * 4));
+      ProfScope ps(h, s);
+      beam_head_kernel<<<n_images, group * 32, 0, s>>>(h->st, h->cp, h->beam, h->logits, n_images, group, h->cfg.vocab, h->t_pad, h->beam_grid_rule);
+    }
+    CUDA_TRY(h, cudaGetLastError());
+    h->launches_this_enqueue++;
+    {
+      set_tag(h, "embed_pe", (double)M * kD * (4 + 4 + 2));
+      ProfScope ps(h, s);
+      embed_pe_kernel<bf16><<<(M * (kD / 4) + 255) / 256, 256, 0, s>>>(h->st, h->cp, h->emb, h->pe, h->x, (bf16*)h->xb, M);
+    }
+    CUDA_TRY(h, cudaGetLastError());
+    h->launches_this_enqueue++;
+    return 0;
+  }
   {
     set_tag(h, "vocab_head", (double)kD * kVPad * 4 + (double)M * (kD * 4 + 8 + 4) + (double)M * kD * (4 + 4 + 2));
     ProfScope ps(h, s);
@@ -920,7 +943,7 @@ static int enqueue_step_fast(capdec_handle h, cudaStream_t s, int n_images, int 
 
 static int enqueue_step(capdec_handle h, cudaStream_t s, int n_images, int S, int group) {
   h->launches_this_enqueue = 0;
-  if (h->fast && !h->beam_mode) return enqueue_step_fast(h, s, n_images, S, group);  // beam search runs the v1 kernels
+  if (h->fast && !(h->beam_mode && h->beam_v1)) return enqueue_step_fast(h, s, n_images, S, group);
   return h->bf16 ? enqueue_step_t<bf16>(h, s, n_images, S, group) : enqueue_step_t<float>(h, s, n_images, S, group);
 }
 
@@ -1173,6 +1196,11 @@ extern "C" int capdec_beam_search(capdec_handle h, const capdec_beam_args* a, vo
   h->beam_mode = true;
   h->beam_grid_rule = (a->flags & CAPDEC_BEAM_STOP_GRID) ? 1 : 0;
   const int T = a->max_len - 1;
+  if (h->fast && !h->beam_v1) {  // input of step 0 (the v2 step embeds at its end, for the step after)
+    embed_pe_kernel<bf16><<<(M * (kD / 4) + 255) / 256, 256, 0, s>>>(h->st, h->cp, h->emb, h->pe, h->x, (bf16*)h->xb, M);
+    CUDA_TRY(h, cudaGetLastError());
+    h->launches++;
+  }
   if (h->use_graph && !h->profiling) {
     StepGraph* g = nullptr;
     const int per = std::max(1, std::min(h->graph_steps, T));

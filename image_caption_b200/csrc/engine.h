@@ -107,8 +107,9 @@ struct capdec_engine {
   bool prefilled = false;
   bool prefilled_once = false;
   std::map<std::tuple<int, int, int, int>, capdec::StepGraph> graphs;  // (n_images, mem_len, group, steps in the graph)
-  // ---- beam search: runs the v1 step kernels with an ancestry table and a per-image head
+  // ---- beam search: the step kernels with an ancestry table for self-attention and a per-image head
   bool beam_mode = false;          // set for the duration of capdec_beam_search
+  bool beam_v1 = false;            // env CAPDEC_BEAM_V1: beam search on the v1 step kernels also in bf16 + tcgen05 mode
   int beam_grid_rule = 0;          // stop rule of the Grid model (grid:308) instead of the ViT model's (vit:402)
   capdec::BeamState beam{};        // buffers allocated on first use
   long long* beam_tok = nullptr;   // [M_max][max_len] token of each slot at each position

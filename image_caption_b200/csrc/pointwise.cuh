@@ -41,6 +41,7 @@ __global__ void embed_pe_kernel(const DecState* st, const CallParams* cp, const 
   if (idx >= M * (kD / 4)) return;
   const int m = idx / (kD / 4), c = (idx % (kD / 4)) * 4;
   const int n = st->step;
+  if (n >= cp->max_len - 1) return;  // launched after the last step's head (v2 beam search): no next position
   const long long tok = cp->ids[(size_t)m * cp->max_len + n];
   const float4 e = __ldg(reinterpret_cast<const float4*>(emb + (size_t)tok * kD + c));
   const float4 p = __ldg(reinterpret_cast<const float4*>(pe + (size_t)n * kD + c));
