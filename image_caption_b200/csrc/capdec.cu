@@ -154,8 +154,10 @@ static int launch_umma_bn(capdec_handle h, cudaStream_t s, const CUtensorMap& ta
   auto kern = gemm_umma_kernel<BN, Epi>;  // dynamic-smem limit raised once in configure_umma_kernels()
   const int num_kb = K / kUmmaBK;
   int stages = std::min(num_kb, 8);
-  while (umma_smem_bytes(BN, stages) > kMaxDynSmem) --stages;
   dim3 grid(N / BN, (M + kUmmaBM - 1) / kUmmaBM);
+  // many tiles per SM (prefill): two CTAs per SM, so that one's epilogue overlaps the other's main loop
+  const int budget = (long long)grid.x * grid.y > 2 * 148 ? 110 * 1024 : kMaxDynSmem;
+  while (stages > 2 && umma_smem_bytes(BN, stages) > budget) --stages;
   ProfScope ps(h, s);
   kern<<<grid, kUmmaThreads, umma_smem_bytes(BN, stages), s>>>(ta, tw, M, N, K, stages, epi, st);
   CUDA_TRY(h, cudaGetLastError());

@@ -24,7 +24,7 @@ __host__ __device__ constexpr int umma_smem_bytes(int block_n, int stages) {
 }
 
 template <int BLOCK_N, typename Epi>
-__global__ void __launch_bounds__(kUmmaThreads, 1)
+__global__ void __launch_bounds__(kUmmaThreads, 2)
 gemm_umma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_w,
                  int M, int N, int K, int stages, Epi epi, const DecState* st) {
   static_assert(BLOCK_N == 32 || BLOCK_N == 64 || BLOCK_N == 128 || BLOCK_N == 256, "BLOCK_N");
