@@ -15,7 +15,7 @@ constexpr int kAttnWarps = 4;
 // q, out: [M, 512]; kc/vc: this layer's cache [M][H][t_pad][64]; positions 0..st->step valid.
 // anc (beam search, beam.cuh; else null): [2][M][t_pad], buffer (step & 1): the cache row that holds position j of
 // the hypothesis in row m -- re-ranked hypotheses read their ancestors' rows instead of copying them.
-template <typename Elem, int NIT>
+template <typename Elem, int NIT, bool kAnc>
 __global__ void __launch_bounds__(kAttnWarps * 32)
 self_attn_kernel(const Elem* __restrict__ q, const Elem* __restrict__ kc, const Elem* __restrict__ vc,
                  Elem* __restrict__ out, int M, int t_pad, const DecState* st, const int* __restrict__ anc) {
@@ -29,10 +29,11 @@ self_attn_kernel(const Elem* __restrict__ q, const Elem* __restrict__ kc, const 
   const size_t row_base = (size_t)gw * t_pad * kHD;  // gw == m*H + h
   const Elem* kb = kc + row_base + c * 8;
   const Elem* vb = vc + row_base + c * 8;
-  const int* arow = anc != nullptr ? anc + ((size_t)(n & 1) * M + gw / kH) * t_pad : nullptr;
+  const int* arow = kAnc ? anc + ((size_t)(n & 1) * M + gw / kH) * t_pad : nullptr;
   // offset of position j's row relative to kb / vb: 0 without ancestry
   auto row_shift = [&](int j) -> long long {
-    return arow != nullptr ? ((long long)arow[j] - gw / kH) * (long long)kH * t_pad * kHD : 0ll;
+    if constexpr (kAnc) return ((long long)arow[j] - gw / kH) * (long long)kH * t_pad * kHD;
+    else return 0ll;
   };
 
   float qv[8];
@@ -102,6 +103,8 @@ __device__ __forceinline__ uint4 ld_stream16(const void* p) {
   asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
   return r;
 }
+template <bool kAnc>  // kAnc: beam search, rows are read through the ancestry table (a separate instantiation: the
+                      // indirection costs ~50 registers, which the plain rollout's occupancy should not pay)
 __global__ void __launch_bounds__(kAttnWarps * 32)
 self_attn_stream_kernel(const bf16* __restrict__ q, const bf16* __restrict__ kc, const bf16* __restrict__ vc,
                         bf16* __restrict__ out, int M, int t_pad, const DecState* st, const int* __restrict__ anc) {
@@ -116,9 +119,10 @@ self_attn_stream_kernel(const bf16* __restrict__ q, const bf16* __restrict__ kc,
   const bf16* kb = kc + row_base;
   const bf16* vb = vc + row_base;
   // beam search (beam.cuh): position j of the hypothesis in row m lives in cache row anc[step & 1][m][j]
-  const int* arow = anc != nullptr ? anc + ((size_t)(n & 1) * M + gw / kH) * t_pad : nullptr;
+  const int* arow = kAnc ? anc + ((size_t)(n & 1) * M + gw / kH) * t_pad : nullptr;
   auto row_shift = [&](int pos) -> long long {
-    return arow != nullptr ? ((long long)arow[pos] - gw / kH) * (long long)kH * t_pad * kHD : 0ll;
+    if constexpr (kAnc) return ((long long)arow[pos] - gw / kH) * (long long)kH * t_pad * kHD;
+    else return 0ll;
   };
   float qv[8];
   {

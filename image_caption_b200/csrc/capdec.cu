@@ -704,10 +704,16 @@ static int launch_self_attn(capdec_handle h, cudaStream_t s, int l, int M) {
   const Elem* vc = (const Elem*)h->self_v + (size_t)l * h->self_layer_elems;
   const int blocks = (M * kH + kAttnWarps - 1) / kAttnWarps;
   ProfScope ps(h, s);
-  if (h->t_pad == 64)
-    self_attn_kernel<Elem, 16><<<blocks, kAttnWarps * 32, 0, s>>>((const Elem*)h->q, kc, vc, (Elem*)h->a, M, h->t_pad, h->st, h->beam_mode ? h->beam.anc : nullptr);
-  else
-    self_attn_kernel<Elem, 32><<<blocks, kAttnWarps * 32, 0, s>>>((const Elem*)h->q, kc, vc, (Elem*)h->a, M, h->t_pad, h->st, h->beam_mode ? h->beam.anc : nullptr);
+  if (h->beam_mode) {
+    if (h->t_pad == 64)
+      self_attn_kernel<Elem, 16, true><<<blocks, kAttnWarps * 32, 0, s>>>((const Elem*)h->q, kc, vc, (Elem*)h->a, M, h->t_pad, h->st, h->beam.anc);
+    else
+      self_attn_kernel<Elem, 32, true><<<blocks, kAttnWarps * 32, 0, s>>>((const Elem*)h->q, kc, vc, (Elem*)h->a, M, h->t_pad, h->st, h->beam.anc);
+  } else if (h->t_pad == 64) {
+    self_attn_kernel<Elem, 16, false><<<blocks, kAttnWarps * 32, 0, s>>>((const Elem*)h->q, kc, vc, (Elem*)h->a, M, h->t_pad, h->st, nullptr);
+  } else {
+    self_attn_kernel<Elem, 32, false><<<blocks, kAttnWarps * 32, 0, s>>>((const Elem*)h->q, kc, vc, (Elem*)h->a, M, h->t_pad, h->st, nullptr);
+  }
   CUDA_TRY(h, cudaGetLastError());
   h->launches_this_enqueue++;
   return 0;
@@ -842,9 +848,12 @@ static int enqueue_step_fast(capdec_handle h, cudaStream_t s, int n_images, int 
       {
         const int blocks = (M * kH + kAttnWarps - 1) / kAttnWarps;
         ProfScope ps(h, s);
-        e = launch_ex(self_attn_stream_kernel, dim3(blocks), dim3(kAttnWarps * 32), 0, s, 1, h->use_pdl, (const bf16*)h->q,
-                      (const bf16*)kc, (const bf16*)vc, (bf16*)h->a, M, h->t_pad, st,
-                      (const int*)(h->beam_mode ? h->beam.anc : nullptr));
+        if (h->beam_mode)
+          e = launch_ex(self_attn_stream_kernel<true>, dim3(blocks), dim3(kAttnWarps * 32), 0, s, 1, h->use_pdl, (const bf16*)h->q,
+                        (const bf16*)kc, (const bf16*)vc, (bf16*)h->a, M, h->t_pad, st, (const int*)h->beam.anc);
+        else
+          e = launch_ex(self_attn_stream_kernel<false>, dim3(blocks), dim3(kAttnWarps * 32), 0, s, 1, h->use_pdl, (const bf16*)h->q,
+                        (const bf16*)kc, (const bf16*)vc, (bf16*)h->a, M, h->t_pad, st, (const int*)nullptr);
       }
       CUDA_TRY(h, e);
       h->launches_this_enqueue++;
