@@ -108,13 +108,17 @@ template <bool kAnc>  // kAnc: beam search, rows are read through the ancestry t
 __global__ void __launch_bounds__(kAttnWarps * 32)
 self_attn_stream_kernel(const bf16* __restrict__ q, const bf16* __restrict__ kc, const bf16* __restrict__ vc,
                         bf16* __restrict__ out, int M, int t_pad, const DecState* st, const int* __restrict__ anc) {
+  // DecState was last written by the head kernel of the previous step, at least two kernels upstream (the QKV
+  // projection sits in between), so it is complete before this grid may start under programmatic launch: reading it
+  // before the wait takes an L2 round trip off the critical path (the K/V addresses depend on `n`).
+  const int n = st->step;  // last valid position
+  const bool done = st->done != 0;
   asm volatile("griddepcontrol.wait;" ::: "memory");  // q and the appended K/V rows (PDL launches)
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-  if (st->done) return;
+  if (done) return;
   const int gw = blockIdx.x * kAttnWarps + (threadIdx.x >> 5);
   if (gw >= M * kH) return;
   const int lane = threadIdx.x & 31, g = lane >> 3, c = lane & 7;
-  const int n = st->step;  // last valid position
   const size_t row_base = (size_t)gw * t_pad * kHD + c * 8;  // gw == m*H + h
   const bf16* kb = kc + row_base;
   const bf16* vb = vc + row_base;

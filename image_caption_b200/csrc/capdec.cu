@@ -903,7 +903,7 @@ static int enqueue_step_fast(capdec_handle h, cudaStream_t s, int n_images, int 
         TRY((launch_swap<false>(h, s, lp.m_2, h->tx_h, M, kD, F, ep, no_ln, st, 4)));
         set_tag(h, "sum_ln", (double)M * kD * (4 * 4 + 4 + 4 + 2));
         ProfScope ps(h, s);
-        e = launch_ex(sum_ln_kernel, dim3((M + 3) / 4), dim3(128), 0, s, 1, h->use_pdl, h->x, (const float*)h->part, 4,
+        e = launch_ex(sum_ln_kernel<4>, dim3((M + 3) / 4), dim3(128), 0, s, 1, h->use_pdl, h->x, (const float*)h->part,
                       (const float*)lp.b_2, (const float*)lp.ln_w[2], (const float*)lp.ln_b[2], (bf16*)h->xb, M, st);
         CUDA_TRY(h, e);
         h->launches_this_enqueue++;

@@ -90,29 +90,44 @@ add_ln_kernel(float* __restrict__ x, const float* __restrict__ t, const float* _
 }
 
 // x <- LN(x + bias + sum_z part[z]) : closes a split-K projection whose k-slices wrote fp32 partial
-// products part[z][M][512] (small batches: FFN2's K = 2048 is 128 tcgen05.mma instructions of ~148 cycles
-// in one CTA, 32 per CTA when divided over 4).  One warp per row.
+// products part[z][M][512] (small batches: FFN2's K = 2048 divided over 4 CTAs per tile).  One warp per row.
+// NZ is a compile-time constant so that all 4 + 4*NZ row loads are in flight together (with a run-time slice count
+// they were issued one slice at a time: ~2.9 us of the kernel's in-chain time at cfg2, measured by skipping it);
+// bias / gamma / beta do not depend on the step and are read before the programmatic-launch wait.
+template <int NZ>
 __global__ void __launch_bounds__(128)
-sum_ln_kernel(float* __restrict__ x, const float* __restrict__ part, int nz, const float* __restrict__ bias,
+sum_ln_kernel(float* __restrict__ x, const float* __restrict__ part, const float* __restrict__ bias,
               const float* __restrict__ gamma, const float* __restrict__ beta, bf16* __restrict__ xb, int M, const DecState* st) {
+  const int lane = threadIdx.x & 31;
+  float4 bi[4], ga[4], be[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int c = i * 128 + lane * 4;
+    bi[i] = __ldg(reinterpret_cast<const float4*>(bias + c));
+    ga[i] = __ldg(reinterpret_cast<const float4*>(gamma + c));
+    be[i] = __ldg(reinterpret_cast<const float4*>(beta + c));
+  }
   asm volatile("griddepcontrol.wait;" ::: "memory");
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   if (st->done) return;
   const int row = blockIdx.x * 4 + (threadIdx.x >> 5);
   if (row >= M) return;
-  const int lane = threadIdx.x & 31;
+  float4 xin[4], pz[NZ][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int c = i * 128 + lane * 4;
+    xin[i] = *reinterpret_cast<const float4*>(x + (size_t)row * kD + c);
+#pragma unroll
+    for (int z = 0; z < NZ; ++z) pz[z][i] = *reinterpret_cast<const float4*>(part + ((size_t)z * M + row) * kD + c);
+  }
   float v[16];
   float s = 0.f;
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
-    const int c = i * 128 + lane * 4;
-    float4 a = *reinterpret_cast<const float4*>(x + (size_t)row * kD + c);
-    const float4 b = __ldg(reinterpret_cast<const float4*>(bias + c));
-    a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
-    for (int z = 0; z < nz; ++z) {
-      const float4 t = *reinterpret_cast<const float4*>(part + ((size_t)z * M + row) * kD + c);
-      a.x += t.x; a.y += t.y; a.z += t.z; a.w += t.w;
-    }
+    float4 a = xin[i];
+    a.x += bi[i].x; a.y += bi[i].y; a.z += bi[i].z; a.w += bi[i].w;
+#pragma unroll
+    for (int z = 0; z < NZ; ++z) { a.x += pz[z][i].x; a.y += pz[z][i].y; a.z += pz[z][i].z; a.w += pz[z][i].w; }
     v[4 * i] = a.x; v[4 * i + 1] = a.y; v[4 * i + 2] = a.z; v[4 * i + 3] = a.w;
     s += (a.x + a.y) + (a.z + a.w);
   }
@@ -124,10 +139,8 @@ sum_ln_kernel(float* __restrict__ x, const float* __restrict__ part, int nz, con
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
     const int c = i * 128 + lane * 4;
-    const float4 g = __ldg(reinterpret_cast<const float4*>(gamma + c));
-    const float4 b = __ldg(reinterpret_cast<const float4*>(beta + c));
-    const float r0 = v[4 * i] * rstd * g.x + b.x, r1 = v[4 * i + 1] * rstd * g.y + b.y;
-    const float r2 = v[4 * i + 2] * rstd * g.z + b.z, r3 = v[4 * i + 3] * rstd * g.w + b.w;
+    const float r0 = v[4 * i] * rstd * ga[i].x + be[i].x, r1 = v[4 * i + 1] * rstd * ga[i].y + be[i].y;
+    const float r2 = v[4 * i + 2] * rstd * ga[i].z + be[i].z, r3 = v[4 * i + 3] * rstd * ga[i].w + be[i].w;
     *reinterpret_cast<float4*>(x + (size_t)row * kD + c) = make_float4(r0, r1, r2, r3);
     store4(xb + (size_t)row * kD + c, r0, r1, r2, r3);
   }
