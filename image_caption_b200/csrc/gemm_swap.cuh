@@ -63,6 +63,13 @@ __device__ __forceinline__ float lane_transpose_sum(float (&v)[32], int lane) {
 // ---------------------------------------------------------------- epilogues (feature-major)
 // chunk(): called by the thread owning output feature f with 32 accumulators for sequence
 // rows r0 .. r0+31 (rows >= M must be skipped).
+// prepare(): called by the same thread while the MMAs are still running (after the programmatic-launch wait): the
+// bias and the step index are global loads; fetched inside chunk() they would add an L2 round trip to the end of
+// every kernel of the chain.
+struct SwapEpiPre {
+  float bias;
+  int step;
+};
 
 // out[row, f] = act(acc + bias[f])
 template <typename OutT, bool kRelu>
@@ -71,8 +78,9 @@ struct SwapLinear {
   const float* bias;
   int ldo;
   long long zstride = 0;  // split-K launches (gridDim.z > 1): k-slice z writes its partial product to out + z * zstride
-  __device__ __forceinline__ void chunk(int f, int r0, int M, const float (&v)[32]) const {
-    const float b = bias ? __ldg(bias + f) : 0.f;
+  __device__ __forceinline__ SwapEpiPre prepare(int f) const { return SwapEpiPre{bias ? __ldg(bias + f) : 0.f, 0}; }
+  __device__ __forceinline__ void chunk(int f, int r0, int M, const float (&v)[32], const SwapEpiPre& pre) const {
+    const float b = pre.bias;
     OutT* o = out + (size_t)blockIdx.z * zstride;
 #pragma unroll
     for (int j = 0; j < 32; ++j) {
@@ -94,9 +102,10 @@ struct SwapQKV {
   const float* bias;
   const DecState* st;
   int t_pad;
-  __device__ __forceinline__ void chunk(int f, int r0, int M, const float (&v)[32]) const {
-    const float b = __ldg(bias + f);
-    const int n = st->step;
+  __device__ __forceinline__ SwapEpiPre prepare(int f) const { return SwapEpiPre{__ldg(bias + f), st->step}; }
+  __device__ __forceinline__ void chunk(int f, int r0, int M, const float (&v)[32], const SwapEpiPre& pre) const {
+    const float b = pre.bias;
+    const int n = pre.step;
     const int which = f >> 9, c = f & (kD - 1);
     Elem* base;
     size_t row_stride, off;
@@ -295,6 +304,10 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
     const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16);
     constexpr int kChunks = BNB / kCStep;  // 32-column chunks per epilogue warp (1 or 2)
     float xres[kLN ? kChunks : 1][kLN ? 32 : 1];  // kLN: residual rows of this thread's feature, fetched while the MMAs run
+    SwapEpiPre epi_pre{0.f, 0};
+    float ln_g = 0.f, ln_be = 0.f, ln_bias = 0.f;  // fetched while the MMAs run
+    if constexpr (kLN) { ln_g = __ldg(ln.gamma + f); ln_be = __ldg(ln.beta + f); ln_bias = __ldg(ln.bias + f); }
+    if constexpr (!kLN) epi_pre = epi.prepare(f);
     if constexpr (kLN) {
       if (active && ks == 0) {
 #pragma unroll
@@ -333,13 +346,13 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
         for (int c0 = cbeg; c0 < BNB; c0 += kCStep) {
           float v[32];
           load_acc(taddr + (uint32_t)c0, v);
-          epi.chunk(f, b0 + c0, M, v);
+          epi.chunk(f, b0 + c0, M, v, epi_pre);
         }
       }
     } else {
       const int e = threadIdx.x - 64;  // 0..kEpi-1
       const int fl = quarter * 32 + lane;  // feature within the tile
-      const float bias_f = __ldg(ln.bias + f);
+      const float bias_f = ln_bias;
       const bool lead = ks == 0;           // this CTA owns the epilogue of its feature tile
       if constexpr (KSPLIT > 1) {
         ptx::cluster_wait();  // #1
@@ -422,7 +435,7 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
         // staged: every MMA has completed (tmem_full), so the operand ring is free to hold the output tile
         float* x_stage = reinterpret_cast<float*>(smem);                             // [BNB][128] fp32
         bf16* xb_stage = reinterpret_cast<bf16*>(smem + (size_t)BNB * kSwapBF * 4);  // [BNB][128] bf16
-        const float g = __ldg(ln.gamma + f), be = __ldg(ln.beta + f);
+        const float g = ln_g, be = ln_be;
 #pragma unroll 1
         for (int c0 = cbeg; c0 < BNB; c0 += kCStep) {
           // the row statistics first, as 16 vector loads: read one by one between the stores below they would be
