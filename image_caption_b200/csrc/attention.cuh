@@ -235,9 +235,10 @@ cross_attn_stream_kernel(const bf16* __restrict__ q, const bf16* __restrict__ ck
     asm volatile("prefetch.global.L2 [%0];" ::"l"(kb - c * 8 + (size_t)(32 + lane) * kHD));
     asm volatile("prefetch.global.L2 [%0];" ::"l"(vb - c * 8 + (size_t)(32 + lane) * kHD));
   }
+  const bool done = st->done != 0;  // written by the previous step's head kernel, long complete (see self_attn_stream_kernel)
   asm volatile("griddepcontrol.wait;" ::: "memory");  // the query projection of this step
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-  if (st->done || !live) return;
+  if (done || !live) return;
   float qv[8];
   {
     const uint4 r = *reinterpret_cast<const uint4*>(q + (size_t)gw * kHD + c * 8);  // group == 1: row == image

@@ -81,10 +81,11 @@ cross_attn_tma_kernel(const __grid_constant__ CUtensorMap tm_kv, const bf16* __r
     ptx::mbar_expect_tx(&bar[1], (uint32_t)SB * 128);
     ptx::tma_load_2d_hint(v_s, &tm_kv, &bar[1], 0, row_v, pol);
   }
+  const bool done = st->done != 0;  // written by the previous step's head kernel, long complete
   __syncthreads();
   ptx::pdl_wait();
   ptx::pdl_trigger();
-  if (st->done) {  // rollout over: nothing to compute, but no copy may outlive the CTA
+  if (done) {  // rollout over: nothing to compute, but no copy may outlive the CTA
     if (tid == 0) { ptx::mbar_wait(&bar[0], 0); ptx::mbar_wait(&bar[1], 0); }
     return;
   }

@@ -107,9 +107,10 @@ sum_ln_kernel(float* __restrict__ x, const float* __restrict__ part, const float
     ga[i] = __ldg(reinterpret_cast<const float4*>(gamma + c));
     be[i] = __ldg(reinterpret_cast<const float4*>(beta + c));
   }
+  const bool done = st->done != 0;  // written by the previous step's head kernel, long complete
   asm volatile("griddepcontrol.wait;" ::: "memory");
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-  if (st->done) return;
+  if (done) return;
   const int row = blockIdx.x * 4 + (threadIdx.x >> 5);
   if (row >= M) return;
   float4 xin[4], pz[NZ][4];
@@ -288,11 +289,21 @@ vocab_head_kernel(DecState* st, const CallParams* cp, float* __restrict__ x, con
     load_slab(b, b);
     asm volatile("cp.async.commit_group;" ::: "memory");
   }
-  asm volatile("griddepcontrol.wait;" ::: "memory");
-  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-  if (st->done) { asm volatile("cp.async.wait_group 0;" ::: "memory"); return; }
+  // the call parameters are constant for the rollout and DecState was written by the previous step's head kernel
+  // (a whole step upstream): read both, and the next position's encoding row, before the wait
   const CallParams p = *cp;
   const int n = st->step;
+  const bool done = st->done != 0;
+  const float4 bv = __ldg(reinterpret_cast<const float4*>(bias) + lane);
+  float4 pe4[4];
+  {
+    const int pn = (n + 1 < p.max_len - 1) ? n + 1 : 0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) pe4[i] = __ldg(reinterpret_cast<const float4*>(pe + (size_t)pn * kD + i * 128 + lane * 4));
+  }
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  if (done) { asm volatile("cp.async.wait_group 0;" ::: "memory"); return; }
   const int r0 = blockIdx.x * R;
   // x rows of this CTA -> smem (rows >= M read as zero)
   for (int i = tid; i < R * kD / 4; i += kThreads) {
@@ -325,7 +336,6 @@ vocab_head_kernel(DecState* st, const CallParams* cp, float* __restrict__ x, con
     if (sl + kVhBufs < kSlabs) load_slab(sl + kVhBufs, sl % kVhBufs);
     asm volatile("cp.async.commit_group;" ::: "memory");
   }
-  const float4 bv = __ldg(reinterpret_cast<const float4*>(bias) + lane);
   {
     const int m = r0 + warp;
     if (m < M) {  // warp-uniform
@@ -360,7 +370,7 @@ vocab_head_kernel(DecState* st, const CallParams* cp, float* __restrict__ x, con
       for (int i = 0; i < 4; ++i) {
         const int c = i * 128 + lane * 4;
         const float4 e4 = __ldg(reinterpret_cast<const float4*>(emb + (size_t)tok * kD + c));
-        const float4 p4 = __ldg(reinterpret_cast<const float4*>(pe + (size_t)(n + 1) * kD + c));
+        const float4 p4 = pe4[i];
         float4 o;
         o.x = __fadd_rn(__fmul_rn(e4.x, sc), p4.x); o.y = __fadd_rn(__fmul_rn(e4.y, sc), p4.y);
         o.z = __fadd_rn(__fmul_rn(e4.z, sc), p4.z); o.w = __fadd_rn(__fmul_rn(e4.w, sc), p4.w);
