@@ -141,7 +141,11 @@ static int make_weight_maps(capdec_handle h, WeightMaps* wm, const void* ptr, in
     int rc = make_map(h, &wm->bn[i], ptr, n, k, bns[i]);
     if (rc) return rc;
   }
-  if (n % kSwapBF == 0 && (k / kUmmaBK) % kSwapWholeKB == 0) return make_map3(h, &wm->w3, ptr, n, k, kSwapBF, kSwapWholeKB / 2);
+  if (n % kSwapBF == 0 && (k / kUmmaBK) % kSwapWholeKB == 0) {
+    int rc = make_map3(h, &wm->w3, ptr, n, k, kSwapBF, kSwapWholeKB / 2);
+    if (rc) return rc;
+    return make_map3(h, &wm->w3g2, ptr, n, k, kSwapBF, 2);
+  }
   return 0;
 }
 
@@ -264,6 +268,35 @@ static int swap_whole_k(capdec_handle h, int bnb, int num_kb, int stages) {
   return (!h->no_whole_k && num_kb == kSwapWholeKB && stages >= kSwapWholeKB && bnb <= 64) ? 1 : 0;
 }
 
+// k-blocks per TMA copy where whole-K copies do not apply (K = 2048, or 128-row tiles whose whole K does not fit):
+// the largest of 4 / 2 that leaves at least two ring slots; launches that run two CTAs per SM keep one box per k-block.
+// Returns the group size (1 = ungrouped) and rounds `stages` to whole groups.
+// Off by default (env CAPDEC_KGROUP=1): measured on B200 it changes nothing (cfg5 526.8 vs 524.8 us/step, cfg3 897.7 vs
+// 889.5).  Those main loops are not waiting for the TMA unit: a k-block of a 128 x 128 tile writes 32 KB into shared
+// memory and its four MMAs read 32 KB back, 512 cycles of the SM's 128 B/clk against 256 cycles of tensor pipe --
+// the phase trace shows 121 cycles per MMA.  Halving the shared-memory traffic per flop needs cta_group::2 tiles.
+static int swap_kgroup(capdec_handle h, int bnb, int num_kb, int ctas, int ksplit, int whole, int* stages) {
+  if (whole || h->no_kgroup || ctas > 148 || h->force_stages > 0) return 1;
+  for (int g = 4; g >= 2; g -= 2) {
+    if (num_kb % g != 0 || num_kb < g) continue;
+    int st = std::min(num_kb, 12) / g * g;
+    while (st > g && swap_smem_bytes(bnb, st, ksplit) > kMaxDynSmem) st -= g;
+    if (st >= 2 * g || (st == g && num_kb == g)) {
+      if (swap_smem_bytes(bnb, st, ksplit) > kMaxDynSmem) continue;
+      *stages = st;
+      return g;
+    }
+  }
+  return 1;
+}
+static void note_plan(capdec_handle h, int bnb, bool ln, int n_out, int K, int ctas, int stages, int whole, int kgrp) {
+  static int left = getenv("CAPDEC_TRACE_GEMM") ? 24 : 0;  // tuning aid: the first launches' copy plans
+  if (left > 0) { --left; fprintf(stderr, "swap plan: bnb=%d ln=%d n_out=%d K=%d ctas=%d stages=%d whole=%d kgrp=%d\n", bnb, (int)ln, n_out, K, ctas, stages, whole, kgrp); }
+  (void)h;
+}
+static const CUtensorMap& pick_w3(const WeightMaps& tw, int kgrp) { return kgrp == 2 ? tw.w3g2 : tw.w3; }
+static const CUtensorMap& pick_x3(const ActMaps& tx, int kgrp) { return kgrp == 2 ? tx.grp2 : (kgrp == 4 ? tx.grp4 : tx.whole); }
+
 template <int BNB, bool kLN, typename Epi, int KSPLIT>
 static int launch_swap_ks(capdec_handle h, cudaStream_t s, const WeightMaps& tw, const ActMaps& tx, int M, int n_out,
                           int K, const Epi& epi, const SwapLNParams& ln, const DecState* st) {
@@ -271,10 +304,13 @@ static int launch_swap_ks(capdec_handle h, cudaStream_t s, const WeightMaps& tw,
   int stages = swap_stages(h, BNB, K / KSPLIT, grid.x * grid.y);
   while (stages > 2 && swap_smem_bytes(BNB, stages, KSPLIT) > kMaxDynSmem) --stages;
   while (kLN && stages * swap_stage_bytes(BNB) < swap_ln_stage_out_bytes(BNB)) ++stages;  // the output tile is staged in the ring
+  const int whole = swap_whole_k(h, BNB, K / kSwapBK / KSPLIT, stages);
+  const int kgrp = swap_kgroup(h, BNB, K / kSwapBK / KSPLIT, grid.x * grid.y, KSPLIT, whole, &stages);
+  note_plan(h, BNB, kLN, n_out, K, grid.x * grid.y, stages, whole, kgrp);
   ProfScope ps(h, s);
   cudaError_t e = launch_ex(gemm_swap_kernel<BNB, kLN, Epi, KSPLIT>, grid, dim3(swap_threads(BNB, kLN)), swap_smem_bytes(BNB, stages, KSPLIT), s,
-                            kLN ? 4 * KSPLIT : 1, h->use_pdl, tw.bn[2], tx.tile, tw.w3, tx.whole,
-                            swap_whole_k(h, BNB, K / kSwapBK / KSPLIT, stages), M, K, stages, epi, ln, st);
+                            kLN ? 4 * KSPLIT : 1, h->use_pdl, tw.bn[2], tx.tile, pick_w3(tw, kgrp), pick_x3(tx, kgrp),
+                            whole, kgrp, M, K, stages, epi, ln, st);
   if (e != cudaSuccess) return fail(h, CAPDEC_ERR_CUDA, "gemm_swap launch failed: %s (BNB=%d n_out=%d K=%d stages=%d ksplit=%d)",
                                     cudaGetErrorString(e), BNB, n_out, K, stages, KSPLIT);
   h->launches_this_enqueue++;
@@ -305,10 +341,13 @@ static int launch_swap_bnb(capdec_handle h, cudaStream_t s, const WeightMaps& tw
   dim3 grid(n_out / kSwapBF, (M + BNB - 1) / BNB, zsplit);
   int stages = swap_stages(h, BNB, K / zsplit, grid.x * grid.y * grid.z);
   while (kLN && stages * swap_stage_bytes(BNB) < swap_ln_stage_out_bytes(BNB)) ++stages;  // the output tile is staged in the ring
+  const int whole = swap_whole_k(h, BNB, K / kSwapBK / zsplit, stages);
+  const int kgrp = swap_kgroup(h, BNB, K / kSwapBK / zsplit, grid.x * grid.y * grid.z, 1, whole, &stages);
+  note_plan(h, BNB, kLN, n_out, K, grid.x * grid.y * grid.z, stages, whole, kgrp);
   ProfScope ps(h, s);
   cudaError_t e = launch_ex(gemm_swap_kernel<BNB, kLN, Epi>, grid, dim3(swap_threads(BNB, kLN)), swap_smem_bytes(BNB, stages), s,
-                            kLN ? 4 : 1, h->use_pdl, tw.bn[2], tx.tile, tw.w3, tx.whole,
-                            swap_whole_k(h, BNB, K / kSwapBK / zsplit, stages), M, K, stages, epi, ln, st);
+                            kLN ? 4 : 1, h->use_pdl, tw.bn[2], tx.tile, pick_w3(tw, kgrp), pick_x3(tx, kgrp),
+                            whole, kgrp, M, K, stages, epi, ln, st);
   if (e != cudaSuccess) return fail(h, CAPDEC_ERR_CUDA, "gemm_swap launch failed: %s (BNB=%d n_out=%d K=%d stages=%d)",
                                     cudaGetErrorString(e), BNB, n_out, K, stages);
   h->launches_this_enqueue++;
@@ -347,6 +386,7 @@ static cudaError_t configure_fast_kernels() {
   if (e == cudaSuccess) e = configure_swap_epi<false, SwapLinear<float, false>>();
   if (e == cudaSuccess) e = configure_swap_epi<false, SwapLinear<float, true>>();
   if (e == cudaSuccess) e = configure_swap_epi<false, SwapQKV<bf16>>();
+  if (e == cudaSuccess) e = configure_swap_epi<false, SwapPartialLN>();
   if (e == cudaSuccess) e = configure_swap_epi<true, SwapNoLN>();
   if (e == cudaSuccess) e = configure_swap_ln_ks<32, 2>();
   if (e == cudaSuccess) e = configure_swap_ln_ks<64, 2>();
@@ -357,8 +397,10 @@ static cudaError_t configure_fast_kernels() {
   if (e == cudaSuccess) e = cudaFuncSetAttribute(cross_attn_tma_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(cross_attn_tma_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(cross_attn_tma_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
-  if (e == cudaSuccess) e = cudaFuncSetAttribute(vocab_head_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, vh_smem_bytes(4));
-  if (e == cudaSuccess) e = cudaFuncSetAttribute(vocab_head_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, vh_smem_bytes(16));
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(vocab_head_kernel<1, 6>, cudaFuncAttributeMaxDynamicSharedMemorySize, vh_smem_bytes(4, 6));
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(vocab_head_kernel<2, 6>, cudaFuncAttributeMaxDynamicSharedMemorySize, vh_smem_bytes(8, 6));
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(vocab_head_kernel<4, 6>, cudaFuncAttributeMaxDynamicSharedMemorySize, vh_smem_bytes(16, 6));
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(vocab_head_kernel<6, 5>, cudaFuncAttributeMaxDynamicSharedMemorySize, vh_smem_bytes(24, 5));
   return e;
 }
 
@@ -493,6 +535,8 @@ static int create_impl(capdec_handle h) {
     TRY(dev_alloc(h, &h->fc_wT, (size_t)kD * kVPad));
     h->part_rows = (int)std::min<size_t>(M, 512);
     TRY(dev_alloc(h, &h->part, (size_t)4 * h->part_rows * kD));
+    TRY(dev_alloc_bytes(h, (void**)&h->tickets, 64 * sizeof(unsigned)));  // one per 32-row tile of <= 512 rows (and slack)
+    CUDA_TRY(h, cudaMemset(h->tickets, 0, 64 * sizeof(unsigned)));
     CUDA_TRY(h, configure_fast_kernels());
   }
   if (h->mega) {
@@ -552,6 +596,9 @@ extern "C" int capdec_create(const capdec_config* cfg, int device, capdec_handle
   if (const char* e = getenv("CAPDEC_LN_TMA_STORE")) h->force_ln_tma_store = atoi(e) != 0 ? 1 : 0;
   if (const char* e = getenv("CAPDEC_NO_CROSS_STREAM")) h->no_cross_stream = atoi(e) != 0;
   if (const char* e = getenv("CAPDEC_NO_WHOLE_K")) h->no_whole_k = atoi(e) != 0;
+  if (const char* e = getenv("CAPDEC_FFN2_FUSE")) h->no_ffn2_fuse = atoi(e) == 0;
+  if (const char* e = getenv("CAPDEC_KGROUP")) h->no_kgroup = atoi(e) == 0;
+  if (const char* e = getenv("CAPDEC_HEAD_RW")) { const int v = atoi(e); h->force_head_rw = (v == 1 || v == 2 || v == 4 || v == 6) ? v : 0; }
   if (const char* e = getenv("CAPDEC_BEAM_V1")) h->beam_v1 = atoi(e) != 0;
   if (const char* e = getenv("CAPDEC_GRAPH_STEPS")) h->graph_steps = std::max(1, atoi(e));
   if (const char* e = getenv("CAPDEC_BNB")) h->force_bnb = atoi(e);
@@ -897,7 +944,16 @@ static int enqueue_step_fast(capdec_handle h, cudaStream_t s, int n_images, int 
       TRY((launch_swap<false>(h, s, lp.m_1, h->tx_xb, M, F, kD, e1, no_ln, st)));
       const int row_tiles = (M + h->bnb - 1) / h->bnb;
       if (M <= h->part_rows && 16 * row_tiles <= 148 && F % (4 * kSwapBK) == 0 && !h->no_ffn2_split) {
-        // small batch: K = d_ff divided over 4 CTAs per tile (fp32 partial products), closed by sum_ln
+        // small batch: K = d_ff divided over 4 CTAs per tile (fp32 partial products), closed by a separate sum_ln launch.
+        // CAPDEC_FFN2_FUSE=1: closed by the last CTA of each row tile instead (SwapPartialLN) -- one launch fewer, but
+        // measured slower on B200 (cfg2 320 vs 293 us/step): 8 CTAs x 7 warps walk 256 rows five at a time behind two
+        // fences and an atomic, where sum_ln's 256 warps take one row each inside a launch that is mostly floor.
+        if (!h->no_ffn2_fuse) {
+          SwapPartialLN ep{h->part, (long long)M * kD, h->x, (bf16*)h->xb, lp.b_2, lp.ln_w[2], lp.ln_b[2], h->tickets};
+          set_tag(h, "gemm_ffn2_sumln", gemm_bytes(M, kD, F, 2, 2, 0) + 2 * 4.0 * M * kD * 4 + (double)M * kD * (4 + 4 + 2));
+          TRY((launch_swap<false>(h, s, lp.m_2, h->tx_h, M, kD, F, ep, no_ln, st, 4)));
+          continue;
+        }
         SwapLinear<float, false> ep{h->part, nullptr, kD, (long long)M * kD};
         set_tag(h, "gemm_ffn2_part", gemm_bytes(M, kD, F, 2, 2, 0) + 4.0 * M * kD * 4);
         TRY((launch_swap<false>(h, s, lp.m_2, h->tx_h, M, kD, F, ep, no_ln, st, 4)));
@@ -938,14 +994,19 @@ static int enqueue_step_fast(capdec_handle h, cudaStream_t s, int n_images, int 
   {
     set_tag(h, "vocab_head", (double)kD * kVPad * 4 + (double)M * (kD * 4 + 8 + 4) + (double)M * kD * (4 + 4 + 2));
     ProfScope ps(h, s);
-    if (M <= 1024)
-      e = launch_ex(vocab_head_kernel<4>, dim3((M + 3) / 4), dim3(128), vh_smem_bytes(4), s, 1, h->use_pdl, h->st,
-                    (const CallParams*)h->cp, h->x, (const float*)h->fc_wT, (const float*)h->fc_b, h->fin, M, h->cfg.vocab,
-                    (const float*)h->emb, (const float*)h->pe, (bf16*)h->xb);
-    else
-      e = launch_ex(vocab_head_kernel<16>, dim3((M + 15) / 16), dim3(512), vh_smem_bytes(16), s, 1, h->use_pdl, h->st,
-                    (const CallParams*)h->cp, h->x, (const float*)h->fc_wT, (const float*)h->fc_b, h->fin, M, h->cfg.vocab,
-                    (const float*)h->emb, (const float*)h->pe, (bf16*)h->xb);
+    // rows per warp: the smallest tile that still covers the batch in one wave of CTAs (148 SMs, one CTA each);
+    // env CAPDEC_HEAD_RW overrides (1, 2, 4 or 6)
+    int rw = M <= 4 * 148 ? 1 : (M <= 8 * 148 ? 2 : (M <= 16 * 148 ? 4 : 6));
+    if (h->force_head_rw > 0) rw = h->force_head_rw;
+    auto launch_head = [&](auto kern, int rows, int bufs) {
+      return launch_ex(kern, dim3((M + rows - 1) / rows), dim3(kVhWarps * 32), vh_smem_bytes(rows, bufs), s, 1, h->use_pdl, h->st,
+                       (const CallParams*)h->cp, h->x, (const float*)h->fc_wT, (const float*)h->fc_b, h->fin, M, h->cfg.vocab,
+                       (const float*)h->emb, (const float*)h->pe, (bf16*)h->xb);
+    };
+    if (rw == 1) e = launch_head(vocab_head_kernel<1, 6>, 4, 6);
+    else if (rw == 2) e = launch_head(vocab_head_kernel<2, 6>, 8, 6);
+    else if (rw == 4) e = launch_head(vocab_head_kernel<4, 6>, 16, 6);
+    else e = launch_head(vocab_head_kernel<6, 5>, 24, 5);
   }
   CUDA_TRY(h, e);
   h->launches_this_enqueue++;
@@ -973,6 +1034,11 @@ static int ensure_activation_maps(capdec_handle h, int M) {
     TRY(make_map3(h, &h->tx_xb.whole, h->xb, M, kD, h->bnb, kSwapWholeKB));
     TRY(make_map3(h, &h->tx_a.whole, h->a, M, kD, h->bnb, kSwapWholeKB));
     TRY(make_map3(h, &h->tx_h.whole, h->hbuf, M, h->cfg.d_ff, h->bnb, kSwapWholeKB));
+    for (int g = 2; g <= 4; g += 2) {
+      TRY(make_map3(h, g == 2 ? &h->tx_xb.grp2 : &h->tx_xb.grp4, h->xb, M, kD, h->bnb, g));
+      TRY(make_map3(h, g == 2 ? &h->tx_a.grp2 : &h->tx_a.grp4, h->a, M, kD, h->bnb, g));
+      TRY(make_map3(h, g == 2 ? &h->tx_h.grp2 : &h->tx_h.grp4, h->hbuf, M, h->cfg.d_ff, h->bnb, g));
+    }
     // measured (B200): staging + bulk stores win for 32-row tiles (cfg2 372.6 -> 368.6 us/step), per-thread stores
     // for wider ones (cfg3 974 -> 958, cfg5 627 -> 620): the 96 KB tile takes ~3.3k cycles to drain
     h->ln_tma_store = h->force_ln_tma_store >= 0 ? h->force_ln_tma_store : (h->bnb == 32 ? 1 : 0);

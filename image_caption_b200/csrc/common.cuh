@@ -146,4 +146,46 @@ __device__ __forceinline__ float philox_uniform(unsigned long long seed, unsigne
   return (float)(r.x >> 8) * (1.0f / 16777216.0f);
 }
 
+
+// x[row] <- LayerNorm(x[row] + bias + sum_z part[z][row]) * gamma + beta, and its bf16 mirror; one warp per row of 512.
+// Shared by sum_ln_kernel and by the split-K projection that closes itself (gemm_swap.cuh, SwapPartialLN) so that
+// both produce the same bits.  Partials and x are read through L2 (ld.global.cg): they were written by other CTAs.
+template <int NZ>
+__device__ __forceinline__ void sum_ln_row(float* __restrict__ x, const float* __restrict__ part, int M, int row, int lane,
+                                           const float4 (&bi)[4], const float4 (&ga)[4], const float4 (&be)[4],
+                                           __nv_bfloat16* __restrict__ xb) {
+  float4 xin[4], pz[NZ][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int c = i * 128 + lane * 4;
+    xin[i] = __ldcg(reinterpret_cast<const float4*>(x + (size_t)row * kD + c));
+#pragma unroll
+    for (int z = 0; z < NZ; ++z) pz[z][i] = __ldcg(reinterpret_cast<const float4*>(part + ((size_t)z * M + row) * kD + c));
+  }
+  float v[16];
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    float4 a = xin[i];
+    a.x += bi[i].x; a.y += bi[i].y; a.z += bi[i].z; a.w += bi[i].w;
+#pragma unroll
+    for (int z = 0; z < NZ; ++z) { a.x += pz[z][i].x; a.y += pz[z][i].y; a.z += pz[z][i].z; a.w += pz[z][i].w; }
+    v[4 * i] = a.x; v[4 * i + 1] = a.y; v[4 * i + 2] = a.z; v[4 * i + 3] = a.w;
+    s += (a.x + a.y) + (a.z + a.w);
+  }
+  const float mean = warp_sum(s) * (1.f / kD);
+  float q = 0.f;
+#pragma unroll
+  for (int i = 0; i < 16; ++i) { v[i] -= mean; q = fmaf(v[i], v[i], q); }
+  const float rstd = rsqrtf(warp_sum(q) * (1.f / kD) + 1e-5f);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int c = i * 128 + lane * 4;
+    const float r0 = v[4 * i] * rstd * ga[i].x + be[i].x, r1 = v[4 * i + 1] * rstd * ga[i].y + be[i].y;
+    const float r2 = v[4 * i + 2] * rstd * ga[i].z + be[i].z, r3 = v[4 * i + 3] * rstd * ga[i].w + be[i].w;
+    *reinterpret_cast<float4*>(x + (size_t)row * kD + c) = make_float4(r0, r1, r2, r3);
+    store4(xb + (size_t)row * kD + c, r0, r1, r2, r3);
+  }
+}
+
 }  // namespace capdec

@@ -16,11 +16,13 @@ namespace capdec {
 struct WeightMaps {
   CUtensorMap bn[3];  // 32, 64, 128
   CUtensorMap w3;     // [64, rows, K/64] view, box = 64 x 128 rows x 4 k-blocks: half of a K = 512 weight slice per copy
+  CUtensorMap w3g2;   // same view, box depth 2 (grouped copies of 128-row activation tiles)
 };
 // TMA views of one activation matrix for the v2 GEMMs
 struct ActMaps {
   CUtensorMap tile;   // box = 64 columns x bnb rows (one k-block)
   CUtensorMap whole;  // [64, rows, K/64] view, box = 64 x bnb rows x 8 k-blocks: all of K = 512 in one copy
+  CUtensorMap grp2, grp4;  // same view, box depth 2 / 4 k-blocks (grouped copies)
 };
 
 struct LayerParams {
@@ -82,12 +84,16 @@ struct capdec_engine {
   CUtensorMap ts_x, ts_xb;         // store views of the residual stream (fp32 / bf16), box = 128 x bnb
   int ln_tma_store = 1;            // LayerNorm epilogue leaves through bulk tensor stores
   int force_ln_tma_store = -1;     // env CAPDEC_LN_TMA_STORE
+  int force_head_rw = 0;           // env CAPDEC_HEAD_RW: rows per warp of the vocabulary head (1, 2, 4, 6)
+  bool no_kgroup = true;           // env CAPDEC_KGROUP=1 clears it: kgrp k-blocks per TMA copy where whole-K copies do not apply
   bool no_whole_k = false;         // env CAPDEC_NO_WHOLE_K: one TMA copy per k-block instead of whole-K copies
   bool no_cross_stream = false;    // env CAPDEC_NO_CROSS_STREAM: keep the tensor-core cross-attention for group == 1
   CUtensorMap tm_ckv;              // whole cross cache as [rows,64], box = 64 x ca_key_rows(S)
   float* fc_wT = nullptr;          // [512][kVPad] fp32: fc_out.weight transposed + padded
   float* part = nullptr;           // [4][min(M_max,512)][512] fp32 split-K partial products (small batches)
   int part_rows = 0;
+  unsigned* tickets = nullptr;     // [row tiles] last-CTA election of the self-closing split-K FFN2 (SwapPartialLN)
+  bool no_ffn2_fuse = true;        // env CAPDEC_FFN2_FUSE=1 clears it: the split-K FFN2 closes itself (no sum_ln launch)
 
   // ---- v3: whole-rollout cluster kernel (rollout_cluster.cuh), used when the shape allows
   bool mega = false;               // enabled (bf16 + tcgen05, not CAPDEC_FLAG_NO_CLUSTER_ROLLOUT)

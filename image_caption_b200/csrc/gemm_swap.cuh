@@ -93,6 +93,62 @@ struct SwapLinear {
   }
 };
 
+// Split-K projection that closes itself (FFN2 at small batch): every k-slice CTA writes its fp32 partial tile
+// part[z][row][f]; the last of the (feature tiles x k-slices) CTAs of a row tile to finish -- elected by a ticket
+// counter in global memory -- adds the slices, the bias and the residual and writes LayerNorm(x + proj) for the
+// tile's rows, one warp per row (sum_ln_row, the arithmetic of sum_ln_kernel).  This removes the sum_ln launch
+// from the step's dependent chain (measured no-work floor of a chained kernel: ~4.2 us).
+struct SwapPartialLN {
+  float* part;          // [gridDim.z][M][512]
+  long long zstride;    // M * 512
+  float* x;             // [M, 512] residual stream, updated in place
+  bf16* xb;             // bf16 mirror
+  const float* bias;    // [512] projection bias
+  const float* gamma;
+  const float* beta;
+  unsigned* tickets;    // [row tiles], zero between launches
+  static constexpr bool kHasFinish = true;
+  __device__ __forceinline__ SwapEpiPre prepare(int) const { return SwapEpiPre{0.f, 0}; }
+  __device__ __forceinline__ void chunk(int f, int r0, int M, const float (&v)[32], const SwapEpiPre&) const {
+    float* o = part + (size_t)blockIdx.z * zstride;
+#pragma unroll
+    for (int j = 0; j < 32; ++j)
+      if (r0 + j < M) o[(size_t)(r0 + j) * kD + f] = v[j];
+  }
+  // every thread of the CTA, after the epilogue warps have stored their partial tile
+  template <int NZ>
+  __device__ __forceinline__ void finish(int b0, int bnb, int M, int* flag) const {
+    __threadfence();  // this thread's partial-tile stores
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      const unsigned total = gridDim.x * gridDim.z;  // CTAs contributing to this row tile
+      const unsigned t = atomicAdd(&tickets[blockIdx.y], 1u);
+      const bool last = t == total - 1;
+      if (last) tickets[blockIdx.y] = 0u;  // nobody else touches it before the next launch
+      __threadfence();
+      *flag = last ? 1 : 0;
+    }
+    __syncthreads();
+    if (*flag == 0) return;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+    float4 bi[4], ga[4], be[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int c = i * 128 + lane * 4;
+      bi[i] = __ldg(reinterpret_cast<const float4*>(bias + c));
+      ga[i] = __ldg(reinterpret_cast<const float4*>(gamma + c));
+      be[i] = __ldg(reinterpret_cast<const float4*>(beta + c));
+    }
+    const int rend = b0 + bnb < M ? b0 + bnb : M;
+    for (int row = b0 + warp; row < rend; row += nwarps) sum_ln_row<NZ>(x, part, M, row, lane, bi, ga, be, xb);
+  }
+};
+
+template <typename Epi, typename = void>
+struct swap_epi_has_finish { static constexpr bool value = false; };
+template <typename Epi>
+struct swap_epi_has_finish<Epi, decltype((void)Epi::kHasFinish)> { static constexpr bool value = Epi::kHasFinish; };
+
 // self-attention in_proj: f in [0,512) -> q, [512,1024) -> K cache row st->step, [1024,1536) -> V cache
 template <typename Elem>
 struct SwapQKV {
@@ -153,7 +209,7 @@ template <int BNB, bool kLN, typename Epi, int KSPLIT = 1>
 __global__ void __launch_bounds__(swap_threads(BNB, kLN), (kLN && BNB > 32) ? 1 : 2)
 gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CUtensorMap tm_x,
                  const __grid_constant__ CUtensorMap tm_w3, const __grid_constant__ CUtensorMap tm_x3, int whole_k,
-                 int M, int K, int stages, Epi epi, const __grid_constant__ SwapLNParams ln, const DecState* st) {
+                 int kgrp, int M, int K, int stages, Epi epi, const __grid_constant__ SwapLNParams ln, const DecState* st) {
   static_assert(BNB == 32 || BNB == 64 || BNB == 128, "BNB");
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -191,7 +247,9 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
     if (ptx::elect_one()) {
       ptx::prefetch_tensormap(&tm_w);
       ptx::prefetch_tensormap(&tm_x);
-      for (int s = 0; s < stages; ++s) { ptx::mbar_init(&full[s], 1); ptx::mbar_init(&empty[s], 1); }
+      // grouped copies: a ring slot holds kgrp k-blocks and is released by every issuer's last k-block of the group
+      const uint32_t empty_cnt = kgrp > 1 ? (uint32_t)kIssuers : 1u;
+      for (int s = 0; s < stages; ++s) { ptx::mbar_init(&full[s], 1); ptx::mbar_init(&empty[s], empty_cnt); }
       ptx::mbar_init(tmem_full, n_acc);  // one arrival per MMA issuer
       ptx::fence_barrier_init();
       // the weights do not depend on the previous kernel of the step: request the first ring of weight tiles now,
@@ -208,6 +266,15 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
           ptx::mbar_expect_tx(&full[hf], (kSwapWholeKB / 2) * kWBytes);
           ptx::tma_load_3d_hint(smem_w + (size_t)hf * (kSwapWholeKB / 2) * kWBytes, &tm_w3, &full[hf], 0, f0,
                                 kb0 + hf * (kSwapWholeKB / 2), keep);
+        }
+      } else if (kgrp > 1) {
+        // kgrp k-blocks per copy (3-D views, box depth kgrp): the TMA unit's throughput is ~2 x copy size / 650 cycles,
+        // so 16 KB per-k-block boxes kept the K = 2048 projection and the 128-row tiles waiting for their operands
+        ptx::prefetch_tensormap(&tm_w3);
+        ptx::prefetch_tensormap(&tm_x3);
+        for (int g = 0; g < n_pre / kgrp; ++g) {
+          ptx::mbar_expect_tx(&full[g], kgrp * (kWBytes + kXBytes));
+          ptx::tma_load_3d_hint(smem_w + (size_t)g * kgrp * kWBytes, &tm_w3, &full[g], 0, f0, kb0 + g * kgrp, keep);
         }
       } else {
         for (int kb = 0; kb < n_pre; ++kb) {
@@ -233,6 +300,9 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
       if (whole_k) {
         ptx::mbar_expect_tx(&full[2], kSwapWholeKB * kXBytes);
         ptx::tma_load_3d(smem_x, &tm_x3, &full[2], 0, b0, kb0);
+      } else if (kgrp > 1) {
+        for (int g = 0; g < n_pre / kgrp; ++g)
+          ptx::tma_load_3d(smem_x + (size_t)g * kgrp * kXBytes, &tm_x3, &full[g], 0, b0, kb0 + g * kgrp);
       } else {
         for (int kb = 0; kb < n_pre; ++kb)
           ptx::tma_load_2d(smem_x + (size_t)kb * kXBytes, &tm_x, &full[kb], (kb0 + kb) * kSwapBK, b0);
@@ -247,6 +317,20 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
   if (warp == 0) {
     if (whole_k) {
       if (!active) { ptx::mbar_wait(&full[0], 0); ptx::mbar_wait(&full[1], 0); ptx::mbar_wait(&full[2], 0); }  // no copy may outlive the CTA
+    } else if (active && kgrp > 1) {
+      const uint64_t keep = ptx::policy_evict_last();
+      const int ng = stages / kgrp;  // ring slots
+      for (int g = n_pre / kgrp; g < num_kb / kgrp; ++g) {
+        const int slot = g % ng;
+        const uint32_t ph = (g / ng) & 1;
+        ptx::mbar_wait(&empty[slot], ph ^ 1);
+        if (ptx::elect_one()) {
+          ptx::mbar_expect_tx(&full[slot], kgrp * (kWBytes + kXBytes));
+          ptx::tma_load_3d_hint(smem_w + (size_t)slot * kgrp * kWBytes, &tm_w3, &full[slot], 0, f0, kb0 + g * kgrp, keep);
+          ptx::tma_load_3d(smem_x + (size_t)slot * kgrp * kXBytes, &tm_x3, &full[slot], 0, b0, kb0 + g * kgrp);
+        }
+        __syncwarp();
+      }
     } else if (active) {
       const uint64_t keep = ptx::policy_evict_last();
       for (int kb = n_pre; kb < num_kb; ++kb) {
@@ -261,7 +345,7 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
         __syncwarp();
       }
     } else {
-      for (int kb = 0; kb < n_pre; ++kb) ptx::mbar_wait(&full[kb], 0);  // no copy may outlive the CTA
+      for (int kb = 0; kb < n_pre / (kgrp > 1 ? kgrp : 1); ++kb) ptx::mbar_wait(&full[kb], 0);  // no copy may outlive the CTA
     }
     __syncwarp();
     if (kLN) { ptx::cluster_wait(); ptx::cluster_arrive(); ptx::cluster_wait(); }
@@ -273,10 +357,12 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
       const uint32_t acc = tmem_base + (uint32_t)(first * BNB);
       const uint32_t w_lo0 = ptx::umma_desc_lo(ptx::smem_u32(smem_w)), x_lo0 = ptx::umma_desc_lo(ptx::smem_u32(smem_x));
       if (whole_k) ptx::mbar_wait(&full[2], 0);  // the activations
+      const int ng = kgrp > 1 ? stages / kgrp : 1;
       for (int kb = first; kb < num_kb; kb += kIssuers) {
-        const int s = whole_k ? kb : kb % stages;
-        const uint32_t ph = whole_k ? 0u : (uint32_t)((kb / stages) & 1);
-        ptx::mbar_wait(&full[whole_k ? kb / (kSwapWholeKB / 2) : s], ph);
+        const int grp = kgrp > 1 ? kb / kgrp : 0, slot = grp % ng;  // grouped copies: ring slot of this k-block's group
+        const int s = whole_k ? kb : (kgrp > 1 ? slot * kgrp + kb % kgrp : kb % stages);
+        const uint32_t ph = whole_k ? 0u : (uint32_t)(((kgrp > 1 ? grp / ng : kb / stages)) & 1);
+        ptx::mbar_wait(&full[whole_k ? kb / (kSwapWholeKB / 2) : (kgrp > 1 ? slot : s)], ph);
         ptx::tc_fence_after();
         if (ptx::elect_one()) {
           if (!kLN && trace_cta && kb == 0) reinterpret_cast<long long*>(red)[1] = clock64();  // first tile landed
@@ -285,7 +371,11 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
 #pragma unroll
           for (int k = 0; k < kSwapBK / 16; ++k)  // 16 bf16 = 32 bytes along K inside the swizzle atom
             ptx::umma_f16_lohi(acc, w_lo + k * 2, x_lo + k * 2, idesc, (kb != first || k != 0) ? 1u : 0u);
-          if (!whole_k) ptx::umma_commit(&empty[s]);  // (no ring reuse in a whole-K launch)
+          if (kgrp > 1) {
+            if (kb % kgrp + kIssuers >= kgrp) ptx::umma_commit(&empty[slot]);  // this issuer's last k-block of the group
+          } else if (!whole_k) {
+            ptx::umma_commit(&empty[s]);  // (no ring reuse in a whole-K launch)
+          }
           if (kb + kIssuers >= num_kb) ptx::umma_commit(tmem_full);  // same thread as the MMAs it tracks
           if (!kLN && trace_cta && kb == num_kb - 1) reinterpret_cast<long long*>(red)[2] = clock64();  // all issued
         }
@@ -495,6 +585,9 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
   ptx::tc_fence_before();
   __syncthreads();
   if (warp == 1) ptx::tmem_dealloc(tmem_base, kIssuers * BNB);
+  if constexpr (swap_epi_has_finish<Epi>::value) {
+    if (active) epi.template finish<4>(b0, BNB, M, reinterpret_cast<int*>(red));  // (launched with 4 k-slices)
+  }
 }
 
 }  // namespace capdec

@@ -113,38 +113,7 @@ sum_ln_kernel(float* __restrict__ x, const float* __restrict__ part, const float
   if (done) return;
   const int row = blockIdx.x * 4 + (threadIdx.x >> 5);
   if (row >= M) return;
-  float4 xin[4], pz[NZ][4];
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const int c = i * 128 + lane * 4;
-    xin[i] = *reinterpret_cast<const float4*>(x + (size_t)row * kD + c);
-#pragma unroll
-    for (int z = 0; z < NZ; ++z) pz[z][i] = *reinterpret_cast<const float4*>(part + ((size_t)z * M + row) * kD + c);
-  }
-  float v[16];
-  float s = 0.f;
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    float4 a = xin[i];
-    a.x += bi[i].x; a.y += bi[i].y; a.z += bi[i].z; a.w += bi[i].w;
-#pragma unroll
-    for (int z = 0; z < NZ; ++z) { a.x += pz[z][i].x; a.y += pz[z][i].y; a.z += pz[z][i].z; a.w += pz[z][i].w; }
-    v[4 * i] = a.x; v[4 * i + 1] = a.y; v[4 * i + 2] = a.z; v[4 * i + 3] = a.w;
-    s += (a.x + a.y) + (a.z + a.w);
-  }
-  const float mean = warp_sum(s) * (1.f / kD);
-  float q = 0.f;
-#pragma unroll
-  for (int i = 0; i < 16; ++i) { v[i] -= mean; q = fmaf(v[i], v[i], q); }
-  const float rstd = rsqrtf(warp_sum(q) * (1.f / kD) + 1e-5f);
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const int c = i * 128 + lane * 4;
-    const float r0 = v[4 * i] * rstd * ga[i].x + be[i].x, r1 = v[4 * i + 1] * rstd * ga[i].y + be[i].y;
-    const float r2 = v[4 * i + 2] * rstd * ga[i].z + be[i].z, r3 = v[4 * i + 3] * rstd * ga[i].w + be[i].w;
-    *reinterpret_cast<float4*>(x + (size_t)row * kD + c) = make_float4(r0, r1, r2, r3);
-    store4(xb + (size_t)row * kD + c, r0, r1, r2, r3);
-  }
+  sum_ln_row<NZ>(x, part, M, row, lane, bi, ga, be, xb);
 }
 
 // Warp-level argmax / categorical draw over one row of kVPad logits (entries >= V are -inf).
@@ -255,23 +224,29 @@ head_kernel(DecState* st, const CallParams* cp, const float* __restrict__ logits
 // Fused vocabulary projection + pick + next-step embedding (SURVEY K11+K12+K13+K2): logits never
 // round-trip to HBM and the step needs no separate embedding kernel.
 // wT: fc_out.weight transposed and padded, [512][kVPad] fp32; x: [M,512] fp32 residual stream.
-// The 256 KB of wT stream through shared memory in 64-row slabs (cp.async); six of the eight slabs are requested
+// The 256 KB of wT stream through shared memory in 64-row slabs (cp.async); BUFS of the eight slabs are requested
 // before the dependency wait (the weights do not depend on the step), so that after the wait a warp only waits
-// for its x row.  Lane l accumulates vocabulary entries 4l..4l+3 of its warp's row.
-constexpr int kVhSlab = 64, kVhBufs = 6;
-__host__ __device__ constexpr int vh_smem_bytes(int rows) { return rows * kD * 4 + kVhBufs * kVhSlab * kVPad * 4; }
+// for its x rows.  Lane l accumulates vocabulary entries 4l..4l+3 of each of its warp's RW rows.
+constexpr int kVhSlab = 64, kVhWarps = 4;
+__host__ __device__ constexpr int vh_smem_bytes(int rows, int bufs) { return rows * kD * 4 + bufs * kVhSlab * kVPad * 4; }
 
-// R = rows per CTA = warps per CTA (one row per warp: the per-row work, 2048 FMA per lane, is the critical path
-// at small batch, so small batches use R = 4 and many CTAs, large batches R = 16 to re-stream wT less often).
-template <int R>
-__global__ void __launch_bounds__(R * 32)
+// 4 warps per CTA, RW rows per warp (R = 4 RW rows per CTA).  Every k step reads one 512-byte weight row per warp
+// from shared memory (4 wavefronts) whatever RW is, so one row per warp is bound by shared-memory bandwidth once
+// many rows share an SM (measured: 16 warps x 1 row, 57 us at 3072 rows); RW rows per warp reuse the weight vector
+// RW times (4 + RW/4 wavefronts per k for 4 RW FMA instructions).  At small batch the per-row chain of 512
+// dependent steps is the critical path instead, so small batches keep RW = 1 and many CTAs.
+// The accumulation order per logit (k ascending, one fmaf chain) does not depend on RW.
+template <int RW, int BUFS>
+__global__ void __launch_bounds__(kVhWarps * 32)
 vocab_head_kernel(DecState* st, const CallParams* cp, float* __restrict__ x, const float* __restrict__ wT,
                   const float* __restrict__ bias, unsigned char* fin, int M, int V, const float* __restrict__ emb,
                   const float* __restrict__ pe, bf16* __restrict__ xb) {
-  constexpr int kThreads = R * 32;
+  constexpr int kThreads = kVhWarps * 32;
+  constexpr int R = kVhWarps * RW;
+  static_assert(BUFS >= 2 && BUFS <= 6, "BUFS");
   extern __shared__ __align__(16) uint8_t vh_smem[];
   float* xs = reinterpret_cast<float*>(vh_smem);   // [R][512]
-  float* ws = xs + R * kD;                         // [3][64][128]
+  float* ws = xs + R * kD;                         // [BUFS][64][128]
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   auto load_slab = [&](int slab, int buf) {  // 64 x 128 floats = 2048 float4
     const float4* src = reinterpret_cast<const float4*>(wT + (size_t)slab * kVhSlab * kVPad);
@@ -285,7 +260,7 @@ vocab_head_kernel(DecState* st, const CallParams* cp, float* __restrict__ x, con
   };
   // the weights do not depend on the previous kernel: start streaming them before the dependency wait
 #pragma unroll
-  for (int b = 0; b < kVhBufs; ++b) {
+  for (int b = 0; b < BUFS; ++b) {
     load_slab(b, b);
     asm volatile("cp.async.commit_group;" ::: "memory");
   }
@@ -312,72 +287,81 @@ vocab_head_kernel(DecState* st, const CallParams* cp, float* __restrict__ x, con
     if (r0 + r < M) v = *reinterpret_cast<const float4*>(x + (size_t)(r0 + r) * kD + c * 4);
     reinterpret_cast<float4*>(xs)[i] = v;
   }
-  float acc[4] = {0.f, 0.f, 0.f, 0.f};
-  const float* xr = xs + warp * kD;
+  float acc[RW][4];
+#pragma unroll
+  for (int j = 0; j < RW; ++j) { acc[j][0] = 0.f; acc[j][1] = 0.f; acc[j][2] = 0.f; acc[j][3] = 0.f; }
+  const float* xr = xs + warp * RW * kD;
   constexpr int kSlabs = kD / kVhSlab;
-  static_assert(kVhBufs == 6, "the wait_group immediate below is kVhBufs - 1");
   for (int sl = 0; sl < kSlabs; ++sl) {
-    // groups committed so far: kVhBufs + sl (one per iteration, possibly empty); slabs 0..sl are needed
-    asm volatile("cp.async.wait_group 5;" ::: "memory");
+    // groups committed so far: BUFS + sl (one per iteration, possibly empty); slabs 0..sl are needed
+    asm volatile("cp.async.wait_group %0;" ::"n"(BUFS - 1) : "memory");
     __syncthreads();
-    const float* wb = ws + (sl % kVhBufs) * kVhSlab * kVPad + lane * 4;
-#pragma unroll 4
+    const float* wb = ws + (sl % BUFS) * kVhSlab * kVPad + lane * 4;
+#pragma unroll 2
     for (int k = 0; k < kVhSlab; k += 4) {
-      const float4 a = *reinterpret_cast<const float4*>(xr + sl * kVhSlab + k);
-      const float av[4] = {a.x, a.y, a.z, a.w};
+      float av[RW][4];
+#pragma unroll
+      for (int j = 0; j < RW; ++j) {
+        const float4 a = *reinterpret_cast<const float4*>(xr + j * kD + sl * kVhSlab + k);
+        av[j][0] = a.x; av[j][1] = a.y; av[j][2] = a.z; av[j][3] = a.w;
+      }
 #pragma unroll
       for (int kk = 0; kk < 4; ++kk) {
         const float4 w = *reinterpret_cast<const float4*>(wb + (k + kk) * kVPad);
-        acc[0] = fmaf(av[kk], w.x, acc[0]); acc[1] = fmaf(av[kk], w.y, acc[1]);
-        acc[2] = fmaf(av[kk], w.z, acc[2]); acc[3] = fmaf(av[kk], w.w, acc[3]);
+#pragma unroll
+        for (int j = 0; j < RW; ++j) {
+          acc[j][0] = fmaf(av[j][kk], w.x, acc[j][0]); acc[j][1] = fmaf(av[j][kk], w.y, acc[j][1]);
+          acc[j][2] = fmaf(av[j][kk], w.z, acc[j][2]); acc[j][3] = fmaf(av[j][kk], w.w, acc[j][3]);
+        }
       }
     }
-    __syncthreads();  // every warp is done with buffer (sl % kVhBufs): refill it
-    if (sl + kVhBufs < kSlabs) load_slab(sl + kVhBufs, sl % kVhBufs);
+    __syncthreads();  // every warp is done with buffer (sl % BUFS): refill it
+    if (sl + BUFS < kSlabs) load_slab(sl + BUFS, sl % BUFS);
     asm volatile("cp.async.commit_group;" ::: "memory");
   }
-  {
-    const int m = r0 + warp;
+#pragma unroll
+  for (int j = 0; j < RW; ++j) {
+    const int m = r0 + warp * RW + j;
     if (m < M) {  // warp-uniform
-    float l[4] = {acc[0] + bv.x, acc[1] + bv.y, acc[2] + bv.z, acc[3] + bv.w};
+      float l[4] = {acc[j][0] + bv.x, acc[j][1] + bv.y, acc[j][2] + bv.z, acc[j][3] + bv.w};
 #pragma unroll
-    for (int i = 0; i < 4; ++i) if (lane * 4 + i >= V) l[i] = -INFINITY;
-    if (p.logits_dump != nullptr) {
-      float* d = p.logits_dump + ((size_t)m * (p.max_len - 1) + n) * V;
+      for (int i = 0; i < 4; ++i) if (lane * 4 + i >= V) l[i] = -INFINITY;
+      if (p.logits_dump != nullptr) {
+        float* d = p.logits_dump + ((size_t)m * (p.max_len - 1) + n) * V;
 #pragma unroll
-      for (int i = 0; i < 4; ++i) if (lane * 4 + i < V) d[lane * 4 + i] = l[i];
-    }
-    const bool sample = (m % p.group) < p.n_sample;
-    const float u = sample ? philox_uniform(p.seed, p.seq_id_base + (unsigned long long)m, n) : 0.f;
-    float lp;
-    const int tok = warp_pick(l, lane, sample, u, V, &lp);
-    if (lane == 0) {
-      p.ids[(size_t)m * p.max_len + n + 1] = tok;
-      const bool ended = tok == p.end_token;
-      if (sample) {
-        const bool was = fin[m] != 0;
-        if (p.logp != nullptr) p.logp[(size_t)m * (p.max_len - 1) + n] = was ? 0.f : lp;  // scst:239
-        if (ended) fin[m] = 1;
-        if (was || ended) atomicAdd(&st->cnt_finished, 1);
-      } else if (ended) {
-        atomicAdd(&st->cnt_end_now, 1);
+        for (int i = 0; i < 4; ++i) if (lane * 4 + i < V) d[lane * 4 + i] = l[i];
       }
-    }
-    // embedding of the token just picked = input of the next step (vit:166-169); pe row n+1 exists iff a next step does
-    if (n + 1 < p.max_len - 1) {
-      const float sc = 22.627416997969522f;
-#pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const int c = i * 128 + lane * 4;
-        const float4 e4 = __ldg(reinterpret_cast<const float4*>(emb + (size_t)tok * kD + c));
-        const float4 p4 = pe4[i];
-        float4 o;
-        o.x = __fadd_rn(__fmul_rn(e4.x, sc), p4.x); o.y = __fadd_rn(__fmul_rn(e4.y, sc), p4.y);
-        o.z = __fadd_rn(__fmul_rn(e4.z, sc), p4.z); o.w = __fadd_rn(__fmul_rn(e4.w, sc), p4.w);
-        *reinterpret_cast<float4*>(x + (size_t)m * kD + c) = o;
-        store4(xb + (size_t)m * kD + c, o.x, o.y, o.z, o.w);
+      const bool sample = (m % p.group) < p.n_sample;
+      const float u = sample ? philox_uniform(p.seed, p.seq_id_base + (unsigned long long)m, n) : 0.f;
+      float lp;
+      const int tok = warp_pick(l, lane, sample, u, V, &lp);
+      if (lane == 0) {
+        p.ids[(size_t)m * p.max_len + n + 1] = tok;
+        const bool ended = tok == p.end_token;
+        if (sample) {
+          const bool was = fin[m] != 0;
+          if (p.logp != nullptr) p.logp[(size_t)m * (p.max_len - 1) + n] = was ? 0.f : lp;  // scst:239
+          if (ended) fin[m] = 1;
+          if (was || ended) atomicAdd(&st->cnt_finished, 1);
+        } else if (ended) {
+          atomicAdd(&st->cnt_end_now, 1);
+        }
       }
-    }
+      // embedding of the token just picked = input of the next step (vit:166-169); pe row n+1 exists iff a next step does
+      if (n + 1 < p.max_len - 1) {
+        const float sc = 22.627416997969522f;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int c = i * 128 + lane * 4;
+          const float4 e4 = __ldg(reinterpret_cast<const float4*>(emb + (size_t)tok * kD + c));
+          const float4 p4 = pe4[i];
+          float4 o;
+          o.x = __fadd_rn(__fmul_rn(e4.x, sc), p4.x); o.y = __fadd_rn(__fmul_rn(e4.y, sc), p4.y);
+          o.z = __fadd_rn(__fmul_rn(e4.z, sc), p4.z); o.w = __fadd_rn(__fmul_rn(e4.w, sc), p4.w);
+          *reinterpret_cast<float4*>(x + (size_t)m * kD + c) = o;
+          store4(xb + (size_t)m * kD + c, o.x, o.y, o.z, o.w);
+        }
+      }
     }
   }
   __syncthreads();

@@ -293,6 +293,67 @@ def test_v2_layernorm_gemm_split_k(dev, monkeypatch, ksplit):
     eng.close()
 
 
+@pytest.mark.parametrize("rw", [1, 2, 4, 6])
+def test_v2_vocab_head_rows_per_warp(dev, monkeypatch, rw):
+    """Fused vocabulary head with 1/2/4/6 rows per warp (4/8/16/24 rows per CTA, ragged last CTA): logits,
+    argmax, sampled ids and log-probs against the oracle; the per-logit accumulation order does not depend on rw,
+    so every variant must return bit-identical logits."""
+    dec = small_decoder(layers=2, end_bias=1.0)
+    w = torch_port.weights_to_numpy(dec)
+    mem = torch_port.synthetic_memory(35, 49)
+    outs = []
+    for r in (1, rw):
+        monkeypatch.setenv("CAPDEC_HEAD_RW", str(r))
+        eng = make_engine(dec.to(dev), "bf16", step_impl="v2", max_images=35, max_group=2, max_mem=49, max_len=10)
+        out = eng.decode_from_memory(mem.to(dev), START, END, max_len=10, group=2, n_sample=1, seed=9, return_logits=True)
+        check_rollout(out, w, mem.numpy(), 2, 1, TOL["bf16"], seed=9)
+        outs.append((out.ids.cpu(), out.logits.cpu(), out.logp.cpu()))
+        eng.close()
+    assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1]) and torch.equal(outs[0][2], outs[1][2])
+
+
+@pytest.mark.parametrize("bnb", [32, 64, 128])
+def test_v2_grouped_k_copies(dev, monkeypatch, bnb):
+    """CAPDEC_KGROUP=1: several k-blocks per TMA copy (3-D views, ring slots of 2 or 4 k-blocks released by every
+    MMA issuer) where whole-K copies do not apply: the K = 2048 LayerNorm GEMM at every tile width and the K = 512
+    GEMMs of 128-row tiles.  Same products in the same order as the per-k-block ring: identical results."""
+    monkeypatch.setenv("CAPDEC_BNB", str(bnb))
+    monkeypatch.setenv("CAPDEC_NO_FFN2_SPLIT", "1")
+    dec = small_decoder(layers=2, end_bias=1.0)
+    w = torch_port.weights_to_numpy(dec)
+    mem = torch_port.synthetic_memory(75, 49)
+    outs = []
+    for on in ("0", "1"):
+        monkeypatch.setenv("CAPDEC_KGROUP", on)
+        eng = make_engine(dec.to(dev), "bf16", step_impl="v2", max_images=75, max_group=2, max_mem=49, max_len=10)
+        out = eng.decode_from_memory(mem.to(dev), START, END, max_len=10, group=2, n_sample=1, seed=3, return_logits=True)
+        check_rollout(out, w, mem.numpy(), 2, 1, TOL["bf16"], seed=3)
+        outs.append((out.ids.cpu(), out.logits.cpu()))
+        eng.close()
+    assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
+
+
+@pytest.mark.parametrize("n_img", [5, 130])
+def test_v2_ffn2_split_k_closes_itself(dev, monkeypatch, n_img):
+    """Small batches run FFN2 as 4 k-slices whose last CTA per row tile (ticket counter) sums the slices and applies
+    residual + LayerNorm (SwapPartialLN) when CAPDEC_FFN2_FUSE=1; the default is the separate sum_ln launch.  Same arithmetic
+    (sum_ln_row) on the same partial products: identical results, ragged last row tile included."""
+    dec = small_decoder(layers=2, end_bias=1.0)
+    w = torch_port.weights_to_numpy(dec)
+    mem = torch_port.synthetic_memory(n_img, 49)
+    outs = []
+    for on in ("0", "1"):
+        monkeypatch.setenv("CAPDEC_FFN2_FUSE", on)
+        eng = make_engine(dec.to(dev), "bf16", step_impl="v2", max_images=n_img, max_group=2, max_mem=49, max_len=12)
+        for seed in (3, 4):  # the second rollout finds the ticket counters reset by the first
+            out = eng.decode_from_memory(mem.to(dev), START, END, max_len=12, group=2, n_sample=1, seed=seed, return_logits=True)
+            check_rollout(out, w, mem.numpy(), 2, 1, TOL["bf16"], seed=seed)
+        outs.append((out.ids.cpu(), out.logits.cpu(), eng.launch_count()))
+        eng.close()
+    assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
+    assert outs[1][2] < outs[0][2]  # one launch fewer per layer and step
+
+
 def test_v2_cross_attention_many_rollouts_per_image(dev):
     """group > 16: the cross-attention CTA walks several 16-row query tiles over one staged K/V tile."""
     dec = small_decoder(layers=2)

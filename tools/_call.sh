@@ -1,4 +1,4 @@
-python -m torch.distributed.run --nnodes=1 --nproc-per-node 4 --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus 4 --steps 10 --warmup 3 > gpurun_out/r1c_bench_cfg2_n4.json 2> gpurun_out/r1c_bench_cfg2_n4.err; echo "n4 cfg2 exit $?"; tail -c 600 gpurun_out/r1c_bench_cfg2_n4.json
-python -m torch.distributed.run --nnodes=1 --nproc-per-node 4 --master-addr 127.0.0.1 --master-port 29512 bench.py --gpus 4 --steps 5 --warmup 3 --workload cfg3 > gpurun_out/r1c_bench_cfg3_n4.json 2> gpurun_out/r1c_bench_cfg3_n4.err; echo "n4 cfg3 exit $?"
-python -m torch.distributed.run --nnodes=1 --nproc-per-node 4 --master-addr 127.0.0.1 --master-port 29513 bench.py --gpus 4 --steps 3 --warmup 3 --impl reference > gpurun_out/r1c_ref_n4.json 2> gpurun_out/r1c_ref_n4.err; echo "n4 ref exit $?"; cat gpurun_out/r1c_ref_n4.json | cut -c1-400
-python tools/show_bench.py gpurun_out/r1c_bench_cfg2_n4.json gpurun_out/r1c_bench_cfg3_n4.json | grep value
+timeout 200 python tools/step_time.py cfg2 --variants v2 --reps 7 2>&1 | grep -v Warn | tail -1
+CAPDEC_NO_FFN2_FUSE=1 timeout 200 python tools/step_time.py cfg2 --variants v2 --reps 7 2>&1 | tail -1 | sed 's/^/nofuse /'
+timeout 200 python tools/step_time.py cfg2 --variants v2 --reps 7 --images 128 2>&1 | tail -1 | sed 's/^/128img /'
+timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -5
