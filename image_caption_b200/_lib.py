@@ -19,7 +19,7 @@ EXPORTS = (
     "capdec_abi_version", "capdec_last_error", "capdec_create", "capdec_destroy", "capdec_set_weights",
     "capdec_prefill", "capdec_decode", "capdec_generate_host", "capdec_sample_logits", "capdec_launch_count",
     "capdec_debug_gemm", "capdec_debug_cross_kv", "capdec_profile_enable", "capdec_profile_report",
-    "capdec_beam_search",
+    "capdec_beam_search", "capdec_set_memory_projection", "capdec_prefill_tokens",
 )
 
 
@@ -92,6 +92,9 @@ def load() -> C.CDLL:
     lib.capdec_sample_logits.argtypes = [H, C.c_void_p, C.c_int32, C.c_int32, C.c_uint64, C.c_uint64, C.c_int32,
                                          C.c_void_p, C.c_void_p, C.c_void_p]
     lib.capdec_beam_search.argtypes = [H, C.POINTER(BeamArgs), C.c_void_p]
+    lib.capdec_set_memory_projection.argtypes = [H, C.c_void_p, C.c_void_p, C.c_int32, C.POINTER(C.c_void_p),
+                                                 C.POINTER(C.c_void_p), C.c_void_p]
+    lib.capdec_prefill_tokens.argtypes = [H, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_void_p]
     lib.capdec_launch_count.restype = C.c_int64
     lib.capdec_launch_count.argtypes = [H]
     lib.capdec_debug_gemm.argtypes = [H, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32,

@@ -706,6 +706,19 @@ extern "C" int capdec_set_weights(capdec_handle h, const capdec_weights* w, void
 }
 
 // ------------------------------------------------------------------ prefill
+static int finish_prefill(capdec_handle h, int n_images, int mem_len) {
+  h->launches += h->launches_this_enqueue;
+  if (h->fast && (h->n_images != n_images || h->mem_len != mem_len || !h->prefilled_once)) {
+    if (mem_len > 256) return fail(h, CAPDEC_ERR_CAPACITY, "memory length %d > 256 is not supported by the TMA cross-attention", mem_len);
+    TRY(make_map(h, &h->tm_ckv, h->cross_kv, h->cfg.n_layer * 2 * n_images * kH * mem_len, kHD, ca_key_rows(mem_len)));
+    h->prefilled_once = true;
+  }
+  h->n_images = n_images;
+  h->mem_len = mem_len;
+  h->prefilled = true;
+  return CAPDEC_OK;
+}
+
 extern "C" int capdec_prefill(capdec_handle h, const float* memory, int32_t n_images, int32_t mem_len, void* stream) {
   if (!h || !memory) return fail(h, CAPDEC_ERR_INVALID, "null argument");
   if (!h->have_weights) return fail(h, CAPDEC_ERR_STATE, "capdec_prefill before capdec_set_weights");
@@ -732,16 +745,84 @@ extern "C" int capdec_prefill(capdec_handle h, const float* memory, int32_t n_im
   if (h->use_umma) TRY(make_map(h, &tm_mem, h->mem_b, M, kD, kUmmaBM));
   set_tag(h, "prefill_gemm_cross_kv", gemm_bytes(M, N, kD, h->esz, h->esz, h->esz));
   TRY(gemm(h, s, h->bf16 ? h->mem_b : (const void*)memory, &tm_mem, h->w_ckv, &h->m_ckv, M, N, kD, e32, e16, nullptr));
-  h->launches += h->launches_this_enqueue;
-  if (h->fast && (h->n_images != n_images || h->mem_len != mem_len || !h->prefilled_once)) {
-    if (mem_len > 256) return fail(h, CAPDEC_ERR_CAPACITY, "memory length %d > 256 is not supported by the TMA cross-attention", mem_len);
-    TRY(make_map(h, &h->tm_ckv, h->cross_kv, h->cfg.n_layer * 2 * n_images * kH * mem_len, kHD, ca_key_rows(mem_len)));
-    h->prefilled_once = true;
+  return finish_prefill(h, n_images, mem_len);
+}
+
+// ------------------------------------------------------------------ encoder hand-off
+// memory = tokens * P^T + pb is only ever used as the operand of the cross K/V projection, so
+//   K|V = memory * Wkv^T + bkv = tokens * (Wkv P)^T + (Wkv pb + bkv):
+// the product Wkv P ([L*1024, in_dim]) is formed once per weight update in fp32, and prefill runs ONE GEMM from the
+// encoder's tokens without materialising the fp32 memory tensor (vit:98) or running the 768 -> 512 projection.
+extern "C" int capdec_set_memory_projection(capdec_handle h, const float* proj_w, const float* proj_b, int32_t in_dim,
+                                            const float* const* cross_in_w, const float* const* cross_in_b, void* stream) {
+  if (!h || !proj_w || !proj_b || !cross_in_w || !cross_in_b) return fail(h, CAPDEC_ERR_INVALID, "null argument");
+  if (in_dim < kUmmaBK || in_dim % kUmmaBK != 0 || in_dim > 4096)
+    return fail(h, CAPDEC_ERR_INVALID, "projection input width %d must be a multiple of %d in [%d, 4096]", in_dim, kUmmaBK, kUmmaBK);
+  cudaStream_t s = (cudaStream_t)stream;
+  CUDA_TRY(h, cudaSetDevice(h->device));
+  const int L = h->cfg.n_layer, N = L * 2 * kD;
+  if (h->proj_dim != in_dim) {  // (buffers of an earlier width stay allocated until destroy)
+    TRY(dev_alloc_bytes(h, &h->w_ckv_f, (size_t)N * in_dim * h->esz));
+    TRY(dev_alloc(h, &h->b_ckv_f, (size_t)N));
+    TRY(dev_alloc(h, &h->fold_tmp, (size_t)in_dim * kD + (size_t)N * in_dim));
+    TRY(dev_alloc_bytes(h, &h->tok_b, (size_t)h->cfg.max_images * h->cfg.max_mem * in_dim * h->esz));
+    h->proj_dim = in_dim;
   }
-  h->n_images = n_images;
-  h->mem_len = mem_len;
-  h->prefilled = true;
+  float* pt = h->fold_tmp;                          // [in_dim][512] = proj_w^T
+  float* prod = h->fold_tmp + (size_t)in_dim * kD;  // [L*1024][in_dim]
+  transpose_pad_kernel<<<(in_dim * kD + 255) / 256, 256, 0, s>>>(proj_w, pt, kD, in_dim, kD);
+  CUDA_TRY(h, cudaGetLastError());
+  h->launches++;
+  h->launches_this_enqueue = 0;
+  for (int l = 0; l < L; ++l) {
+    if (!cross_in_w[l] || !cross_in_b[l]) return fail(h, CAPDEC_ERR_INVALID, "null cross-attention weight pointer in layer %d", l);
+    const float* wkv = cross_in_w[l] + (size_t)kD * kD;  // rows [512,1536) of in_proj_weight: K then V
+    EpiLinear<float, false> ew{prod + (size_t)l * 2 * kD * in_dim, nullptr, in_dim};
+    TRY((launch_simt<float, float, EpiLinear<float, false>>(h, s, wkv, kD, pt, kD, 2 * kD, in_dim, kD, ew, nullptr)));
+    EpiLinear<float, false> eb{h->b_ckv_f + (size_t)l * 2 * kD, cross_in_b[l] + kD, 2 * kD};
+    TRY((launch_simt<float, float, EpiLinear<float, false>>(h, s, proj_b, kD, wkv, kD, 1, 2 * kD, kD, eb, nullptr)));
+  }
+  h->launches += h->launches_this_enqueue;
+  TRY(pack_matrix(h, s, prod, h->w_ckv_f, N, in_dim, N));
+  if (h->use_umma) {
+    const int bns[3] = {32, 64, 128};
+    for (int i = 0; i < 3; ++i) TRY(make_map(h, &h->m_ckv_f.bn[i], h->w_ckv_f, N, in_dim, bns[i]));
+  }
   return CAPDEC_OK;
+}
+
+extern "C" int capdec_prefill_tokens(capdec_handle h, const float* tokens, int32_t n_images, int32_t tokens_per_image,
+                                     int32_t first_token, int32_t mem_len, void* stream) {
+  if (!h || !tokens) return fail(h, CAPDEC_ERR_INVALID, "null argument");
+  if (!h->have_weights) return fail(h, CAPDEC_ERR_STATE, "capdec_prefill_tokens before capdec_set_weights");
+  if (h->proj_dim == 0) return fail(h, CAPDEC_ERR_STATE, "capdec_prefill_tokens before capdec_set_memory_projection");
+  if (n_images < 1 || mem_len < 1 || first_token < 0 || first_token + mem_len > tokens_per_image)
+    return fail(h, CAPDEC_ERR_INVALID, "token range [%d, %d) outside the %d tokens of an image", first_token, first_token + mem_len,
+                tokens_per_image);
+  if (n_images > h->cfg.max_images || mem_len > h->cfg.max_mem)
+    return fail(h, CAPDEC_ERR_CAPACITY, "prefill of %d images x %d exceeds capacity %d x %d", n_images, mem_len,
+                h->cfg.max_images, h->cfg.max_mem);
+  cudaStream_t s = (cudaStream_t)stream;
+  CUDA_TRY(h, cudaSetDevice(h->device));
+  h->prefilled = false;
+  h->launches_this_enqueue = 0;
+  const int E = h->proj_dim, M = n_images * mem_len, N = h->cfg.n_layer * 2 * kD;
+  {
+    const size_t n4 = (size_t)M * E / 4;
+    set_tag(h, "prefill_gather_tokens", (double)M * E * (4 + h->esz));
+    ProfScope ps(h, s);
+    if (h->bf16) gather_tokens_kernel<bf16><<<(unsigned)((n4 + 255) / 256), 256, 0, s>>>(tokens, (bf16*)h->tok_b, n_images, tokens_per_image, first_token, mem_len, E / 4);
+    else gather_tokens_kernel<float><<<(unsigned)((n4 + 255) / 256), 256, 0, s>>>(tokens, (float*)h->tok_b, n_images, tokens_per_image, first_token, mem_len, E / 4);
+    CUDA_TRY(h, cudaGetLastError());
+    h->launches_this_enqueue++;
+  }
+  EpiCrossKV<float> e32{(float*)h->cross_kv, h->b_ckv_f, n_images, mem_len};
+  EpiCrossKV<bf16> e16{(bf16*)h->cross_kv, h->b_ckv_f, n_images, mem_len};
+  CUtensorMap tm_tok;
+  if (h->use_umma) TRY(make_map(h, &tm_tok, h->tok_b, M, E, kUmmaBM));
+  set_tag(h, "prefill_gemm_cross_kv", gemm_bytes(M, N, E, h->esz, h->esz, h->esz));
+  TRY(gemm(h, s, h->tok_b, &tm_tok, h->w_ckv_f, &h->m_ckv_f, M, N, E, e32, e16, nullptr));
+  return finish_prefill(h, n_images, mem_len);
 }
 
 // ------------------------------------------------------------------ one decode step

@@ -60,6 +60,14 @@ struct capdec_engine {
   float *emb = nullptr, *pe = nullptr, *fc_w = nullptr, *fc_b = nullptr;  // fc padded to kVPad rows
   bool have_weights = false;
 
+  // ---- encoder hand-off: the encoder's output projection folded into the cross K/V projection
+  int proj_dim = 0;              // input width of the folded projection (768 for ViT-B/16); 0 = not set
+  void* w_ckv_f = nullptr;       // [L*1024, proj_dim] = w_ckv * proj_w, engine element type
+  float* b_ckv_f = nullptr;      // [L*1024] = w_ckv * proj_b + b_ckv
+  float* fold_tmp = nullptr;     // fp32 scratch: [proj_dim, 512] transposed projection + [L*1024, proj_dim] product
+  void* tok_b = nullptr;         // [max_images*max_mem, proj_dim] gathered tokens (GEMM operand)
+  capdec::WeightMaps m_ckv_f;
+
   // ---- caches
   void *self_k = nullptr, *self_v = nullptr;  // [L][M_max][H][t_pad][64]
   void* cross_kv = nullptr;                   // [L][2][n_images][H][S][64]

@@ -409,6 +409,20 @@ __global__ void convert_kernel(const float* __restrict__ in, Out* __restrict__ o
   store4(out + i * 4, v.x, v.y, v.z, v.w);
 }
 
+// Encoder hand-off: rows first..first+mem_len-1 of every image's [tokens_per_image, dim] fp32 token block
+// (the ViT encoder output minus its class token, vit:95) -> contiguous [n_images*mem_len, dim] GEMM operand.
+template <typename Out>
+__global__ void gather_tokens_kernel(const float* __restrict__ in, Out* __restrict__ out, int n_images, int tokens_per_image,
+                                     int first, int mem_len, int dim4) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (size_t)n_images * mem_len * dim4) return;
+  const int c = (int)(i % dim4);
+  const size_t r = i / dim4;
+  const int img = (int)(r / mem_len), s = (int)(r % mem_len);
+  const float4 v = __ldg(reinterpret_cast<const float4*>(in) + ((size_t)img * tokens_per_image + first + s) * dim4 + c);
+  store4(out + i * 4, v.x, v.y, v.z, v.w);
+}
+
 // pack rows [r0, r0+rows) of a [*, cols] fp32 matrix into out (Out), optional zero row padding
 template <typename Out>
 __global__ void pack_rows_kernel(const float* __restrict__ in, Out* __restrict__ out, int rows, int cols, int rows_out) {

@@ -48,6 +48,15 @@ def _stream_ptr(device: torch.device) -> int:
     return torch.cuda.current_stream(device).cuda_stream
 
 
+def vit_encoder_tokens(encoder: torch.nn.Module, images: torch.Tensor) -> torch.Tensor:
+    """``VisionTransformerEncoder.forward`` (models/vit_transformer_model.py:70-100) up to, not including, the
+    class-token drop and the output projection: (B, 1 + patches, 768)."""
+    vit = encoder.vit
+    x = vit._process_input(images)                                          # vit:84
+    x = torch.cat([vit.class_token.expand(x.shape[0], -1, -1), x], dim=1)   # vit:88-89
+    return vit.encoder(x)                                                   # vit:92
+
+
 class CaptionDecodeEngine:
     def __init__(self, decoder: torch.nn.Module, precision: str = "bf16", max_images: int = 64,
                  max_group: int = 1, max_mem: int = 196, max_len: int = 50, use_graph: bool = True,
@@ -94,6 +103,7 @@ class CaptionDecodeEngine:
         _lib.check(None, rc)
         self._h = h
         self._weights_sig = None
+        self._proj_sig = None
 
     def close(self) -> None:
         if getattr(self, "_h", None) is not None and self._h.value:
@@ -151,6 +161,31 @@ class CaptionDecodeEngine:
         self._keep = keep  # released on the next repack; the pack kernels are stream-ordered before that
         self._weights_sig = sig
 
+    def sync_projection(self, projection: torch.nn.Linear) -> None:
+        """Fold an encoder output projection (``VisionTransformerEncoder.projection``, vit:61) into the cross K/V
+        weights (capdec_set_memory_projection).  Re-done when the projection or the decoder parameters changed."""
+        self.sync_weights()
+        sig = (projection.weight.data_ptr(), projection.weight._version, projection.bias.data_ptr(),
+               projection.bias._version, self._weights_sig)
+        if sig == getattr(self, "_proj_sig", None):
+            return
+        if projection.out_features != self.d_model:
+            raise ValueError(f"projection must map to d_model={self.d_model}, got {projection.out_features}")
+        sd = self.decoder.state_dict()
+        keep = [projection.weight.detach().to(self.device, torch.float32).contiguous(),
+                projection.bias.detach().to(self.device, torch.float32).contiguous()]
+        ws = (C.c_void_p * self.n_layer)()
+        bs = (C.c_void_p * self.n_layer)()
+        for i in range(self.n_layer):
+            w = sd[f"transformer_decoder.layers.{i}.multihead_attn.in_proj_weight"].detach().to(torch.float32).contiguous()
+            b = sd[f"transformer_decoder.layers.{i}.multihead_attn.in_proj_bias"].detach().to(torch.float32).contiguous()
+            keep += [w, b]
+            ws[i], bs[i] = w.data_ptr(), b.data_ptr()
+        _lib.check(self._h, self._lib.capdec_set_memory_projection(
+            self._h, keep[0].data_ptr(), keep[1].data_ptr(), projection.in_features, ws, bs, _stream_ptr(self.device)))
+        self._keep_proj = keep  # released on the next fold; the fold kernels are stream-ordered before that
+        self._proj_sig = sig
+
     # ------------------------------------------------------------------ decode
     def _check_lengths(self, max_len: int) -> None:
         if max_len < 2:
@@ -163,18 +198,32 @@ class CaptionDecodeEngine:
     def decode_from_memory(self, memory: torch.Tensor, start_token: int, end_token: int, max_len: int = 50,
                            group: int = 1, n_sample: int = 0, seed: int = 0, seq_id_base: int = 0,
                            pad_token: int = 0, return_logits: bool = False, trim: bool = True,
-                           early_stop: bool = True) -> Rollout:
+                           early_stop: bool = True, projection: Optional[torch.nn.Linear] = None,
+                           first_token: int = 0) -> Rollout:
         """Decode ``group`` sequences per image of ``memory`` (B, S, 512) float32: rows ``g < n_sample``
         of each group are sampled, the rest greedy.  A CUDA ``memory`` runs on the current stream and
         returns CUDA tensors; a CPU ``memory`` takes the host-buffer entry point
-        (capdec_generate_host) and returns CPU tensors."""
-        if memory.dim() != 3 or memory.shape[2] != self.d_model:
+        (capdec_generate_host) and returns CPU tensors.
+
+        Encoder hand-off: with ``projection`` (the encoder's final ``nn.Linear``, vit:61) ``memory``
+        is the encoder's *un-projected* CUDA token tensor (B, T, in_features); tokens ``first_token ..`` of every
+        image are the memory positions (``first_token=1`` drops the ViT class token, vit:95) and the projection is
+        applied inside the K/V prefill GEMM (capdec_prefill_tokens)."""
+        if projection is not None:
+            if memory.dim() != 3 or memory.shape[2] != projection.in_features or not memory.is_cuda:
+                raise ValueError(f"tokens must be CUDA (B, T, {projection.in_features}), got {tuple(memory.shape)}")
+            if not 0 <= first_token < memory.shape[1]:
+                raise ValueError("first_token outside the token axis")
+        elif memory.dim() != 3 or memory.shape[2] != self.d_model:
             raise ValueError(f"memory must be (B, S, {self.d_model}), got {tuple(memory.shape)}")
         self._check_lengths(max_len)
-        n_images, mem_len = memory.shape[0], memory.shape[1]
+        n_images, mem_len = memory.shape[0], memory.shape[1] - (first_token if projection is not None else 0)
         m = n_images * group
         self._ensure_capacity(n_images, group, mem_len, max_len)
-        self.sync_weights()
+        if projection is not None:
+            self.sync_projection(projection)
+        else:
+            self.sync_weights()
         memory = memory.detach().to(torch.float32).contiguous()
         steps = C.c_int32(0)
         args = _lib.DecodeArgs(group=group, n_sample=n_sample, start_token=start_token, end_token=end_token,
@@ -193,7 +242,11 @@ class CaptionDecodeEngine:
             args.ids_out = ids.data_ptr()
             args.logp_out = logp.data_ptr() if want_logp else None
             args.logits_out = logits.data_ptr() if return_logits else None
-            _lib.check(self._h, self._lib.capdec_prefill(self._h, memory.data_ptr(), n_images, mem_len, stream))
+            if projection is not None:
+                _lib.check(self._h, self._lib.capdec_prefill_tokens(self._h, memory.data_ptr(), n_images, memory.shape[1],
+                                                                    first_token, mem_len, stream))
+            else:
+                _lib.check(self._h, self._lib.capdec_prefill(self._h, memory.data_ptr(), n_images, mem_len, stream))
             _lib.check(self._h, self._lib.capdec_decode(self._h, C.byref(args), stream))
         else:
             if return_logits:
@@ -245,6 +298,46 @@ class CaptionDecodeEngine:
         _lib.check(self._h, self._lib.capdec_beam_search(self._h, C.byref(args), stream))
         return ids, lens, scores
 
+    # ------------------------------------------------------------------ encoder hand-off
+    fuse_encoder_projection = True
+
+    def _encode(self, model: torch.nn.Module, images: torch.Tensor):
+        """``model.encoder(images)`` -- or, for the ViT encoder, its token tensor *before* the class-token drop and
+        the 768 -> 512 projection (vit:80-98), which the engine folds into the K/V prefill.  Returns the keyword
+        arguments of ``decode_from_memory``'s memory input."""
+        enc = model.encoder
+        vit, proj = getattr(enc, "vit", None), getattr(enc, "projection", None)
+        if (self.fuse_encoder_projection and vit is not None and isinstance(proj, torch.nn.Linear)
+                and not torch.is_grad_enabled() and proj.in_features % 64 == 0 and images.is_cuda):
+            # vit:95-98 (class-token drop + projection) happen in the prefill GEMM
+            return dict(memory=vit_encoder_tokens(enc, images), projection=proj, first_token=1)
+        return dict(memory=enc(images))
+
+    def scst_rollouts(self, model: torch.nn.Module, images: torch.Tensor, start_token: int, end_token: int,
+                      max_len: int = 50, n_samples: int = 1, seed: Optional[int] = None):
+        """The two rollouts of one SCST step from ONE encoder pass: ``SCSTLoss.forward`` encodes the batch twice
+        (scst:213 for the sampled rollout, vit:304 inside ``model.generate`` for the greedy baseline).  Returns
+        ``(sample_ids (B, n_samples, L), sample_logp (B, n_samples, L-1), greedy_ids (B, L))``; the sampled and greedy
+        sequences of an image share its cross K/V on the device.  Eval-mode encoder and decoder, no autograd (the
+        caller recomputes the sampled log-probs teacher-forced when it needs gradients, as ``sample_with_log_probs``
+        does)."""
+        with torch.no_grad():
+            was_training = model.training
+            model.eval()
+            try:
+                kw = self._encode(model, images)
+            finally:
+                model.train(was_training)
+            if seed is None:
+                seed = int(torch.randint(0, 2 ** 62, (1,)).item())
+            g = n_samples + 1
+            out = self.decode_from_memory(start_token=start_token, end_token=end_token, max_len=max_len, group=g,
+                                          n_sample=n_samples, seed=seed, **kw)
+        b, width = images.shape[0], out.ids.shape[1]
+        ids = out.ids.view(b, g, width)
+        logp = out.logp.view(b, g, width - 1)
+        return ids[:, :n_samples], logp[:, :n_samples], ids[:, n_samples]
+
     # ------------------------------------------------------------------ reference-facing entry points
     @torch.no_grad()
     def generate(self, model: torch.nn.Module, images: torch.Tensor, start_token: int, end_token: int,
@@ -258,8 +351,8 @@ class CaptionDecodeEngine:
         by the class name."""
         if method == "greedy":
             model.eval()  # vit:298 - a side effect the reference never undoes
-            memory = model.encoder(images)
-            return self.decode_from_memory(memory, start_token, end_token, max_len).ids
+            return self.decode_from_memory(start_token=start_token, end_token=end_token, max_len=max_len,
+                                           **self._encode(model, images)).ids
         if method == "beam_search":
             model.eval()  # vit:329
             is_grid = "grid" in type(model).__name__.lower()
@@ -336,6 +429,15 @@ class CaptionDecodeEngine:
         _lib.check(self._h, self._lib.capdec_debug_cross_kv(self._h, layer, which, out.data_ptr(),
                                                             _stream_ptr(self.device)))
         return out
+
+    def prefill_tokens(self, tokens: torch.Tensor, projection: torch.nn.Linear, first_token: int = 1) -> None:
+        tokens = tokens.detach().to(self.device, torch.float32).contiguous()
+        mem_len = tokens.shape[1] - first_token
+        self._ensure_capacity(tokens.shape[0], 1, mem_len, 2)
+        self.sync_projection(projection)
+        self._keep_mem = tokens
+        _lib.check(self._h, self._lib.capdec_prefill_tokens(self._h, tokens.data_ptr(), tokens.shape[0], tokens.shape[1],
+                                                            first_token, mem_len, _stream_ptr(self.device)))
 
     def prefill(self, memory: torch.Tensor) -> None:
         memory = memory.detach().to(self.device, torch.float32).contiguous()

@@ -138,6 +138,21 @@ int capdec_set_weights(capdec_handle h, const capdec_weights* w, void* cuda_stre
  * cross-attention K and V. */
 int capdec_prefill(capdec_handle h, const float* memory, int32_t n_images, int32_t mem_len, void* cuda_stream);
 
+/* Encoder hand-off.  The ViT encoder ends in `features = self.projection(patch_features)`
+ * (models/vit_transformer_model.py:61,95-98) and the decoder only ever multiplies that memory by the cross-attention
+ * K/V weights, so the projection can be folded into them:  K|V = tokens (Wkv P)^T + (Wkv pb + bkv).
+ * capdec_set_memory_projection forms the folded weights on the device (fp32 product, then the engine's element type);
+ * call it after capdec_set_weights and again whenever either set of parameters changes.
+ *   proj_w [D, in_dim], proj_b [D]: DEVICE fp32 (nn.Linear layout); in_dim a multiple of 64.
+ *   cross_in_w / cross_in_b: HOST arrays of n_layer DEVICE pointers to multihead_attn.in_proj_weight [3D, D] / in_proj_bias.
+ * capdec_prefill_tokens then replaces encoder.projection + capdec_prefill: tokens is DEVICE fp32
+ * [n_images, tokens_per_image, in_dim]; rows first_token .. first_token+mem_len-1 of every image are the memory
+ * positions (first_token = 1 drops the class token, vit:95). */
+int capdec_set_memory_projection(capdec_handle h, const float* proj_w, const float* proj_b, int32_t in_dim,
+                                 const float* const* cross_in_w, const float* const* cross_in_b, void* cuda_stream);
+int capdec_prefill_tokens(capdec_handle h, const float* tokens, int32_t n_images, int32_t tokens_per_image,
+                          int32_t first_token, int32_t mem_len, void* cuda_stream);
+
 /* One rollout over the images of the last prefill.  ids_out/logp_out/logits_out are DEVICE
  * pointers.  Synchronises the stream only if steps_out != NULL. */
 int capdec_decode(capdec_handle h, const capdec_decode_args* args, void* cuda_stream);

@@ -615,3 +615,122 @@ def test_beam_search_rejects_bad_arguments(dev):
     ids, lens, _ = eng.beam_search_from_memory(mem, START, END, 12, beam_size=6)  # capacity grows on demand
     assert ids.shape == (2, 12)
     eng.close()
+
+
+# ---------------------------------------------------------------- encoder hand-off
+def _tokens_and_projection(n_img=4, tokens=50, dim=192, seed=5):
+    g = torch.Generator().manual_seed(seed)
+    tok = torch.randn(n_img, tokens, dim, generator=g)
+    proj = torch.nn.Linear(dim, 512)
+    with torch.no_grad():
+        proj.weight.copy_(torch.randn(512, dim, generator=g) / dim ** 0.5)
+        proj.bias.copy_(torch.randn(512, generator=g) * 0.1)
+    with torch.no_grad():
+        mem = proj(tok[:, 1:])  # vit:95-98: drop the class token, project
+    return tok, proj, mem
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_prefill_tokens_folds_the_encoder_projection(dev, precision):
+    """capdec_prefill_tokens (K|V = tokens (Wkv P)^T + Wkv pb + bkv) against the reference's two steps
+    (memory = projection(tokens[:, 1:]); K|V = memory Wkv^T + bkv)."""
+    dec = small_decoder(layers=3)
+    w = torch_port.weights_to_numpy(dec)
+    tok, proj, mem = _tokens_and_projection()
+    eng = make_engine(dec.to(dev), precision, max_images=4, max_mem=49)
+    eng.prefill_tokens(tok.to(dev), proj.to(dev), first_token=1)
+    tol = 2e-4 if precision == "fp32" else 6e-2
+    for layer in range(3):
+        wi = w[f"transformer_decoder.layers.{layer}.multihead_attn.in_proj_weight"]
+        bi = w[f"transformer_decoder.layers.{layer}.multihead_attn.in_proj_bias"]
+        for which in (0, 1):
+            lo = 512 * (1 + which)
+            ref = mem.numpy() @ wi[lo:lo + 512].T + bi[lo:lo + 512]
+            got = eng.debug_cross_kv(layer, which, 4, 49).cpu().numpy()
+            assert np.abs(got - ref).max() < tol, (layer, which)
+    eng.close()
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_rollout_from_encoder_tokens(dev, precision):
+    """Greedy + sampled rollouts entered with un-projected tokens: logits / ids / log-probs against the oracle run on
+    the reference's projected memory; the projection is re-folded after an in-place update of its weights."""
+    dec = small_decoder(layers=2, end_bias=1.0)
+    w = torch_port.weights_to_numpy(dec)
+    tok, proj, mem = _tokens_and_projection(n_img=5)
+    proj_d = proj.to(dev)
+    eng = make_engine(dec.to(dev), precision, max_images=5, max_group=2, max_mem=49, max_len=10)
+    out = eng.decode_from_memory(tok.to(dev), START, END, max_len=10, group=2, n_sample=1, seed=21, return_logits=True,
+                                 projection=proj_d, first_token=1)
+    check_rollout(out, w, mem.numpy(), 2, 1, TOL[precision], seed=21)
+    with torch.no_grad():
+        proj_d.weight.mul_(0.5)  # optimiser-style in-place update
+        mem2 = proj_d(tok.to(dev)[:, 1:]).cpu()
+    out = eng.decode_from_memory(tok.to(dev), START, END, max_len=10, group=2, n_sample=1, seed=22, return_logits=True,
+                                 projection=proj_d, first_token=1)
+    check_rollout(out, w, mem2.numpy(), 2, 1, TOL[precision], seed=22)
+    with pytest.raises(ValueError):
+        eng.decode_from_memory(tok.to(dev)[:, :, :100], START, END, max_len=10, projection=proj_d, first_token=1)
+    eng.close()
+
+
+class _StandInTrunk(torch.nn.Module):
+    """The three members of torchvision's VisionTransformer that VisionTransformerEncoder.forward uses (vit:84-92)."""
+
+    def __init__(self, dim=128, patch=56):
+        super().__init__()
+        self.conv_proj = torch.nn.Conv2d(3, dim, patch, patch)
+        self.class_token = torch.nn.Parameter(torch.randn(1, 1, dim) * 0.1)
+        self.encoder = torch.nn.LayerNorm(dim)
+
+    def _process_input(self, x):
+        x = self.conv_proj(x)
+        return x.flatten(2).permute(0, 2, 1)
+
+
+class _StandInViTEncoder(torch.nn.Module):
+    def __init__(self, dim=128):
+        super().__init__()
+        self.vit = _StandInTrunk(dim)
+        self.projection = torch.nn.Linear(dim, 512)
+
+    def forward(self, images):  # the statements of vit:80-100
+        x = self.vit._process_input(images)
+        x = torch.cat([self.vit.class_token.expand(x.shape[0], -1, -1), x], dim=1)
+        x = self.vit.encoder(x)
+        return self.projection(x[:, 1:, :])
+
+
+def test_generate_and_scst_rollouts_hand_tokens_to_the_engine(dev):
+    """model.generate through the installed shim takes the ViT encoder's tokens (projection folded into the prefill) and
+    returns what it returns from the projected memory; scst_rollouts gives the sampled and the greedy rollout of one
+    SCST step from one encoder pass."""
+    from image_caption_b200 import patch
+
+    class Model(torch.nn.Module):
+        def __init__(self, decoder):
+            super().__init__()
+            self.encoder = _StandInViTEncoder()
+            self.decoder = decoder
+
+        def generate(self, *a, **k):
+            raise AssertionError("the reference path must not run")
+
+    torch.manual_seed(11)
+    model = Model(small_decoder(seed=6, layers=2, pe_rows=24, end_bias=1.0)).to(dev)
+    images = torch.randn(3, 3, 224, 224, device=dev)
+    eng = patch.install(model, precision="fp32", max_images=3, max_group=3, max_mem=16, max_len=12)
+    fused = model.generate(images, START, END, max_len=12)
+    eng.fuse_encoder_projection = False
+    plain = model.generate(images, START, END, max_len=12)
+    eng.fuse_encoder_projection = True
+    assert torch.equal(fused, plain)
+    s_ids, s_lp, g_ids = eng.scst_rollouts(model, images, START, END, max_len=12, n_samples=2, seed=5)
+    assert s_ids.shape[:2] == (3, 2) and s_lp.shape[:2] == (3, 2) and g_ids.shape[0] == 3
+    n = min(g_ids.shape[1], plain.shape[1])
+    assert torch.equal(g_ids[:, :n], plain[:, :n])
+    with torch.no_grad():
+        ref = eng.decode_from_memory(model.encoder(images), START, END, max_len=12, group=3, n_sample=2, seed=5)
+    assert torch.equal(ref.ids.view(3, 3, -1)[:, :2], s_ids)
+    assert (ref.logp.view(3, 3, -1)[:, :2] - s_lp).abs().max() < 1e-4
+    patch.uninstall(model)

@@ -162,3 +162,27 @@ def test_sharded_rollout_world2_gloo(tmp_path, n_images, group, n_sample):
     assert w < max_len
     assert torch.equal(ids, ids_all[:, :w]) and torch.equal(lp, lp_all[:, : w - 1])
     assert ids.dtype == torch.int64
+
+
+def test_vit_encoder_tokens_restates_the_reference_encoder():
+    """image_caption_b200.engine.vit_encoder_tokens stops VisionTransformerEncoder.forward (vit:70-100) before the
+    class-token drop and the projection: applying both to its result must reproduce the reference encoder bit for
+    bit.  Runs only where the reference checkout is mounted."""
+    import importlib.util, os, sys
+    import pytest
+    import torch
+    path = "/root/reference/models/vit_transformer_model.py"
+    if not os.path.exists(path):
+        pytest.skip("reference checkout not present")
+    spec = importlib.util.spec_from_file_location("_ref_vit_model", path)
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    from image_caption_b200.engine import vit_encoder_tokens
+    torch.manual_seed(0)
+    enc = mod.VisionTransformerEncoder(pretrained=False).eval()
+    images = torch.randn(1, 3, 224, 224)
+    with torch.no_grad():
+        ref = enc(images)
+        tok = vit_encoder_tokens(enc, images)
+        assert tok.shape == (1, 197, 768)
+        assert torch.equal(enc.projection(tok[:, 1:, :]), ref)
