@@ -6,13 +6,14 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libcapdec.so")
+LIB_PATH = os.environ.get("CAPDEC_LIB") or os.path.join(_HERE, "libcapdec.so")  # CAPDEC_LIB: A/B builds (tuning aid)
 
 ABI_VERSION = 1
 MAX_LAYERS = 12
 PREC_FP32, PREC_BF16 = 0, 1
 FLAG_NO_GRAPH, FLAG_NO_UMMA, FLAG_V1_STEP, FLAG_NO_PDL, FLAG_NO_CLUSTER_ROLLOUT = 1, 2, 4, 8, 16
 DECODE_NO_EARLY_STOP = 1
+DECODE_TEACHER_FORCED = 2
 BEAM_STOP_GRID = 1
 
 EXPORTS = (

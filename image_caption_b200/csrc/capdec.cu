@@ -1251,6 +1251,9 @@ extern "C" int capdec_decode(capdec_handle h, const capdec_decode_args* a, void*
   cp.end_token = a->end_token;
   cp.pad_token = a->pad_token;
   cp.no_early_stop = (a->flags & CAPDEC_DECODE_NO_EARLY_STOP) ? 1 : 0;
+  cp.forced = (a->flags & CAPDEC_DECODE_TEACHER_FORCED) ? 1 : 0;
+  if (cp.forced && mega_applicable(h, n_images, S, group))
+    return fail(h, CAPDEC_ERR_INVALID, "teacher forcing is not built into the cluster rollout (step_impl v3)");
   cp.n_sample_rows = n_images * a->n_sample;
   cp.n_greedy_rows = M - cp.n_sample_rows;
   // pageable source: the runtime stages it before returning, so `cp` may die with this frame
@@ -1395,6 +1398,7 @@ extern "C" int capdec_generate_host(capdec_handle h, const float* memory_host, i
                                     const capdec_decode_args* ah, void* stream) {
   if (!h || !memory_host || !ah) return fail(h, CAPDEC_ERR_INVALID, "null argument");
   if (ah->logits_out) return fail(h, CAPDEC_ERR_INVALID, "logits_out is not supported by capdec_generate_host");
+  if (ah->flags & CAPDEC_DECODE_TEACHER_FORCED) return fail(h, CAPDEC_ERR_INVALID, "teacher forcing needs device buffers (capdec_decode)");
   if (n_images < 1 || mem_len < 1 || n_images > h->cfg.max_images || mem_len > h->cfg.max_mem)
     return fail(h, CAPDEC_ERR_CAPACITY, "%d images x %d exceeds capacity %d x %d", n_images, mem_len, h->cfg.max_images, h->cfg.max_mem);
   if (ah->group < 1 || ah->group > h->cfg.max_group || ah->max_len < 2 || ah->max_len > h->cfg.max_len)

@@ -21,7 +21,7 @@ __global__ void init_rollout_kernel(DecState* st, const CallParams* cp, unsigned
   }
   const int total = M * p.max_len;
   for (int i = tid; i < total; i += gridDim.x * blockDim.x) {
-    p.ids[i] = (i % p.max_len == 0) ? p.start_token : p.pad_token;
+    if (!p.forced) p.ids[i] = (i % p.max_len == 0) ? p.start_token : p.pad_token;
     if (p.logp != nullptr && i < M * (p.max_len - 1)) p.logp[i] = 0.f;
   }
   if (tid < M) fin[tid] = 0;
@@ -118,7 +118,9 @@ sum_ln_kernel(float* __restrict__ x, const float* __restrict__ part, const float
 
 // Warp-level argmax / categorical draw over one row of kVPad logits (entries >= V are -inf).
 // Lane l owns vocabulary entries 4l .. 4l+3.  Returns token; *logp_out = log_softmax[token].
-__device__ __forceinline__ int warp_pick(const float (&l)[4], int lane, bool sample, float u, int V, float* logp_out) {
+// forced >= 0 (teacher forcing): the returned token is `forced` and *logp_out its log-probability.
+__device__ __forceinline__ int warp_pick(const float (&l)[4], int lane, bool sample, float u, int V, float* logp_out,
+                                         int forced = -1) {
   float mx = fmaxf(fmaxf(l[0], l[1]), fmaxf(l[2], l[3]));
   mx = warp_max(mx);
   float e[4];
@@ -155,6 +157,7 @@ __device__ __forceinline__ int warp_pick(const float (&l)[4], int lane, bool sam
     for (int o = 16; o > 0; o >>= 1) cand = min(cand, __shfl_xor_sync(0xffffffffu, cand, o));
     tok = (cand == 0x7fffffff) ? V - 1 : cand;
   }
+  if (forced >= 0) tok = forced;
   float lt = 0.f;
 #pragma unroll
   for (int i = 0; i < 4; ++i) if (lane * 4 + i == tok) lt = l[i];
@@ -189,9 +192,10 @@ head_kernel(DecState* st, const CallParams* cp, const float* __restrict__ logits
     const bool sample = (m % p.group) < p.n_sample;
     const float u = sample ? philox_uniform(p.seed, p.seq_id_base + (unsigned long long)m, n) : 0.f;
     float lp;
-    const int tok = warp_pick(l, lane, sample, u, V, &lp);
+    const int forced = p.forced ? (int)p.ids[(size_t)m * p.max_len + n + 1] : -1;
+    const int tok = warp_pick(l, lane, sample, u, V, &lp, forced);
     if (lane == 0) {
-      p.ids[(size_t)m * p.max_len + n + 1] = tok;
+      if (!p.forced) p.ids[(size_t)m * p.max_len + n + 1] = tok;
       const bool ended = tok == p.end_token;
       if (sample) {
         const bool was = fin[m] != 0;
@@ -334,9 +338,10 @@ vocab_head_kernel(DecState* st, const CallParams* cp, float* __restrict__ x, con
       const bool sample = (m % p.group) < p.n_sample;
       const float u = sample ? philox_uniform(p.seed, p.seq_id_base + (unsigned long long)m, n) : 0.f;
       float lp;
-      const int tok = warp_pick(l, lane, sample, u, V, &lp);
+      const int forced = p.forced ? (int)p.ids[(size_t)m * p.max_len + n + 1] : -1;
+      const int tok = warp_pick(l, lane, sample, u, V, &lp, forced);
       if (lane == 0) {
-        p.ids[(size_t)m * p.max_len + n + 1] = tok;
+        if (!p.forced) p.ids[(size_t)m * p.max_len + n + 1] = tok;
         const bool ended = tok == p.end_token;
         if (sample) {
           const bool was = fin[m] != 0;

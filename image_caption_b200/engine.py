@@ -265,6 +265,52 @@ class CaptionDecodeEngine:
             logits = logits[:, :n] if logits is not None else None
         return Rollout(ids=ids, logp=logp, steps=n, logits=logits)
 
+    def score(self, memory: torch.Tensor, ids: torch.Tensor, end_token: int, group: int = 1,
+              return_logits: bool = True, pad_token: int = 0):
+        """Teacher-forced pass over given sequences (CAPDEC_DECODE_TEACHER_FORCED): ``ids`` (B*group, L) int64 with
+        column 0 = <start>; returns ``(logits (M, L-1, V) or None, logp (M, L-1))`` where ``logits[:, k]`` is what the
+        reference's ``model.decoder(ids[:, :k+1], memory, tgt_mask=causal)[:, -1]`` returns (scst:223-226, vit:312-315)
+        and ``logp[:, k] = log_softmax(logits[:, k])[ids[:, k+1]]``, zero after a row's <end> (scst:236-239).
+        Inference only: no autograd graph is built."""
+        if memory.dim() != 3 or memory.shape[2] != self.d_model or not memory.is_cuda:
+            raise ValueError(f"memory must be CUDA (B, S, {self.d_model}), got {tuple(memory.shape)}")
+        n_images, mem_len = memory.shape[0], memory.shape[1]
+        if ids.dim() != 2 or ids.shape[0] != n_images * group:
+            raise ValueError(f"ids must be ({n_images * group}, L), got {tuple(ids.shape)}")
+        max_len = ids.shape[1]
+        self._check_lengths(max_len)
+        ids = ids.to(self.device, torch.int64).contiguous()
+        if int(ids.min()) < 0 or int(ids.max()) >= self.vocab:
+            raise ValueError("token id outside the vocabulary")
+        self._ensure_capacity(n_images, group, mem_len, max_len)
+        self.sync_weights()
+        memory = memory.detach().to(torch.float32).contiguous()
+        m = n_images * group
+        logp = torch.empty((m, max_len - 1), dtype=torch.float32, device=self.device)
+        logits = (torch.empty((m, max_len - 1, self.vocab), dtype=torch.float32, device=self.device)
+                  if return_logits else None)
+        args = _lib.DecodeArgs(group=group, n_sample=group, start_token=int(ids[0, 0]), end_token=end_token,
+                               pad_token=pad_token, max_len=max_len, seed=0, seq_id_base=0,
+                               flags=_lib.DECODE_NO_EARLY_STOP | _lib.DECODE_TEACHER_FORCED)
+        args.ids_out = ids.data_ptr()
+        args.logp_out = logp.data_ptr()
+        args.logits_out = logits.data_ptr() if return_logits else None
+        stream = _stream_ptr(self.device)
+        _lib.check(self._h, self._lib.capdec_prefill(self._h, memory.data_ptr(), n_images, mem_len, stream))
+        _lib.check(self._h, self._lib.capdec_decode(self._h, C.byref(args), stream))
+        self._keep_ids = ids
+        return logits, logp
+
+    @torch.no_grad()
+    def decoder_forward(self, tgt: torch.Tensor, memory: torch.Tensor) -> torch.Tensor:
+        """``model.decoder(tgt, memory, tgt_mask=causal)`` (vit:155-182 as called at vit:312 / scst:223) on the
+        engine: (B, t) token ids -> (B, t, V) logits.  Causal mask only (the hot path's call shape); no autograd."""
+        b, t = tgt.shape
+        ids = torch.cat([tgt.to(self.device, torch.int64),
+                         torch.zeros((b, 1), dtype=torch.int64, device=self.device)], dim=1)  # step t-1 scores a dummy token
+        logits, _ = self.score(memory, ids, end_token=0)  # the end token only shapes the (discarded) log-probs
+        return logits
+
     def beam_search_from_memory(self, memory: torch.Tensor, start_token: int, end_token: int, max_len: int = 50,
                                 beam_size: int = 5, pad_token: int = 0, stop_rule: str = "vit"):
         """Batched beam search (C ABI ``capdec_beam_search``) over ``memory`` (B, S, 512) CUDA float32.

@@ -124,6 +124,12 @@ typedef struct {
 /* Run all max_len-1 steps even if the stop condition is met (sharded greedy rollouts: the
  * global "all rows emit <end> on one step" test of vit:322 needs every rank's later tokens). */
 #define CAPDEC_DECODE_NO_EARLY_STOP 1
+/* Teacher forcing: ids_out holds the whole sequences on entry ([M, max_len], column 0 = <start>) and is not written;
+ * step n feeds ids[:, n] and scores ids[:, n+1] (logp_out, rows g < n_sample; 0 after a row's <end>, scst:239) instead
+ * of picking a token; logits_out receives every step's logits.  This is the reference's per-step call
+ * `model.decoder(prefix, memory, tgt_mask=causal)` (utils/scst_loss.py:223, vit_transformer_model.py:312) evaluated for
+ * a given sequence: row k of its output = the logits of step k.  Stop rules apply to the forced tokens. */
+#define CAPDEC_DECODE_TEACHER_FORCED 2
 
 int capdec_abi_version(void);
 const char* capdec_last_error(capdec_handle h); /* h may be NULL: error of a failed create */

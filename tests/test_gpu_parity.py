@@ -734,3 +734,54 @@ def test_generate_and_scst_rollouts_hand_tokens_to_the_engine(dev):
     assert torch.equal(ref.ids.view(3, 3, -1)[:, :2], s_ids)
     assert (ref.logp.view(3, 3, -1)[:, :2] - s_lp).abs().max() < 1e-4
     patch.uninstall(model)
+
+
+# ---------------------------------------------------------------- teacher forcing (the reference's per-step decoder call)
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_teacher_forced_pass_against_the_reference(dev, golden_case, precision):
+    """CAPDEC_DECODE_TEACHER_FORCED through engine.score / engine.decoder_forward against outputs of the REAL reference
+    (tests/golden): its decoder's logits on random token sequences (`model.decoder(tgt, memory, tgt_mask)`, vit:312 /
+    scst:223), and the logits and log-probs `_sample_with_log_probs` (scst:202-254) produced on its own sampled ids,
+    zeros after a row's <end> included."""
+    name, z, dec, mem = golden_case
+    max_len = int(z["max_len"])
+    tol = TOL[precision]
+    eng = make_engine(dec.to(dev), precision, max_images=8, max_mem=int(z["mem_len"]), max_len=max_len)
+    tf_ids = torch.from_numpy(z["tf_ids"]).to(dev)
+    logits, _ = eng.score(mem.to(dev), tf_ids, END)
+    assert np.abs(logits.cpu().numpy() - z["tf_logits"]).max() < tol
+    assert torch.equal(tf_ids.cpu(), torch.from_numpy(z["tf_ids"]))  # the given sequences are not overwritten
+    fwd = eng.decoder_forward(tf_ids[:, :-1], mem.to(dev))
+    assert fwd.shape == (tf_ids.shape[0], max_len - 1, VOCAB) and torch.equal(fwd, logits)
+    s_ids = torch.from_numpy(z["sample_ids"]).to(dev)
+    logits, logp = eng.score(mem.to(dev), s_ids, END)
+    assert np.abs(logits.cpu().numpy() - z["sample_logits"]).max() < tol
+    assert np.abs(logp.cpu().numpy() - z["sample_logp"]).max() < tol
+    assert ((z["sample_logp"] == 0.0) == (logp.cpu().numpy() == 0.0)).all()  # finished rows: exactly zero (scst:239)
+    # an ordinary rollout afterwards starts from <start> again
+    out = eng.decode_from_memory(mem.to(dev), START, END, max_len=max_len)
+    if precision == "fp32":
+        np.testing.assert_array_equal(out.ids.cpu().numpy(), z["greedy_ids"])
+    with pytest.raises(ValueError):
+        eng.score(mem.to(dev), torch.full_like(s_ids, VOCAB), END)
+    eng.close()
+
+
+def test_teacher_forced_grouped_and_v1(dev):
+    """Teacher forcing with several sequences per image (shared cross K/V) on the v2 and the v1 step kernels."""
+    dec = small_decoder(layers=2)
+    w = torch_port.weights_to_numpy(dec)
+    mem = torch_port.synthetic_memory(5, 49)
+    g = torch.Generator().manual_seed(2)
+    ids = torch.randint(0, VOCAB, (15, 9), generator=g)
+    ids[:, 0] = START
+    ref = decoder_np.decoder_forward(w, ids[:, :-1].numpy(), np.repeat(mem.numpy(), 3, 0))
+    for impl in ("v2", "v1"):
+        eng = make_engine(dec.to(dev), "bf16", step_impl=impl, max_images=5, max_group=3, max_mem=49, max_len=9)
+        logits, logp = eng.score(mem.to(dev), ids.to(dev), END, group=3)
+        assert np.abs(logits.cpu().numpy() - ref).max() < TOL["bf16"]
+        lsm = torch.log_softmax(logits, -1).gather(2, ids.to(dev)[:, 1:, None]).squeeze(2)
+        ended = ids[:, 1:] == END
+        before = ((ended.cumsum(1) - ended.long()) > 0).to(dev)
+        assert (logp - lsm.masked_fill(before, 0.0)).abs().max() < 1e-4
+        eng.close()
