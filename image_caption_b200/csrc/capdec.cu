@@ -265,7 +265,7 @@ static int swap_stages(capdec_handle h, int bnb, int K, int ctas) {
 // All of a CTA's K range in three copies (two weight halves + the activations) when it is exactly 8 k-blocks and the
 // ring holds them all (env CAPDEC_NO_WHOLE_K=1 keeps one copy per k-block and operand).
 static int swap_whole_k(capdec_handle h, int bnb, int num_kb, int stages) {
-  return (!h->no_whole_k && num_kb == kSwapWholeKB && stages >= kSwapWholeKB && bnb <= 64) ? 1 : 0;
+  return (!h->no_whole_k && num_kb == kSwapWholeKB && stages >= kSwapWholeKB && bnb <= 64) ? h->whole_x_parts : 0;
 }
 
 // k-blocks per TMA copy where whole-K copies do not apply (K = 2048, or 128-row tiles whose whole K does not fit):
@@ -296,6 +296,8 @@ static void note_plan(capdec_handle h, int bnb, bool ln, int n_out, int K, int c
 }
 static const CUtensorMap& pick_w3(const WeightMaps& tw, int kgrp) { return kgrp == 2 ? tw.w3g2 : tw.w3; }
 static const CUtensorMap& pick_x3(const ActMaps& tx, int kgrp) { return kgrp == 2 ? tx.grp2 : (kgrp == 4 ? tx.grp4 : tx.whole); }
+// whole-K launches: the activations arrive in `parts` copies of 8 / parts k-blocks
+static const CUtensorMap& pick_x3_whole(const ActMaps& tx, int parts) { return parts == 4 ? tx.grp2 : (parts == 2 ? tx.grp4 : tx.whole); }
 
 template <int BNB, bool kLN, typename Epi, int KSPLIT>
 static int launch_swap_ks(capdec_handle h, cudaStream_t s, const WeightMaps& tw, const ActMaps& tx, int M, int n_out,
@@ -309,7 +311,7 @@ static int launch_swap_ks(capdec_handle h, cudaStream_t s, const WeightMaps& tw,
   note_plan(h, BNB, kLN, n_out, K, grid.x * grid.y, stages, whole, kgrp);
   ProfScope ps(h, s);
   cudaError_t e = launch_ex(gemm_swap_kernel<BNB, kLN, Epi, KSPLIT>, grid, dim3(swap_threads(BNB, kLN)), swap_smem_bytes(BNB, stages, KSPLIT), s,
-                            kLN ? 4 * KSPLIT : 1, h->use_pdl, tw.bn[2], tx.tile, pick_w3(tw, kgrp), pick_x3(tx, kgrp),
+                            kLN ? 4 * KSPLIT : 1, h->use_pdl, tw.bn[2], tx.tile, pick_w3(tw, kgrp), whole ? pick_x3_whole(tx, whole) : pick_x3(tx, kgrp),
                             whole, kgrp, M, K, stages, epi, ln, st);
   if (e != cudaSuccess) return fail(h, CAPDEC_ERR_CUDA, "gemm_swap launch failed: %s (BNB=%d n_out=%d K=%d stages=%d ksplit=%d)",
                                     cudaGetErrorString(e), BNB, n_out, K, stages, KSPLIT);
@@ -346,7 +348,7 @@ static int launch_swap_bnb(capdec_handle h, cudaStream_t s, const WeightMaps& tw
   note_plan(h, BNB, kLN, n_out, K, grid.x * grid.y * grid.z, stages, whole, kgrp);
   ProfScope ps(h, s);
   cudaError_t e = launch_ex(gemm_swap_kernel<BNB, kLN, Epi>, grid, dim3(swap_threads(BNB, kLN)), swap_smem_bytes(BNB, stages), s,
-                            kLN ? 4 : 1, h->use_pdl, tw.bn[2], tx.tile, pick_w3(tw, kgrp), pick_x3(tx, kgrp),
+                            kLN ? 4 : 1, h->use_pdl, tw.bn[2], tx.tile, pick_w3(tw, kgrp), whole ? pick_x3_whole(tx, whole) : pick_x3(tx, kgrp),
                             whole, kgrp, M, K, stages, epi, ln, st);
   if (e != cudaSuccess) return fail(h, CAPDEC_ERR_CUDA, "gemm_swap launch failed: %s (BNB=%d n_out=%d K=%d stages=%d)",
                                     cudaGetErrorString(e), BNB, n_out, K, stages);
@@ -596,6 +598,7 @@ extern "C" int capdec_create(const capdec_config* cfg, int device, capdec_handle
   if (const char* e = getenv("CAPDEC_LN_TMA_STORE")) h->force_ln_tma_store = atoi(e) != 0 ? 1 : 0;
   if (const char* e = getenv("CAPDEC_NO_CROSS_STREAM")) h->no_cross_stream = atoi(e) != 0;
   if (const char* e = getenv("CAPDEC_NO_WHOLE_K")) h->no_whole_k = atoi(e) != 0;
+  if (const char* e = getenv("CAPDEC_WHOLE_X_PARTS")) { const int v = atoi(e); if (v == 1 || v == 2 || v == 4) h->whole_x_parts = v; }
   if (const char* e = getenv("CAPDEC_FFN2_FUSE")) h->no_ffn2_fuse = atoi(e) == 0;
   if (const char* e = getenv("CAPDEC_KGROUP")) h->no_kgroup = atoi(e) == 0;
   if (const char* e = getenv("CAPDEC_HEAD_RW")) { const int v = atoi(e); h->force_head_rw = (v == 1 || v == 2 || v == 4 || v == 6) ? v : 0; }

@@ -94,6 +94,7 @@ struct capdec_engine {
   int force_ln_tma_store = -1;     // env CAPDEC_LN_TMA_STORE
   int force_head_rw = 0;           // env CAPDEC_HEAD_RW: rows per warp of the vocabulary head (1, 2, 4, 6)
   bool no_kgroup = true;           // env CAPDEC_KGROUP=1 clears it: kgrp k-blocks per TMA copy where whole-K copies do not apply
+  int whole_x_parts = 1;           // env CAPDEC_WHOLE_X_PARTS: copies the activations of a whole-K launch arrive in (1, 2, 4)
   bool no_whole_k = false;         // env CAPDEC_NO_WHOLE_K: one TMA copy per k-block instead of whole-K copies
   bool no_cross_stream = false;    // env CAPDEC_NO_CROSS_STREAM: keep the tensor-core cross-attention for group == 1
   CUtensorMap tm_ckv;              // whole cross cache as [rows,64], box = 64 x ca_key_rows(S)

@@ -298,8 +298,13 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
   if (warp == 0) {       // the activation tiles are on the critical path: request them before anything else
     if (ptx::elect_one()) {  // (also when the rollout is over: the prologue's barriers must complete)
       if (whole_k) {
-        ptx::mbar_expect_tx(&full[2], kSwapWholeKB * kXBytes);
-        ptx::tma_load_3d(smem_x, &tm_x3, &full[2], 0, b0, kb0);
+        // whole_k = number of copies the activations arrive in (1, 2 or 4; tm_x3's box depth is 8 / whole_k):
+        // the MMAs of the first k-blocks start when the first part has landed
+        const int kbp = kSwapWholeKB / whole_k;
+        for (int j = 0; j < whole_k; ++j) {
+          ptx::mbar_expect_tx(&full[2 + j], kbp * kXBytes);
+          ptx::tma_load_3d(smem_x + (size_t)j * kbp * kXBytes, &tm_x3, &full[2 + j], 0, b0, kb0 + j * kbp);
+        }
       } else if (kgrp > 1) {
         for (int g = 0; g < n_pre / kgrp; ++g)
           ptx::tma_load_3d(smem_x + (size_t)g * kgrp * kXBytes, &tm_x3, &full[g], 0, b0, kb0 + g * kgrp);
@@ -316,7 +321,7 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
 
   if (warp == 0) {
     if (whole_k) {
-      if (!active) { ptx::mbar_wait(&full[0], 0); ptx::mbar_wait(&full[1], 0); ptx::mbar_wait(&full[2], 0); }  // no copy may outlive the CTA
+      if (!active) for (int j = 0; j < 2 + whole_k; ++j) ptx::mbar_wait(&full[j], 0);  // no copy may outlive the CTA
     } else if (active && kgrp > 1) {
       const uint64_t keep = ptx::policy_evict_last();
       const int ng = stages / kgrp;  // ring slots
@@ -356,12 +361,12 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
       const int first = warp == 1 ? 0 : warp - kIssuer2 + 1;  // this issuer's k-blocks: first, first + kIssuers, ...
       const uint32_t acc = tmem_base + (uint32_t)(first * BNB);
       const uint32_t w_lo0 = ptx::umma_desc_lo(ptx::smem_u32(smem_w)), x_lo0 = ptx::umma_desc_lo(ptx::smem_u32(smem_x));
-      if (whole_k) ptx::mbar_wait(&full[2], 0);  // the activations
       const int ng = kgrp > 1 ? stages / kgrp : 1;
       for (int kb = first; kb < num_kb; kb += kIssuers) {
         const int grp = kgrp > 1 ? kb / kgrp : 0, slot = grp % ng;  // grouped copies: ring slot of this k-block's group
         const int s = whole_k ? kb : (kgrp > 1 ? slot * kgrp + kb % kgrp : kb % stages);
         const uint32_t ph = whole_k ? 0u : (uint32_t)(((kgrp > 1 ? grp / ng : kb / stages)) & 1);
+        if (whole_k) ptx::mbar_wait(&full[2 + kb / (kSwapWholeKB / whole_k)], 0);  // this k-block's part of the activations
         ptx::mbar_wait(&full[whole_k ? kb / (kSwapWholeKB / 2) : (kgrp > 1 ? slot : s)], ph);
         ptx::tc_fence_after();
         if (ptx::elect_one()) {
