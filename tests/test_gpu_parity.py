@@ -785,3 +785,63 @@ def test_teacher_forced_grouped_and_v1(dev):
         before = ((ended.cumsum(1) - ended.long()) > 0).to(dev)
         assert (logp - lsm.masked_fill(before, 0.0)).abs().max() < 1e-4
         eng.close()
+
+
+# ---------------------------------------------------------------- BASELINE.json sizes: size-independent properties
+FULL_SIZE = {  # images, memory length, rollouts per image, sampled rollouts, max_len (bench.py WORKLOADS)
+    "cfg2": (256, 49, 1, 0, 50),
+    "cfg3": (512, 196, 6, 5, 50),
+    "cfg5_per_gpu": (1024, 49, 1, 0, 64),
+}
+
+
+@pytest.mark.parametrize("name", list(FULL_SIZE))
+def test_full_size_rollout_properties(dev, name):
+    """The benchmark workloads at full size (6 layers, bf16, every decode step): (1) every greedy token is the argmax
+    of its step's logits; (2) sampled log-probs are log_softmax(logits)[id], exactly 0 after a row's <end> and for
+    greedy rows; (3) a teacher-forced replay of the produced ids returns the rollout's logits and log-probs bit for
+    bit (KV caches, step state and graph replay hold no hidden state); (4) permuting the images permutes the results
+    (rows do not interact; a row's arithmetic does not depend on its tile position); (5) rows at tile boundaries
+    against the CPU oracle within the bf16 tolerance."""
+    from image_caption_b200.synthetic import random_decoder, random_memory
+    n_img, S, G, ns, max_len = FULL_SIZE[name]
+    M = n_img * G
+    dec = random_decoder(0, pe_rows=max(52, max_len))
+    w = torch_port.weights_to_numpy(dec)
+    mem = random_memory(n_img, S)
+    memd = mem.to(dev)
+    eng = make_engine(dec.to(dev), "bf16", max_images=n_img, max_group=G, max_mem=S, max_len=max_len)
+    run = lambda m: eng.decode_from_memory(m, START, END, max_len=max_len, group=G, n_sample=ns, seed=2024,
+                                           return_logits=True, early_stop=False, trim=False)
+    out = run(memd)
+    assert out.steps == max_len - 1 and out.ids.shape == (M, max_len) and (out.ids[:, 0] == START).all()
+    ids, logits = out.ids, out.logits
+    sample = (torch.arange(M, device=dev) % G) < ns
+    # (1)
+    assert torch.equal(ids[~sample][:, 1:], logits[~sample].argmax(-1))
+    # (2)
+    if ns:
+        tok = ids[:, 1:]
+        lsm = torch.log_softmax(logits, -1).gather(2, tok[..., None]).squeeze(2)
+        ended = tok == END
+        after = (ended.cumsum(1) - ended.long()) > 0
+        want = lsm.masked_fill(after | ~sample[:, None], 0.0)
+        assert (out.logp - want).abs().max() < 1e-4
+        assert (out.logp[after | ~sample[:, None]] == 0).all()
+    # (3)
+    l2, lp2 = eng.score(memd, ids.clone(), END, group=G)
+    assert torch.equal(l2, logits)
+    if ns:
+        assert torch.equal(lp2[sample], out.logp[sample])
+    # (4)
+    perm = torch.randperm(n_img, generator=torch.Generator().manual_seed(3)).to(dev)
+    outp = run(memd[perm].contiguous())
+    rows = (perm[:, None] * G + torch.arange(G, device=dev)[None]).flatten()
+    assert torch.equal(outp.logits[:, 0], logits[rows, 0])
+    assert torch.equal(outp.ids[~sample], ids[rows][~sample])
+    assert torch.equal(outp.logits[~sample], logits[rows][~sample])
+    # (5)
+    R = sorted({0, 31, 32, 127, 128, M // 2 + 1, M - 129, M - 33, M - 1})
+    ref = decoder_np.decoder_forward(w, ids[R, :-1].cpu().numpy(), mem.numpy()[[r // G for r in R]])
+    assert np.abs(logits[R].cpu().numpy() - ref).max() < TOL["bf16"]
+    eng.close()
