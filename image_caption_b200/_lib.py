@@ -77,8 +77,9 @@ def load() -> C.CDLL:
             f"{LIB_PATH} not found: build it with `python __graft_entry__.py build` "
             "(nvcc, sm_100a). There is no CPU or PyTorch fallback for the decode path.")
     lib = C.CDLL(LIB_PATH)
+    ab_build = bool(os.environ.get("CAPDEC_LIB"))  # an older A/B build may lack the newest entry points
     for name in EXPORTS:
-        if not hasattr(lib, name):
+        if not hasattr(lib, name) and not ab_build:
             raise ImportError(f"{LIB_PATH} does not export {name}")
     H = C.c_void_p
     lib.capdec_abi_version.restype = C.c_int
@@ -93,9 +94,10 @@ def load() -> C.CDLL:
     lib.capdec_sample_logits.argtypes = [H, C.c_void_p, C.c_int32, C.c_int32, C.c_uint64, C.c_uint64, C.c_int32,
                                          C.c_void_p, C.c_void_p, C.c_void_p]
     lib.capdec_beam_search.argtypes = [H, C.POINTER(BeamArgs), C.c_void_p]
-    lib.capdec_set_memory_projection.argtypes = [H, C.c_void_p, C.c_void_p, C.c_int32, C.POINTER(C.c_void_p),
-                                                 C.POINTER(C.c_void_p), C.c_void_p]
-    lib.capdec_prefill_tokens.argtypes = [H, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_void_p]
+    if hasattr(lib, "capdec_prefill_tokens"):
+        lib.capdec_set_memory_projection.argtypes = [H, C.c_void_p, C.c_void_p, C.c_int32, C.POINTER(C.c_void_p),
+                                                     C.POINTER(C.c_void_p), C.c_void_p]
+        lib.capdec_prefill_tokens.argtypes = [H, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_void_p]
     lib.capdec_launch_count.restype = C.c_int64
     lib.capdec_launch_count.argtypes = [H]
     lib.capdec_debug_gemm.argtypes = [H, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32,
@@ -104,7 +106,7 @@ def load() -> C.CDLL:
     lib.capdec_profile_enable.argtypes = [H, C.c_int32]
     lib.capdec_profile_report.argtypes = [H, C.c_char_p, C.c_int32]
     for name in EXPORTS:
-        if name not in ("capdec_last_error", "capdec_launch_count"):
+        if name not in ("capdec_last_error", "capdec_launch_count") and hasattr(lib, name):
             getattr(lib, name).restype = C.c_int
     if lib.capdec_abi_version() != ABI_VERSION:
         raise ImportError(f"libcapdec ABI {lib.capdec_abi_version()} != binding {ABI_VERSION}")

@@ -142,9 +142,7 @@ static int make_weight_maps(capdec_handle h, WeightMaps* wm, const void* ptr, in
     if (rc) return rc;
   }
   if (n % kSwapBF == 0 && (k / kUmmaBK) % kSwapWholeKB == 0) {
-    int rc = make_map3(h, &wm->w3, ptr, n, k, kSwapBF, kSwapWholeKB / 2);
-    if (rc) return rc;
-    return make_map3(h, &wm->w3g2, ptr, n, k, kSwapBF, 2);
+    return make_map3(h, &wm->w3, ptr, n, k, kSwapBF, kSwapWholeKB / 2);
   }
   return 0;
 }
@@ -265,39 +263,8 @@ static int swap_stages(capdec_handle h, int bnb, int K, int ctas) {
 // All of a CTA's K range in three copies (two weight halves + the activations) when it is exactly 8 k-blocks and the
 // ring holds them all (env CAPDEC_NO_WHOLE_K=1 keeps one copy per k-block and operand).
 static int swap_whole_k(capdec_handle h, int bnb, int num_kb, int stages) {
-  return (!h->no_whole_k && num_kb == kSwapWholeKB && stages >= kSwapWholeKB && bnb <= 64) ? h->whole_x_parts : 0;
+  return (!h->no_whole_k && num_kb == kSwapWholeKB && stages >= kSwapWholeKB && bnb <= 64) ? 1 : 0;
 }
-
-// k-blocks per TMA copy where whole-K copies do not apply (K = 2048, or 128-row tiles whose whole K does not fit):
-// the largest of 4 / 2 that leaves at least two ring slots; launches that run two CTAs per SM keep one box per k-block.
-// Returns the group size (1 = ungrouped) and rounds `stages` to whole groups.
-// Off by default (env CAPDEC_KGROUP=1): measured on B200 it changes nothing (cfg5 526.8 vs 524.8 us/step, cfg3 897.7 vs
-// 889.5).  Those main loops are not waiting for the TMA unit: a k-block of a 128 x 128 tile writes 32 KB into shared
-// memory and its four MMAs read 32 KB back, 512 cycles of the SM's 128 B/clk against 256 cycles of tensor pipe --
-// the phase trace shows 121 cycles per MMA.  Halving the shared-memory traffic per flop needs cta_group::2 tiles.
-static int swap_kgroup(capdec_handle h, int bnb, int num_kb, int ctas, int ksplit, int whole, int* stages) {
-  if (whole || h->no_kgroup || ctas > 148 || h->force_stages > 0) return 1;
-  for (int g = 4; g >= 2; g -= 2) {
-    if (num_kb % g != 0 || num_kb < g) continue;
-    int st = std::min(num_kb, 12) / g * g;
-    while (st > g && swap_smem_bytes(bnb, st, ksplit) > kMaxDynSmem) st -= g;
-    if (st >= 2 * g || (st == g && num_kb == g)) {
-      if (swap_smem_bytes(bnb, st, ksplit) > kMaxDynSmem) continue;
-      *stages = st;
-      return g;
-    }
-  }
-  return 1;
-}
-static void note_plan(capdec_handle h, int bnb, bool ln, int n_out, int K, int ctas, int stages, int whole, int kgrp) {
-  static int left = getenv("CAPDEC_TRACE_GEMM") ? 24 : 0;  // tuning aid: the first launches' copy plans
-  if (left > 0) { --left; fprintf(stderr, "swap plan: bnb=%d ln=%d n_out=%d K=%d ctas=%d stages=%d whole=%d kgrp=%d\n", bnb, (int)ln, n_out, K, ctas, stages, whole, kgrp); }
-  (void)h;
-}
-static const CUtensorMap& pick_w3(const WeightMaps& tw, int kgrp) { return kgrp == 2 ? tw.w3g2 : tw.w3; }
-static const CUtensorMap& pick_x3(const ActMaps& tx, int kgrp) { return kgrp == 2 ? tx.grp2 : (kgrp == 4 ? tx.grp4 : tx.whole); }
-// whole-K launches: the activations arrive in `parts` copies of 8 / parts k-blocks
-static const CUtensorMap& pick_x3_whole(const ActMaps& tx, int parts) { return parts == 4 ? tx.grp2 : (parts == 2 ? tx.grp4 : tx.whole); }
 
 template <int BNB, bool kLN, typename Epi, int KSPLIT>
 static int launch_swap_ks(capdec_handle h, cudaStream_t s, const WeightMaps& tw, const ActMaps& tx, int M, int n_out,
@@ -307,12 +274,10 @@ static int launch_swap_ks(capdec_handle h, cudaStream_t s, const WeightMaps& tw,
   while (stages > 2 && swap_smem_bytes(BNB, stages, KSPLIT) > kMaxDynSmem) --stages;
   while (kLN && stages * swap_stage_bytes(BNB) < swap_ln_stage_out_bytes(BNB)) ++stages;  // the output tile is staged in the ring
   const int whole = swap_whole_k(h, BNB, K / kSwapBK / KSPLIT, stages);
-  const int kgrp = swap_kgroup(h, BNB, K / kSwapBK / KSPLIT, grid.x * grid.y, KSPLIT, whole, &stages);
-  note_plan(h, BNB, kLN, n_out, K, grid.x * grid.y, stages, whole, kgrp);
   ProfScope ps(h, s);
   cudaError_t e = launch_ex(gemm_swap_kernel<BNB, kLN, Epi, KSPLIT>, grid, dim3(swap_threads(BNB, kLN)), swap_smem_bytes(BNB, stages, KSPLIT), s,
-                            kLN ? 4 * KSPLIT : 1, h->use_pdl, tw.bn[2], tx.tile, pick_w3(tw, kgrp), whole ? pick_x3_whole(tx, whole) : pick_x3(tx, kgrp),
-                            whole, kgrp, M, K, stages, epi, ln, st);
+                            kLN ? 4 * KSPLIT : 1, h->use_pdl, tw.bn[2], tx.tile, tw.w3, tx.whole,
+                            whole, M, K, stages, epi, ln, st);
   if (e != cudaSuccess) return fail(h, CAPDEC_ERR_CUDA, "gemm_swap launch failed: %s (BNB=%d n_out=%d K=%d stages=%d ksplit=%d)",
                                     cudaGetErrorString(e), BNB, n_out, K, stages, KSPLIT);
   h->launches_this_enqueue++;
@@ -344,12 +309,10 @@ static int launch_swap_bnb(capdec_handle h, cudaStream_t s, const WeightMaps& tw
   int stages = swap_stages(h, BNB, K / zsplit, grid.x * grid.y * grid.z);
   while (kLN && stages * swap_stage_bytes(BNB) < swap_ln_stage_out_bytes(BNB)) ++stages;  // the output tile is staged in the ring
   const int whole = swap_whole_k(h, BNB, K / kSwapBK / zsplit, stages);
-  const int kgrp = swap_kgroup(h, BNB, K / kSwapBK / zsplit, grid.x * grid.y * grid.z, 1, whole, &stages);
-  note_plan(h, BNB, kLN, n_out, K, grid.x * grid.y * grid.z, stages, whole, kgrp);
   ProfScope ps(h, s);
   cudaError_t e = launch_ex(gemm_swap_kernel<BNB, kLN, Epi>, grid, dim3(swap_threads(BNB, kLN)), swap_smem_bytes(BNB, stages), s,
-                            kLN ? 4 : 1, h->use_pdl, tw.bn[2], tx.tile, pick_w3(tw, kgrp), whole ? pick_x3_whole(tx, whole) : pick_x3(tx, kgrp),
-                            whole, kgrp, M, K, stages, epi, ln, st);
+                            kLN ? 4 : 1, h->use_pdl, tw.bn[2], tx.tile, tw.w3, tx.whole,
+                            whole, M, K, stages, epi, ln, st);
   if (e != cudaSuccess) return fail(h, CAPDEC_ERR_CUDA, "gemm_swap launch failed: %s (BNB=%d n_out=%d K=%d stages=%d)",
                                     cudaGetErrorString(e), BNB, n_out, K, stages);
   h->launches_this_enqueue++;
@@ -598,9 +561,7 @@ extern "C" int capdec_create(const capdec_config* cfg, int device, capdec_handle
   if (const char* e = getenv("CAPDEC_LN_TMA_STORE")) h->force_ln_tma_store = atoi(e) != 0 ? 1 : 0;
   if (const char* e = getenv("CAPDEC_NO_CROSS_STREAM")) h->no_cross_stream = atoi(e) != 0;
   if (const char* e = getenv("CAPDEC_NO_WHOLE_K")) h->no_whole_k = atoi(e) != 0;
-  if (const char* e = getenv("CAPDEC_WHOLE_X_PARTS")) { const int v = atoi(e); if (v == 1 || v == 2 || v == 4) h->whole_x_parts = v; }
   if (const char* e = getenv("CAPDEC_FFN2_FUSE")) h->no_ffn2_fuse = atoi(e) == 0;
-  if (const char* e = getenv("CAPDEC_KGROUP")) h->no_kgroup = atoi(e) == 0;
   if (const char* e = getenv("CAPDEC_HEAD_RW")) { const int v = atoi(e); h->force_head_rw = (v == 1 || v == 2 || v == 4 || v == 6) ? v : 0; }
   if (const char* e = getenv("CAPDEC_BEAM_V1")) h->beam_v1 = atoi(e) != 0;
   if (const char* e = getenv("CAPDEC_GRAPH_STEPS")) h->graph_steps = std::max(1, atoi(e));
@@ -1118,11 +1079,6 @@ static int ensure_activation_maps(capdec_handle h, int M) {
     TRY(make_map3(h, &h->tx_xb.whole, h->xb, M, kD, h->bnb, kSwapWholeKB));
     TRY(make_map3(h, &h->tx_a.whole, h->a, M, kD, h->bnb, kSwapWholeKB));
     TRY(make_map3(h, &h->tx_h.whole, h->hbuf, M, h->cfg.d_ff, h->bnb, kSwapWholeKB));
-    for (int g = 2; g <= 4; g += 2) {
-      TRY(make_map3(h, g == 2 ? &h->tx_xb.grp2 : &h->tx_xb.grp4, h->xb, M, kD, h->bnb, g));
-      TRY(make_map3(h, g == 2 ? &h->tx_a.grp2 : &h->tx_a.grp4, h->a, M, kD, h->bnb, g));
-      TRY(make_map3(h, g == 2 ? &h->tx_h.grp2 : &h->tx_h.grp4, h->hbuf, M, h->cfg.d_ff, h->bnb, g));
-    }
     // measured (B200): staging + bulk stores win for 32-row tiles (cfg2 372.6 -> 368.6 us/step), per-thread stores
     // for wider ones (cfg3 974 -> 958, cfg5 627 -> 620): the 96 KB tile takes ~3.3k cycles to drain
     h->ln_tma_store = h->force_ln_tma_store >= 0 ? h->force_ln_tma_store : (h->bnb == 32 ? 1 : 0);

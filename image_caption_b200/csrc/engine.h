@@ -16,13 +16,11 @@ namespace capdec {
 struct WeightMaps {
   CUtensorMap bn[3];  // 32, 64, 128
   CUtensorMap w3;     // [64, rows, K/64] view, box = 64 x 128 rows x 4 k-blocks: half of a K = 512 weight slice per copy
-  CUtensorMap w3g2;   // same view, box depth 2 (grouped copies of 128-row activation tiles)
 };
 // TMA views of one activation matrix for the v2 GEMMs
 struct ActMaps {
   CUtensorMap tile;   // box = 64 columns x bnb rows (one k-block)
   CUtensorMap whole;  // [64, rows, K/64] view, box = 64 x bnb rows x 8 k-blocks: all of K = 512 in one copy
-  CUtensorMap grp2, grp4;  // same view, box depth 2 / 4 k-blocks (grouped copies)
 };
 
 struct LayerParams {
@@ -93,8 +91,6 @@ struct capdec_engine {
   int ln_tma_store = 1;            // LayerNorm epilogue leaves through bulk tensor stores
   int force_ln_tma_store = -1;     // env CAPDEC_LN_TMA_STORE
   int force_head_rw = 0;           // env CAPDEC_HEAD_RW: rows per warp of the vocabulary head (1, 2, 4, 6)
-  bool no_kgroup = true;           // env CAPDEC_KGROUP=1 clears it: kgrp k-blocks per TMA copy where whole-K copies do not apply
-  int whole_x_parts = 1;           // env CAPDEC_WHOLE_X_PARTS: copies the activations of a whole-K launch arrive in (1, 2, 4)
   bool no_whole_k = false;         // env CAPDEC_NO_WHOLE_K: one TMA copy per k-block instead of whole-K copies
   bool no_cross_stream = false;    // env CAPDEC_NO_CROSS_STREAM: keep the tensor-core cross-attention for group == 1
   CUtensorMap tm_ckv;              // whole cross cache as [rows,64], box = 64 x ca_key_rows(S)

@@ -209,7 +209,7 @@ template <int BNB, bool kLN, typename Epi, int KSPLIT = 1>
 __global__ void __launch_bounds__(swap_threads(BNB, kLN), (kLN && BNB > 32) ? 1 : 2)
 gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CUtensorMap tm_x,
                  const __grid_constant__ CUtensorMap tm_w3, const __grid_constant__ CUtensorMap tm_x3, int whole_k,
-                 int kgrp, int M, int K, int stages, Epi epi, const __grid_constant__ SwapLNParams ln, const DecState* st) {
+                 int M, int K, int stages, Epi epi, const __grid_constant__ SwapLNParams ln, const DecState* st) {
   static_assert(BNB == 32 || BNB == 64 || BNB == 128, "BNB");
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -247,9 +247,7 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
     if (ptx::elect_one()) {
       ptx::prefetch_tensormap(&tm_w);
       ptx::prefetch_tensormap(&tm_x);
-      // grouped copies: a ring slot holds kgrp k-blocks and is released by every issuer's last k-block of the group
-      const uint32_t empty_cnt = kgrp > 1 ? (uint32_t)kIssuers : 1u;
-      for (int s = 0; s < stages; ++s) { ptx::mbar_init(&full[s], 1); ptx::mbar_init(&empty[s], empty_cnt); }
+      for (int s = 0; s < stages; ++s) { ptx::mbar_init(&full[s], 1); ptx::mbar_init(&empty[s], 1); }
       ptx::mbar_init(tmem_full, n_acc);  // one arrival per MMA issuer
       ptx::fence_barrier_init();
       // the weights do not depend on the previous kernel of the step: request the first ring of weight tiles now,
@@ -266,15 +264,6 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
           ptx::mbar_expect_tx(&full[hf], (kSwapWholeKB / 2) * kWBytes);
           ptx::tma_load_3d_hint(smem_w + (size_t)hf * (kSwapWholeKB / 2) * kWBytes, &tm_w3, &full[hf], 0, f0,
                                 kb0 + hf * (kSwapWholeKB / 2), keep);
-        }
-      } else if (kgrp > 1) {
-        // kgrp k-blocks per copy (3-D views, box depth kgrp): the TMA unit's throughput is ~2 x copy size / 650 cycles,
-        // so 16 KB per-k-block boxes kept the K = 2048 projection and the 128-row tiles waiting for their operands
-        ptx::prefetch_tensormap(&tm_w3);
-        ptx::prefetch_tensormap(&tm_x3);
-        for (int g = 0; g < n_pre / kgrp; ++g) {
-          ptx::mbar_expect_tx(&full[g], kgrp * (kWBytes + kXBytes));
-          ptx::tma_load_3d_hint(smem_w + (size_t)g * kgrp * kWBytes, &tm_w3, &full[g], 0, f0, kb0 + g * kgrp, keep);
         }
       } else {
         for (int kb = 0; kb < n_pre; ++kb) {
@@ -298,16 +287,8 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
   if (warp == 0) {       // the activation tiles are on the critical path: request them before anything else
     if (ptx::elect_one()) {  // (also when the rollout is over: the prologue's barriers must complete)
       if (whole_k) {
-        // whole_k = number of copies the activations arrive in (1, 2 or 4; tm_x3's box depth is 8 / whole_k):
-        // the MMAs of the first k-blocks start when the first part has landed
-        const int kbp = kSwapWholeKB / whole_k;
-        for (int j = 0; j < whole_k; ++j) {
-          ptx::mbar_expect_tx(&full[2 + j], kbp * kXBytes);
-          ptx::tma_load_3d(smem_x + (size_t)j * kbp * kXBytes, &tm_x3, &full[2 + j], 0, b0, kb0 + j * kbp);
-        }
-      } else if (kgrp > 1) {
-        for (int g = 0; g < n_pre / kgrp; ++g)
-          ptx::tma_load_3d(smem_x + (size_t)g * kgrp * kXBytes, &tm_x3, &full[g], 0, b0, kb0 + g * kgrp);
+        ptx::mbar_expect_tx(&full[2], kSwapWholeKB * kXBytes);
+        ptx::tma_load_3d(smem_x, &tm_x3, &full[2], 0, b0, kb0);
       } else {
         for (int kb = 0; kb < n_pre; ++kb)
           ptx::tma_load_2d(smem_x + (size_t)kb * kXBytes, &tm_x, &full[kb], (kb0 + kb) * kSwapBK, b0);
@@ -321,21 +302,7 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
 
   if (warp == 0) {
     if (whole_k) {
-      if (!active) for (int j = 0; j < 2 + whole_k; ++j) ptx::mbar_wait(&full[j], 0);  // no copy may outlive the CTA
-    } else if (active && kgrp > 1) {
-      const uint64_t keep = ptx::policy_evict_last();
-      const int ng = stages / kgrp;  // ring slots
-      for (int g = n_pre / kgrp; g < num_kb / kgrp; ++g) {
-        const int slot = g % ng;
-        const uint32_t ph = (g / ng) & 1;
-        ptx::mbar_wait(&empty[slot], ph ^ 1);
-        if (ptx::elect_one()) {
-          ptx::mbar_expect_tx(&full[slot], kgrp * (kWBytes + kXBytes));
-          ptx::tma_load_3d_hint(smem_w + (size_t)slot * kgrp * kWBytes, &tm_w3, &full[slot], 0, f0, kb0 + g * kgrp, keep);
-          ptx::tma_load_3d(smem_x + (size_t)slot * kgrp * kXBytes, &tm_x3, &full[slot], 0, b0, kb0 + g * kgrp);
-        }
-        __syncwarp();
-      }
+      if (!active) { ptx::mbar_wait(&full[0], 0); ptx::mbar_wait(&full[1], 0); ptx::mbar_wait(&full[2], 0); }  // no copy may outlive the CTA
     } else if (active) {
       const uint64_t keep = ptx::policy_evict_last();
       for (int kb = n_pre; kb < num_kb; ++kb) {
@@ -350,7 +317,7 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
         __syncwarp();
       }
     } else {
-      for (int kb = 0; kb < n_pre / (kgrp > 1 ? kgrp : 1); ++kb) ptx::mbar_wait(&full[kb], 0);  // no copy may outlive the CTA
+      for (int kb = 0; kb < n_pre; ++kb) ptx::mbar_wait(&full[kb], 0);  // no copy may outlive the CTA
     }
     __syncwarp();
     if (kLN) { ptx::cluster_wait(); ptx::cluster_arrive(); ptx::cluster_wait(); }
@@ -361,13 +328,11 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
       const int first = warp == 1 ? 0 : warp - kIssuer2 + 1;  // this issuer's k-blocks: first, first + kIssuers, ...
       const uint32_t acc = tmem_base + (uint32_t)(first * BNB);
       const uint32_t w_lo0 = ptx::umma_desc_lo(ptx::smem_u32(smem_w)), x_lo0 = ptx::umma_desc_lo(ptx::smem_u32(smem_x));
-      const int ng = kgrp > 1 ? stages / kgrp : 1;
+      if (whole_k) ptx::mbar_wait(&full[2], 0);  // the activations
       for (int kb = first; kb < num_kb; kb += kIssuers) {
-        const int grp = kgrp > 1 ? kb / kgrp : 0, slot = grp % ng;  // grouped copies: ring slot of this k-block's group
-        const int s = whole_k ? kb : (kgrp > 1 ? slot * kgrp + kb % kgrp : kb % stages);
-        const uint32_t ph = whole_k ? 0u : (uint32_t)(((kgrp > 1 ? grp / ng : kb / stages)) & 1);
-        if (whole_k) ptx::mbar_wait(&full[2 + kb / (kSwapWholeKB / whole_k)], 0);  // this k-block's part of the activations
-        ptx::mbar_wait(&full[whole_k ? kb / (kSwapWholeKB / 2) : (kgrp > 1 ? slot : s)], ph);
+        const int s = whole_k ? kb : kb % stages;
+        const uint32_t ph = whole_k ? 0u : (uint32_t)((kb / stages) & 1);
+        ptx::mbar_wait(&full[whole_k ? kb / (kSwapWholeKB / 2) : s], ph);
         ptx::tc_fence_after();
         if (ptx::elect_one()) {
           if (!kLN && trace_cta && kb == 0) reinterpret_cast<long long*>(red)[1] = clock64();  // first tile landed
@@ -376,11 +341,7 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
 #pragma unroll
           for (int k = 0; k < kSwapBK / 16; ++k)  // 16 bf16 = 32 bytes along K inside the swizzle atom
             ptx::umma_f16_lohi(acc, w_lo + k * 2, x_lo + k * 2, idesc, (kb != first || k != 0) ? 1u : 0u);
-          if (kgrp > 1) {
-            if (kb % kgrp + kIssuers >= kgrp) ptx::umma_commit(&empty[slot]);  // this issuer's last k-block of the group
-          } else if (!whole_k) {
-            ptx::umma_commit(&empty[s]);  // (no ring reuse in a whole-K launch)
-          }
+          if (!whole_k) ptx::umma_commit(&empty[s]);  // (no ring reuse in a whole-K launch)
           if (kb + kIssuers >= num_kb) ptx::umma_commit(tmem_full);  // same thread as the MMAs it tracks
           if (!kLN && trace_cta && kb == num_kb - 1) reinterpret_cast<long long*>(red)[2] = clock64();  // all issued
         }

@@ -312,27 +312,6 @@ def test_v2_vocab_head_rows_per_warp(dev, monkeypatch, rw):
     assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1]) and torch.equal(outs[0][2], outs[1][2])
 
 
-@pytest.mark.parametrize("bnb", [32, 64, 128])
-def test_v2_grouped_k_copies(dev, monkeypatch, bnb):
-    """CAPDEC_KGROUP=1: several k-blocks per TMA copy (3-D views, ring slots of 2 or 4 k-blocks released by every
-    MMA issuer) where whole-K copies do not apply: the K = 2048 LayerNorm GEMM at every tile width and the K = 512
-    GEMMs of 128-row tiles.  Same products in the same order as the per-k-block ring: identical results."""
-    monkeypatch.setenv("CAPDEC_BNB", str(bnb))
-    monkeypatch.setenv("CAPDEC_NO_FFN2_SPLIT", "1")
-    dec = small_decoder(layers=2, end_bias=1.0)
-    w = torch_port.weights_to_numpy(dec)
-    mem = torch_port.synthetic_memory(75, 49)
-    outs = []
-    for on in ("0", "1"):
-        monkeypatch.setenv("CAPDEC_KGROUP", on)
-        eng = make_engine(dec.to(dev), "bf16", step_impl="v2", max_images=75, max_group=2, max_mem=49, max_len=10)
-        out = eng.decode_from_memory(mem.to(dev), START, END, max_len=10, group=2, n_sample=1, seed=3, return_logits=True)
-        check_rollout(out, w, mem.numpy(), 2, 1, TOL["bf16"], seed=3)
-        outs.append((out.ids.cpu(), out.logits.cpu()))
-        eng.close()
-    assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
-
-
 @pytest.mark.parametrize("n_img", [5, 130])
 def test_v2_ffn2_split_k_closes_itself(dev, monkeypatch, n_img):
     """Small batches run FFN2 as 4 k-slices whose last CTA per row tile (ticket counter) sums the slices and applies
