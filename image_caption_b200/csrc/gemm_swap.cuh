@@ -305,9 +305,12 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
       if (!active) { ptx::mbar_wait(&full[0], 0); ptx::mbar_wait(&full[1], 0); ptx::mbar_wait(&full[2], 0); }  // no copy may outlive the CTA
     } else if (active) {
       const uint64_t keep = ptx::policy_evict_last();
-      for (int kb = n_pre; kb < num_kb; ++kb) {
-        const int s = kb % stages;
-        const uint32_t ph = (kb / stages) & 1;
+      // ring slot and phase advance by counters: `stages` is a run-time value, and a division per k-block in this
+      // loop (and in the issue loop below) is latency on the way to the first MMA of the block
+      int s = n_pre % stages;      // n_pre == stages (wraps to 0) or num_kb < stages (loop does not run)
+      uint32_t ph = n_pre >= stages ? 1u : 0u;
+      for (int kb = n_pre; kb < num_kb; ++kb, ++s) {
+        if (s == stages) { s = 0; ph ^= 1u; }
         ptx::mbar_wait(&empty[s], ph ^ 1);
         if (ptx::elect_one()) {
           ptx::mbar_expect_tx(&full[s], kWBytes + kXBytes);
@@ -329,9 +332,10 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
       const uint32_t acc = tmem_base + (uint32_t)(first * BNB);
       const uint32_t w_lo0 = ptx::umma_desc_lo(ptx::smem_u32(smem_w)), x_lo0 = ptx::umma_desc_lo(ptx::smem_u32(smem_x));
       if (whole_k) ptx::mbar_wait(&full[2], 0);  // the activations
-      for (int kb = first; kb < num_kb; kb += kIssuers) {
-        const int s = whole_k ? kb : kb % stages;
-        const uint32_t ph = whole_k ? 0u : (uint32_t)((kb / stages) & 1);
+      int s = first;  // ring slot of this issuer's next k-block (whole-K launches: slot == k-block, no reuse)
+      uint32_t ph = 0u;
+      for (int kb = first; kb < num_kb; kb += kIssuers, s += kIssuers) {
+        if (!whole_k) while (s >= stages) { s -= stages; ph ^= 1u; }
         ptx::mbar_wait(&full[whole_k ? kb / (kSwapWholeKB / 2) : s], ph);
         ptx::tc_fence_after();
         if (ptx::elect_one()) {
