@@ -146,6 +146,39 @@ def run_reference_arm(args) -> None:
     print(json.dumps(line), flush=True)
 
 
+def run_torch_gpu_arm(args) -> None:
+    """Not part of the driver's contract: the reference's own loop (no KV cache, eager PyTorch fp32, oracle/torch_port)
+    on ONE B200 over the whole workload -- SURVEY 8d's "real bar to beat".  Device time, CUDA events."""
+    import torch
+    from oracle import torch_port
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    desc, n_img, S, G, ns, max_len = WORKLOADS[args.workload]
+    if args.images:
+        n_img = args.images
+    dev = torch.device("cuda", 0)
+    dec = torch_port.build_decoder(0, max_len=max(52, max_len)).to(dev)
+    mem = torch_port.synthetic_memory(n_img, S).to(dev)
+    mem = mem.repeat_interleave(G, 0) if G > 1 else mem
+    times = []
+    for i in range(args.warmup + args.steps):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        ids = torch_port.greedy_recompute(dec, mem, START, END, max_len)
+        e1.record()
+        torch.cuda.synchronize()
+        if i >= args.warmup:
+            times.append(e0.elapsed_time(e1))
+    assert ids.shape[1] == max_len
+    ms = sum(times) / len(times)
+    print(json.dumps({"impl": "torch_eager_gpu", "metric": "captions/s", "value": mem.shape[0] / (ms * 1e-3), "unit": "captions/s",
+                      "n_gpus": 1, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
+                      "dtype": "f32", "data": "synthetic", "decode_step_us": 1e3 * ms / (max_len - 1),
+                      "config": {"workload": f"{args.workload}: {desc}", "sequences": mem.shape[0], "mem_len": S, "max_len": max_len,
+                                 "note": f"reference no-KV-cache loop, eager torch {torch.__version__} fp32 on one B200, "
+                                         "greedy for every sequence (sampling costs the same decoder calls)"}}), flush=True)
+
+
 # --------------------------------------------------------------------------- B200 arm
 def run_b200_arm(args) -> None:
     import torch
@@ -298,7 +331,7 @@ def main() -> None:
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference", "torch_gpu"])
     ap.add_argument("--workload", default="cfg2", choices=sorted(WORKLOADS))
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
@@ -310,6 +343,8 @@ def main() -> None:
         args.warmup = 3
     if args.impl == "reference":
         run_reference_arm(args)
+    elif args.impl == "torch_gpu":
+        run_torch_gpu_arm(args)
     else:
         run_b200_arm(args)
 
