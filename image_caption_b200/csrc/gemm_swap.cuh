@@ -331,25 +331,48 @@ gemm_swap_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
       const int first = warp == 1 ? 0 : warp - kIssuer2 + 1;  // this issuer's k-blocks: first, first + kIssuers, ...
       const uint32_t acc = tmem_base + (uint32_t)(first * BNB);
       const uint32_t w_lo0 = ptx::umma_desc_lo(ptx::smem_u32(smem_w)), x_lo0 = ptx::umma_desc_lo(ptx::smem_u32(smem_x));
-      if (whole_k) ptx::mbar_wait(&full[2], 0);  // the activations
-      int s = first;  // ring slot of this issuer's next k-block (whole-K launches: slot == k-block, no reuse)
-      uint32_t ph = 0u;
-      for (int kb = first; kb < num_kb; kb += kIssuers, s += kIssuers) {
-        if (!whole_k) while (s >= stages) { s -= stages; ph ^= 1u; }
-        ptx::mbar_wait(&full[whole_k ? kb / (kSwapWholeKB / 2) : s], ph);
+      if (whole_k) {
+        // Whole K resident: one straight run of MMAs with compile-time descriptor offsets.  The per-k-block loop below
+        // spends ~550 cycles per iteration of this warp (barrier poll, fence, election, descriptor arithmetic in the
+        // uniform datapath) against ~160 cycles of tensor pipe for its four N = 32 MMAs.
+        ptx::mbar_wait(&full[0], 0);  // the weight halves were requested in the prologue, before the dependency wait
+        ptx::mbar_wait(&full[1], 0);
+        ptx::mbar_wait(&full[2], 0);  // the activations
         ptx::tc_fence_after();
         if (ptx::elect_one()) {
-          if (!kLN && trace_cta && kb == 0) reinterpret_cast<long long*>(red)[1] = clock64();  // first tile landed
-          const uint32_t w_lo = w_lo0 + (uint32_t)s * (kWBytes >> 4);  // descriptor low words: address >> 4
-          const uint32_t x_lo = x_lo0 + (uint32_t)s * (kXBytes >> 4);
+          if (!kLN && trace_cta && first == 0) reinterpret_cast<long long*>(red)[1] = clock64();  // first tile landed
+          const uint32_t w_lo = w_lo0 + (uint32_t)first * (kWBytes >> 4);  // descriptor low words: address >> 4
+          const uint32_t x_lo = x_lo0 + (uint32_t)first * (kXBytes >> 4);
 #pragma unroll
-          for (int k = 0; k < kSwapBK / 16; ++k)  // 16 bf16 = 32 bytes along K inside the swizzle atom
-            ptx::umma_f16_lohi(acc, w_lo + k * 2, x_lo + k * 2, idesc, (kb != first || k != 0) ? 1u : 0u);
-          if (!whole_k) ptx::umma_commit(&empty[s]);  // (no ring reuse in a whole-K launch)
-          if (kb + kIssuers >= num_kb) ptx::umma_commit(tmem_full);  // same thread as the MMAs it tracks
-          if (!kLN && trace_cta && kb == num_kb - 1) reinterpret_cast<long long*>(red)[2] = clock64();  // all issued
+          for (int i = 0; i < kSwapWholeKB / kIssuers; ++i)  // k-blocks first, first + kIssuers, ...
+#pragma unroll
+            for (int k = 0; k < kSwapBK / 16; ++k)  // 16 bf16 = 32 bytes along K inside the swizzle atom
+              ptx::umma_f16_lohi(acc, w_lo + (uint32_t)(i * kIssuers) * (kWBytes >> 4) + k * 2,
+                                 x_lo + (uint32_t)(i * kIssuers) * (kXBytes >> 4) + k * 2, idesc, (i != 0 || k != 0) ? 1u : 0u);
+          ptx::umma_commit(tmem_full);  // same thread as the MMAs it tracks
+          if (!kLN && trace_cta && first == kIssuers - 1) reinterpret_cast<long long*>(red)[2] = clock64();  // all issued
         }
         __syncwarp();
+      } else {
+        int s = first;  // ring slot of this issuer's next k-block
+        uint32_t ph = 0u;
+        for (int kb = first; kb < num_kb; kb += kIssuers, s += kIssuers) {
+          while (s >= stages) { s -= stages; ph ^= 1u; }
+          ptx::mbar_wait(&full[s], ph);
+          ptx::tc_fence_after();
+          if (ptx::elect_one()) {
+            if (!kLN && trace_cta && kb == 0) reinterpret_cast<long long*>(red)[1] = clock64();  // first tile landed
+            const uint32_t w_lo = w_lo0 + (uint32_t)s * (kWBytes >> 4);  // descriptor low words: address >> 4
+            const uint32_t x_lo = x_lo0 + (uint32_t)s * (kXBytes >> 4);
+#pragma unroll
+            for (int k = 0; k < kSwapBK / 16; ++k)  // 16 bf16 = 32 bytes along K inside the swizzle atom
+              ptx::umma_f16_lohi(acc, w_lo + k * 2, x_lo + k * 2, idesc, (kb != first || k != 0) ? 1u : 0u);
+            ptx::umma_commit(&empty[s]);
+            if (kb + kIssuers >= num_kb) ptx::umma_commit(tmem_full);  // same thread as the MMAs it tracks
+            if (!kLN && trace_cta && kb == num_kb - 1) reinterpret_cast<long long*>(red)[2] = clock64();  // all issued
+          }
+          __syncwarp();
+        }
       }
     }
     __syncwarp();

@@ -1,4 +1,6 @@
-timeout 300 python bench.py --impl torch_gpu --workload cfg2 --steps 3 --warmup 1 2>/dev/null | tee gpurun_out/torch_gpu_cfg2.json | cut -c1-250
-timeout 600 python bench.py --impl torch_gpu --workload cfg3 --steps 1 --warmup 1 2>/dev/null | tee gpurun_out/torch_gpu_cfg3.json | cut -c1-250
-timeout 300 python bench.py --impl torch_gpu --workload vit_greedy --images 8 --steps 3 --warmup 1 2>/dev/null | tee gpurun_out/torch_gpu_vit8.json | cut -c1-250
-timeout 300 python bench.py --impl reference --steps 2 --warmup 1 2>/dev/null | tee gpurun_out/ref_cfg2.json | cut -c1-300
+for w in cfg2 cfg5 cfg3; do for v in prev new prev new; do
+if [ $v = prev ]; then export CAPDEC_LIB=$PWD/build/lib_prev.so; else unset CAPDEC_LIB; fi
+timeout 200 python tools/step_time.py $w --variants v2 --reps 7 2>&1 | tail -1 | sed "s/^/$v /"
+done; done
+unset CAPDEC_LIB
+timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -3
