@@ -1210,6 +1210,7 @@ extern "C" int capdec_decode(capdec_handle h, const capdec_decode_args* a, void*
   cp.end_token = a->end_token;
   cp.pad_token = a->pad_token;
   cp.no_early_stop = (a->flags & CAPDEC_DECODE_NO_EARLY_STOP) ? 1 : 0;
+  cp.vocab = h->cfg.vocab;
   cp.forced = (a->flags & CAPDEC_DECODE_TEACHER_FORCED) ? 1 : 0;
   if (cp.forced && mega_applicable(h, n_images, S, group))
     return fail(h, CAPDEC_ERR_INVALID, "teacher forcing is not built into the cluster rollout (step_impl v3)");
@@ -1303,6 +1304,7 @@ extern "C" int capdec_beam_search(capdec_handle h, const capdec_beam_args* a, vo
   cp.end_token = a->end_token;
   cp.pad_token = a->pad_token;
   cp.n_greedy_rows = M;
+  cp.vocab = V;
   CUDA_TRY(h, cudaMemcpyAsync(h->cp, &cp, sizeof cp, cudaMemcpyHostToDevice, s));
   init_rollout_kernel<<<std::min((M * a->max_len + 255) / 256, 1024), 256, 0, s>>>(h->st, h->cp, h->fin, M, h->counters);
   beam_init_kernel<<<std::min((2 * M * h->t_pad + 255) / 256, 1024), 256, 0, s>>>(h->beam, h->cp, n_images, beam, h->t_pad);

@@ -40,6 +40,7 @@ struct CallParams {
   int start_token, end_token, pad_token;
   int n_greedy_rows, n_sample_rows;
   int no_early_stop;
+  int vocab;               // rows of the embedding table
   int forced;              // teacher forcing: ids holds the whole sequence, the head scores ids[:, n+1] instead of picking
 };
 

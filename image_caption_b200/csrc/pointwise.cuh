@@ -10,6 +10,9 @@
 
 namespace capdec {
 
+// teacher forcing reads caller-supplied token ids: an id outside the vocabulary must not become an out-of-bounds read
+__device__ __forceinline__ int clamp_token(long long t, int vocab) { return t < 0 ? 0 : (t >= vocab ? vocab - 1 : (int)t); }
+
 __global__ void init_rollout_kernel(DecState* st, const CallParams* cp, unsigned char* fin, int M, int* counters) {
   const CallParams p = *cp;
   const int tid = blockIdx.x * blockDim.x + threadIdx.x;
@@ -42,7 +45,8 @@ __global__ void embed_pe_kernel(const DecState* st, const CallParams* cp, const 
   const int m = idx / (kD / 4), c = (idx % (kD / 4)) * 4;
   const int n = st->step;
   if (n >= cp->max_len - 1) return;  // launched after the last step's head (v2 beam search): no next position
-  const long long tok = cp->ids[(size_t)m * cp->max_len + n];
+  long long tok = cp->ids[(size_t)m * cp->max_len + n];
+  if (cp->forced) tok = clamp_token(tok, cp->vocab);  // caller-supplied sequence (teacher forcing): never index outside the table
   const float4 e = __ldg(reinterpret_cast<const float4*>(emb + (size_t)tok * kD + c));
   const float4 p = __ldg(reinterpret_cast<const float4*>(pe + (size_t)n * kD + c));
   const float sc = 22.627416997969522f;  // sqrt(512) rounded to fp32, as torch does for the scalar
@@ -192,7 +196,7 @@ head_kernel(DecState* st, const CallParams* cp, const float* __restrict__ logits
     const bool sample = (m % p.group) < p.n_sample;
     const float u = sample ? philox_uniform(p.seed, p.seq_id_base + (unsigned long long)m, n) : 0.f;
     float lp;
-    const int forced = p.forced ? (int)p.ids[(size_t)m * p.max_len + n + 1] : -1;
+    const int forced = p.forced ? clamp_token(p.ids[(size_t)m * p.max_len + n + 1], V) : -1;
     const int tok = warp_pick(l, lane, sample, u, V, &lp, forced);
     if (lane == 0) {
       if (!p.forced) p.ids[(size_t)m * p.max_len + n + 1] = tok;
@@ -338,7 +342,7 @@ vocab_head_kernel(DecState* st, const CallParams* cp, float* __restrict__ x, con
       const bool sample = (m % p.group) < p.n_sample;
       const float u = sample ? philox_uniform(p.seed, p.seq_id_base + (unsigned long long)m, n) : 0.f;
       float lp;
-      const int forced = p.forced ? (int)p.ids[(size_t)m * p.max_len + n + 1] : -1;
+      const int forced = p.forced ? clamp_token(p.ids[(size_t)m * p.max_len + n + 1], V) : -1;
       const int tok = warp_pick(l, lane, sample, u, V, &lp, forced);
       if (lane == 0) {
         if (!p.forced) p.ids[(size_t)m * p.max_len + n + 1] = tok;
