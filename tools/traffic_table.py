@@ -3,9 +3,9 @@
     python tools/traffic_table.py"""
 import csv, json, os
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-out = {"_source": "profiles/r01_v2_ncu_full_cfg2.csv, r01_v2_ncu_full_cfg3.csv (ncu --set full --clock-control none, one decode "
+out = {"_source": "profiles/r01_v2_ncu_full_cfg{2,3,5}.csv (ncu --set full --clock-control none, one decode "
                   "step; dram__bytes_read.sum + dram__bytes_write.sum per launch, median over the step's launches of that kernel)"}
-for w in ("cfg2", "cfg3"):
+for w in ("cfg2", "cfg3", "cfg5"):
     rows = list(csv.reader(open(os.path.join(ROOT, "profiles", f"r01_v2_ncu_full_{w}.csv"))))
     h = rows[0]
     ir = [i for i, x in enumerate(h) if x.startswith("dram__bytes_read")][0]
