@@ -1,18 +1,25 @@
 #!/usr/bin/env python
 """bench.py - captions/s of batched caption decoding on B200 (BASELINE.json metric).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload cfg2|cfg3|cfg5|vit_greedy]
-                    [--precision bf16|fp32] [--impl b200|reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload auto|cfg2|cfg3|cfg4|cfg5|vit_greedy]
+                    [--precision bf16|fp32] [--impl b200|reference|torch_gpu] [--no-sub] [--no-verify]
 
-A "step" is one whole rollout of the hot path over one batch: cross-K/V prefill plus
-max_len-1 decode steps (BASELINE.json configs).  Default workload = configs[1]
-(Grid 7x7 + Transformer greedy, 256 images, max_len 50) per GPU, weak scaling.
+A "step" is one whole rollout of the hot path over one batch: cross-K/V prefill plus max_len-1 decode
+steps (BASELINE.json configs).
 
-Prints ONE JSON line (rank 0).  `value` = captions/s with the encoder memory already resident in
-HBM; `e2e` = the same through the host-buffer C-ABI call (pinned host memory in, token ids out,
-copies inside the timed region); `roofline` = the dominant kernel (per-launch CUDA events from
-the engine's profiling pass); `cpu_baseline` = the reference's no-KV-cache loop on the host cores.
-`--impl reference` times only that CPU loop (the reference ships no GPU kernels of its own).
+Default workload (``auto``):
+  * 1 GPU  -> cfg3, the largest single-GPU configuration (ViT + Transformer SCST rollout: 512 images x
+    (5 samples + greedy), S = 196, max_len 50); cfg2, the cfg5 per-GPU shape, an fp32-mode run and the
+    reference loop in eager PyTorch on the same B200 go into the same JSON line as ``sub`` records.
+  * N GPUs -> cfg4 = the SAME 512-image global batch and seed sharded 512/N images per rank
+    (``scaling: strong``), gathered by the path's one collective and verified bit-equal against an
+    unsharded rollout on rank 0; cfg5 (1024 images per GPU) and cfg2 go in as weak-scaled ``sub`` records.
+
+Prints ONE JSON line (rank 0).  ``value`` = captions/s with the encoder memory already resident in HBM;
+``e2e`` = the same through the host-buffer entry points (pinned host memory in, token ids / log-probs back
+on the host, copies inside the timed region); ``roofline`` = the dominant kernel (per-launch CUDA events
+from the engine's profiling pass); ``cpu_baseline`` = the reference's no-KV-cache loop on the host cores.
+``--impl reference`` times only that CPU loop on the same ``config`` (the reference ships no GPU kernels).
 """
 from __future__ import annotations
 
@@ -34,12 +41,45 @@ P_STEP = 22_128_237      # parameters read by every decode step
 P_PREFILL = 3_151_872    # cross K/V projection parameters (prefill only)
 
 WORKLOADS = {
-    # name: (description, images per GPU, S, group, n_sample, max_len)
-    "cfg2": ("Grid(ResNet 7x7)+Transformer greedy decode, batch 256, max_len 50", 256, 49, 1, 0, 50),
-    "cfg3": ("ViT+Transformer SCST rollout, 512 images x (5 samples + greedy), max_len 50", 512, 196, 6, 5, 50),
-    "cfg5": ("Grid+Transformer greedy, 1024 images per GPU (8192 over 8), max_len 64", 1024, 49, 1, 0, 64),
-    "vit_greedy": ("ViT+Transformer greedy decode, batch 512, max_len 50", 512, 196, 1, 0, 50),
+    # name: (description, images, S, group, n_sample, max_len, scaling); images = per GPU (weak) or global (strong)
+    "cfg2": ("Grid(ResNet 7x7)+Transformer greedy decode, batch 256, max_len 50", 256, 49, 1, 0, 50, "weak"),
+    "cfg3": ("ViT+Transformer SCST rollout, 512 images x (5 samples + greedy), max_len 50", 512, 196, 6, 5, 50, "weak"),
+    "cfg4": ("ViT+Transformer SCST rollout, 512 images x (5 samples + greedy) sharded over the GPUs, max_len 50",
+             512, 196, 6, 5, 50, "strong"),
+    "cfg5": ("Grid+Transformer greedy, 1024 images per GPU (8192 over 8), max_len 64", 1024, 49, 1, 0, 64, "weak"),
+    "vit_greedy": ("ViT+Transformer greedy decode, batch 512, max_len 50", 512, 196, 1, 0, 50, "weak"),
 }
+CPU_SAMPLE = {"cfg2": 8, "cfg3": 4, "cfg4": 4, "cfg5": 8, "vit_greedy": 8}  # images in the bounded CPU sample
+
+
+def pick_workload(name: str, world: int) -> str:
+    if name != "auto":
+        return name
+    return "cfg3" if world == 1 else "cfg4"
+
+
+def shard_images(name: str, world: int, rank: int, images_override: int = 0):
+    """(first image, images on this rank, images in the global batch)."""
+    from image_caption_b200.dist import shard_bounds
+    desc, n_img, S, G, ns, max_len, scaling = WORKLOADS[name]
+    if images_override:
+        n_img = images_override
+    if scaling == "strong":
+        lo, hi = shard_bounds(n_img, world, rank)
+        return lo, hi - lo, n_img
+    return rank * n_img, n_img, world * n_img
+
+
+def workload_config(name: str, world: int, precision: str, images_override: int = 0) -> dict:
+    """The ``config`` object: identical in the product arm and in the reference arm."""
+    desc, n_img, S, G, ns, max_len, scaling = WORKLOADS[name]
+    if images_override:
+        n_img = images_override
+    n_global = n_img if scaling == "strong" else n_img * world
+    return {"workload": f"{name}: {desc}", "images_global": n_global, "images_per_gpu": n_global // world, "mem_len": S,
+            "group": G, "n_sample": ns, "max_len": max_len, "sequences_global": n_global * G, "decode_steps": max_len - 1,
+            "n_gpus": world, "scaling": scaling, "weights": "random init, torch.manual_seed(0)",
+            "memory": "randn(images, S, 512), torch.Generator().manual_seed(1234)"}
 
 
 def algorithmic_bytes(n_img: int, S: int, G: int, max_len: int, e: int) -> dict:
@@ -88,57 +128,59 @@ class ClockSampler:
                 sm.append(float(f[0])); mx.append(float(f[1]))
             except ValueError:
                 continue
-            for name, v in zip(names, f[3:7]):
+            for nm, v in zip(names, f[3:7]):
                 if v.lower().startswith("active"):
-                    reasons.add(name)
+                    reasons.add(nm)
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
 # --------------------------------------------------------------------------- CPU reference arm
-def cpu_reference(workload: str, steps: int, warmup: int, sample_images: int):
-    """The reference's own algorithm (vit:307-323: full decoder over the whole prefix at every step,
-    memory re-projected every call) on the host cores, on the first ``sample_images`` images of the
-    workload.  /root/reference is absent on the GPU box, so the timed code is oracle/torch_port
-    (same torch.nn modules, same loop)."""
+def cpu_reference(name: str, steps: int, warmup: int, sample_images: int):
+    """The reference's own algorithm (vit:307-323: full decoder over the whole prefix at every step, memory
+    re-projected every call) on the host cores, on the first ``sample_images`` images of the workload's global batch,
+    all rollouts of those images, all decode steps.  /root/reference is absent on the GPU box, so the timed code is
+    oracle/torch_port (the same torch.nn modules in the same loop).  At least one un-timed warm-up run."""
     import torch
     from oracle import torch_port
-    desc, n_img, S, G, ns, max_len = WORKLOADS[workload]
+    desc, n_img, S, G, ns, max_len, scaling = WORKLOADS[name]
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
     dec = torch_port.build_decoder(0, max_len=max(52, max_len))
     mem = torch_port.synthetic_memory(sample_images, S)
     mem = mem.repeat_interleave(G, 0) if G > 1 else mem  # the reference decodes each rollout separately
     times = []
-    for i in range(warmup + steps):
+    for i in range(max(1, warmup) + steps):
         t0 = time.perf_counter()
         ids = torch_port.greedy_recompute(dec, mem, START, END, max_len)
         dt = time.perf_counter() - t0
-        if i >= warmup:
+        if i >= max(1, warmup):
             times.append(dt)
     assert ids.shape[1] == max_len
     caps = mem.shape[0]
     sec = sum(times) / len(times)
     return {"value": caps / sec, "unit": "captions/s", "cores": cores, "kind": "port",
-            "sample": f"first {sample_images} of {n_img} images x {G} rollouts, all {max_len - 1} steps, "
-                      f"reference no-KV-cache loop (oracle/torch_port.greedy_recompute), torch {torch.__version__} "
-                      f"fp32, {cores} threads, mean of {len(times)}",
+            "sample": f"first {sample_images} images x {G} rollouts of the workload's batch, all {max_len - 1} decode steps, "
+                      f"reference no-KV-cache loop (oracle/torch_port.greedy_recompute), torch {torch.__version__} fp32, "
+                      f"{cores} threads, {max(1, warmup)} warm-up + mean of {len(times)} runs",
             "sec_per_sample": sec, "ms_per_decode_step": 1e3 * sec / (max_len - 1)}
 
 
 def run_reference_arm(args) -> None:
     rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
     if rank != 0:
         return
-    desc, n_img, S, G, ns, max_len = WORKLOADS[args.workload]
-    r = cpu_reference(args.workload, args.steps, args.warmup, args.cpu_sample)
+    name = pick_workload(args.workload, world)
+    desc, n_img, S, G, ns, max_len, scaling = WORKLOADS[name]
+    r = cpu_reference(name, args.steps, args.warmup, args.cpu_sample or CPU_SAMPLE[name])
     line = {
         "impl": "reference", "metric": "captions/s", "value": r["value"], "unit": "captions/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": 1e3 * r["sec_per_sample"], "higher_is_better": True, "scaling": "weak",
+        "ms_per_step": 1e3 * r["sec_per_sample"], "higher_is_better": True, "scaling": scaling,
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"{args.workload}: {desc}", "images_per_gpu": n_img, "mem_len": S, "group": G,
-                   "max_len": max_len, "note": "CPU reference arm: bounded sample, see cpu_baseline.sample"},
+        "config": workload_config(name, world, args.precision, args.images),
+        "sample": r["sample"],
         "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
         "e2e": {"value": r["value"], "unit": "captions/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0, "decode_step_us": 1e3 * r["ms_per_decode_step"],
@@ -146,80 +188,105 @@ def run_reference_arm(args) -> None:
     print(json.dumps(line), flush=True)
 
 
-def run_torch_gpu_arm(args) -> None:
-    """Not part of the driver's contract: the reference's own loop (no KV cache, eager PyTorch fp32, oracle/torch_port)
-    on ONE B200 over the whole workload -- SURVEY 8d's "real bar to beat".  Device time, CUDA events."""
+def torch_eager_gpu(name: str, steps: int, warmup: int, local: int, images_override: int = 0) -> dict:
+    """The reference's own loop (no KV cache, eager PyTorch fp32, oracle/torch_port) on ONE B200 over the whole
+    workload -- SURVEY 8d's "real bar to beat".  Device time (CUDA events), clocks sampled during the timed runs."""
     import torch
     from oracle import torch_port
-    if int(os.environ.get("RANK", "0")) != 0:
-        return
-    desc, n_img, S, G, ns, max_len = WORKLOADS[args.workload]
-    if args.images:
-        n_img = args.images
-    dev = torch.device("cuda", 0)
+    desc, n_img, S, G, ns, max_len, scaling = WORKLOADS[name]
+    if images_override:
+        n_img = images_override
+    dev = torch.device("cuda", local)
     dec = torch_port.build_decoder(0, max_len=max(52, max_len)).to(dev)
     mem = torch_port.synthetic_memory(n_img, S).to(dev)
     mem = mem.repeat_interleave(G, 0) if G > 1 else mem
+    for _ in range(warmup):
+        torch_port.greedy_recompute(dec, mem, START, END, max_len)
+    torch.cuda.synchronize(dev)
+    clocks = ClockSampler(local)
     times = []
-    for i in range(args.warmup + args.steps):
+    for _ in range(steps):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         ids = torch_port.greedy_recompute(dec, mem, START, END, max_len)
         e1.record()
-        torch.cuda.synchronize()
-        if i >= args.warmup:
-            times.append(e0.elapsed_time(e1))
+        torch.cuda.synchronize(dev)
+        times.append(e0.elapsed_time(e1))
+    clk = clocks.stop()
     assert ids.shape[1] == max_len
     ms = sum(times) / len(times)
-    print(json.dumps({"impl": "torch_eager_gpu", "metric": "captions/s", "value": mem.shape[0] / (ms * 1e-3), "unit": "captions/s",
-                      "n_gpus": 1, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
-                      "dtype": "f32", "data": "synthetic", "decode_step_us": 1e3 * ms / (max_len - 1),
-                      "config": {"workload": f"{args.workload}: {desc}", "sequences": mem.shape[0], "mem_len": S, "max_len": max_len,
-                                 "note": f"reference no-KV-cache loop, eager torch {torch.__version__} fp32 on one B200, "
-                                         "greedy for every sequence (sampling costs the same decoder calls)"}}), flush=True)
+    del dec, mem
+    torch.cuda.empty_cache()
+    return {"impl": "torch_eager_gpu", "metric": "captions/s", "value": n_img * G / (ms * 1e-3), "unit": "captions/s",
+            "n_gpus": 1, "steps": steps, "warmup": warmup, "ms_per_step": ms, "dtype": "f32",
+            "decode_step_us": 1e3 * ms / (max_len - 1), "clocks": clk, "sequences": n_img * G,
+            "note": f"reference no-KV-cache loop (oracle/torch_port.greedy_recompute), eager torch {torch.__version__} fp32 on "
+                    "one B200, greedy for every sequence (sampling costs the same decoder calls)"}
+
+
+def run_torch_gpu_arm(args) -> None:
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    name = pick_workload(args.workload, 1)
+    r = torch_eager_gpu(name, args.steps, max(1, args.warmup), 0, args.images)
+    r.update(higher_is_better=True, data="synthetic", config=workload_config(name, 1, "fp32", args.images))
+    print(json.dumps(r), flush=True)
 
 
 # --------------------------------------------------------------------------- B200 arm
-def run_b200_arm(args) -> None:
+def measure(name: str, precision: str, steps: int, warmup: int, world: int, rank: int, local: int, images_override: int = 0,
+            profile: bool = True, verify: bool = False) -> dict:
+    """Time one workload on this process group; returns the record (complete on rank 0)."""
     import torch
     import torch.distributed as dist
     from image_caption_b200 import CaptionDecodeEngine
-    from image_caption_b200.dist import gather_rollout
+    from image_caption_b200.dist import sharded_rollout
     from image_caption_b200.synthetic import random_decoder, random_memory
 
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py needs a CUDA device: there is no CPU path for the product arm")
-    torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
-    desc, n_img, S, G, ns, max_len = WORKLOADS[args.workload]
-    if args.images:
-        n_img = args.images
-    if args.scaling == "strong":
-        n_img = n_img // world
+    desc, _, S, G, ns, max_len, scaling = WORKLOADS[name]
+    lo, n_img, n_global = shard_images(name, world, rank, images_override)
     M = n_img * G
-    e = 2 if args.precision == "bf16" else 4
+    e = 2 if precision == "bf16" else 4
     T = max_len - 1
 
     dec = random_decoder(0, pe_rows=max(52, max_len)).to(dev)
-    eng = CaptionDecodeEngine(dec, precision=args.precision, max_images=n_img, max_group=G, max_mem=S, max_len=max_len)
-    # distinct images per rank (global image index seeds nothing but the slice)
-    mem_host = random_memory(n_img, S, seed=1234 + rank).pin_memory()
+    eng = CaptionDecodeEngine(dec, precision=precision, max_images=n_img, max_group=G, max_mem=S, max_len=max_len)
+    # ONE global batch (seed 1234); every rank takes its contiguous block of images, so the sharded job decodes the
+    # same images with the same Philox sequence ids (seq_id_base = first image * group) at every N
+    mem_global = random_memory(n_global, S, seed=1234)
+    mem_host = mem_global[lo:lo + n_img].clone().pin_memory()
+    del mem_global
     mem_dev = mem_host.to(dev)
     flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
-    seq_base = rank * M
-    counts = [n_img] * world
+
+    def local_decode(memory, seed):
+        return eng.decode_from_memory(memory, START, END, max_len=max_len, group=G, n_sample=ns, seed=seed,
+                                      seq_id_base=lo * G, trim=False, early_stop=(world == 1))
 
     def rollout(memory, seed):
-        out = eng.decode_from_memory(memory, START, END, max_len=max_len, group=G, n_sample=ns, seed=seed,
-                                     seq_id_base=seq_base, trim=False)
-        if world > 1:  # the path's one collective: ids + log-probs for the reward step (SURVEY 8e)
-            gather_rollout(out.ids, out.logp, counts, G)
-        return out
+        """Device-resident input; N > 1: the path's one collective (ids + log-probs for the reward step)."""
+        if world == 1:
+            out = local_decode(memory, seed)
+            return out.ids, out.logp, out.steps
+
+        def shard(lo_, hi_, base):
+            assert lo_ == lo and hi_ == lo + n_img and base == lo * G
+            o = local_decode(memory, seed)
+            return o.ids, o.logp
+        ids, logp = sharded_rollout(shard, n_global, START, END, max_len, group=G, n_sample=ns, seed=seed)
+        return ids, logp, ids.shape[1] - 1
+
+    def rollout_host(seed):
+        """Host buffers in, host results out.  1 GPU: the C-ABI host entry point (capdec_generate_host).  N GPUs: H2D of
+        this rank's shard, decode, gather ON THE DEVICE, then one D2H of the gathered result."""
+        if world == 1:
+            out = local_decode(mem_host, seed)
+            return out.ids, out.logp
+        ids, logp, _ = rollout(mem_host.to(dev, non_blocking=True), seed)
+        ids_h = ids.cpu()
+        logp_h = logp.cpu() if logp is not None else None
+        return ids_h, logp_h
 
     def barrier():
         if world > 1:
@@ -227,14 +294,14 @@ def run_b200_arm(args) -> None:
         torch.cuda.synchronize(dev)
 
     # ---- device-resident timing: per-step CUDA events, L2 flushed between steps (outside the events)
-    for i in range(args.warmup):
-        out = rollout(mem_dev, 2024 + i)
-    assert out.steps == T, f"rollout stopped early ({out.steps} of {T} steps): random-init rows must not all end"
+    for i in range(warmup):
+        ids, logp, n_steps = rollout(mem_dev, 2024 + i)
+    assert n_steps == T, f"rollout stopped early ({n_steps} of {T} steps): random-init rows must not all end"
     barrier()
     launches0 = eng.launch_count()
     clocks = ClockSampler(local) if rank == 0 else None
-    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-    for i in range(args.steps):
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    for i in range(steps):
         flush.zero_()
         ev[i][0].record()
         rollout(mem_dev, 3000 + i)
@@ -247,39 +314,55 @@ def run_b200_arm(args) -> None:
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     dev_ms = float(t.item())
-    ms_per_step = dev_ms / args.steps
-    value = world * M * args.steps / (dev_ms * 1e-3)
+    ms_per_step = dev_ms / steps
+    value = n_global * G * steps / (dev_ms * 1e-3)
 
-    # ---- end to end through the host-buffer entry point (capdec_generate_host), wall clock
-    for i in range(max(1, args.warmup // 2)):
-        rollout(mem_host, 4000 + i)
+    # ---- end to end through the host-buffer entry points, wall clock
+    for i in range(max(1, warmup // 2)):
+        rollout_host(4000 + i)
     barrier()
     t0 = time.perf_counter()
-    for i in range(args.steps):
-        oh = rollout(mem_host, 5000 + i)
+    for i in range(steps):
+        ids_h, logp_h = rollout_host(5000 + i)
     barrier()
     e2e_s = time.perf_counter() - t0
     t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_s = float(t.item())
-    assert not oh.ids.is_cuda
+    assert not ids_h.is_cuda
     h2d = mem_host.numel() * 4
-    d2h = M * max_len * 8 + (M * T * 4 if ns else 0)
-    e2e = {"value": world * M * args.steps / e2e_s, "unit": "captions/s", "h2d_bytes_per_step": h2d,
-           "d2h_bytes_per_step": d2h, "ms_per_step": 1e3 * e2e_s / args.steps}
+    d2h = ids_h.numel() * 8 + (logp_h.numel() * 4 if logp_h is not None else 0)
+    e2e = {"value": n_global * G * steps / e2e_s, "unit": "captions/s", "h2d_bytes_per_step": h2d,
+           "d2h_bytes_per_step": d2h, "ms_per_step": 1e3 * e2e_s / steps,
+           "path": "capdec_generate_host (pinned host memory in, ids/log-probs out, H2D chunks pipelined with the prefill)"
+                   if world == 1 else "per rank: H2D of the shard, decode, all-gather on the device, one D2H of the gathered result"}
 
-    line = {
-        "metric": "captions/s", "value": value, "unit": "captions/s", "n_gpus": world, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": args.scaling,
-        "vs_baseline": None, "dtype": args.precision, "data": "synthetic",
-        "config": {"workload": f"{args.workload}: {desc}", "images_per_gpu": n_img, "mem_len": S, "group": G,
-                   "n_sample": ns, "max_len": max_len, "sequences_per_gpu": M, "decode_steps": T,
-                   "l2": "flushed between timed steps (512 MiB memset outside the event pairs)",
-                   "weights": "random init, torch.manual_seed(0)", "collective": "all-gather ids+logp" if world > 1 else "none",
-                   "engine": "v2 step kernels, 7 decode steps per CUDA graph, programmatic dependent launch"},
-        "decode_step_us": 1e3 * ms_per_step / T, "e2e": e2e, "gpu_launches": int(launches), "clocks": clk,
-    }
+    cfg = workload_config(name, world, precision, images_override)
+    cfg.update({"l2": "flushed between timed steps (512 MiB memset outside the event pairs)",
+                "collective": "all-gather ids+logp (NCCL), trimmed to the reference's global width" if world > 1 else "none",
+                "engine": os.environ.get("CAPDEC_ENGINE_NOTE", "v2 step kernels, 7 decode steps per CUDA graph, programmatic dependent launch")})
+    rec = {"metric": "captions/s", "value": value, "unit": "captions/s", "n_gpus": world, "steps": steps,
+           "warmup": warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": scaling,
+           "vs_baseline": None, "dtype": precision, "data": "synthetic", "config": cfg,
+           "decode_step_us": 1e3 * ms_per_step / T, "e2e": e2e, "gpu_launches": int(launches), "clocks": clk}
+
+    # ---- sharded result == unsharded result (same global batch, same seed): rank 0 decodes everything alone
+    if verify and world > 1:
+        ids_s, logp_s, _ = rollout(mem_dev, 777)
+        ok = None
+        if rank == 0:
+            eng1 = CaptionDecodeEngine(dec, precision=precision, max_images=n_global, max_group=G, max_mem=S, max_len=max_len)
+            full = eng1.decode_from_memory(random_memory(n_global, S, seed=1234).to(dev), START, END, max_len=max_len, group=G,
+                                           n_sample=ns, seed=777, seq_id_base=0, trim=False, early_stop=False)
+            w = ids_s.shape[1]
+            ok = {"ids_bit_equal": bool(torch.equal(full.ids[:, :w], ids_s)),
+                  "logp_bit_equal": bool(torch.equal(full.logp[:, :w - 1], logp_s)) if logp_s is not None else None,
+                  "ids_mismatch_rows": int((full.ids[:, :w] != ids_s).any(1).sum()), "width": int(w),
+                  "what": f"gathered {world}-rank rollout vs one unsharded rollout of the same {n_global} images on rank 0"}
+            eng1.close()
+        rec["verify"] = ok
+        barrier()
 
     if rank == 0:
         ab = algorithmic_bytes(n_img, S, G, max_len, e)
@@ -290,37 +373,79 @@ def run_b200_arm(args) -> None:
             pass
         hbm = float(peaks.get("hbm_gbs", 6650.0))
         peak_src = "measured (MEASURED_PEAKS.json)" if peaks else "fallback (B200_PROFILING.md)"
-        line["rollout_roofline"] = {"bound": "hbm", "algorithmic_bytes": ab["rollout"],
-                                    "achieved": ab["rollout"] / (ms_per_step * 1e-3) / 1e9, "peak": hbm, "unit": "GB/s",
-                                    "frac": ab["rollout"] / (ms_per_step * 1e-3) / 1e9 / hbm, "peak_source": peak_src}
-        # per-kernel pass: same rollout, direct launches, one CUDA-event pair per launch
-        eng.profile(True)
-        flush.zero_()
-        eng.decode_from_memory(mem_dev, START, END, max_len=max_len, group=G, n_sample=ns, seed=1, trim=False)
-        rep = eng.profile_report()
-        eng.profile(False)
-        tot = sum(v["ms"] for v in rep.values())
-        kernels = {k: {"launches": v["launches"], "us_per_launch": 1e3 * v["ms"] / v["launches"],
-                       "share": v["ms"] / tot, "GBps": v["bytes"] / (v["ms"] * 1e-3) / 1e9 if v["ms"] > 0 else None}
-                   for k, v in sorted(rep.items(), key=lambda kv: -kv[1]["ms"])}
-        top = next(iter(kernels))
-        tv = rep[top]
-        traffic = None
-        try:  # dram__bytes_read+write per launch of this kernel from the committed ncu --set full capture
-            traffic = json.load(open(os.path.join(ROOT, "profiles", "r01_traffic.json"))).get(args.workload, {}).get(top)
-        except OSError:
-            pass
-        line["roofline"] = {"kernel": top, "bound": "hbm", "achieved": tv["bytes"] / (tv["ms"] * 1e-3) / 1e9,
-                            "peak": hbm, "unit": "GB/s", "frac": tv["bytes"] / (tv["ms"] * 1e-3) / 1e9 / hbm,
-                            "traffic": traffic, "bytes_per_launch": tv["bytes"] / tv["launches"],
-                            "us_per_launch": 1e3 * tv["ms"] / tv["launches"], "share_of_step": tv["ms"] / tot,
-                            "peak_source": peak_src}
-        line["kernels"] = kernels
+        rec["rollout_roofline"] = {"bound": "hbm", "algorithmic_bytes": ab["rollout"],
+                                   "achieved": ab["rollout"] / (ms_per_step * 1e-3) / 1e9, "peak": hbm, "unit": "GB/s",
+                                   "frac": ab["rollout"] / (ms_per_step * 1e-3) / 1e9 / hbm, "peak_source": peak_src,
+                                   "note": "per GPU: this rank's shard"}
+        if profile:
+            # per-kernel pass: same rollout, direct launches, one CUDA-event pair per launch (each pair carries ~5 us of
+            # launch/event floor: the SHARES are meaningful, the absolute per-launch times are upper bounds; the ncu
+            # gpu__time_duration list of the same command is committed under profiles/)
+            eng.profile(True)
+            flush.zero_()
+            eng.decode_from_memory(mem_dev, START, END, max_len=max_len, group=G, n_sample=ns, seed=1, trim=False)
+            rep = eng.profile_report()
+            eng.profile(False)
+            tot = sum(v["ms"] for v in rep.values())
+            kernels = {k: {"launches": v["launches"], "us_per_launch": 1e3 * v["ms"] / v["launches"],
+                           "share": v["ms"] / tot, "GBps": v["bytes"] / (v["ms"] * 1e-3) / 1e9 if v["ms"] > 0 else None}
+                       for k, v in sorted(rep.items(), key=lambda kv: -kv[1]["ms"])}
+            ncu = {}
+            try:  # per-kernel gpu__time_duration (us) and dram bytes per launch from the committed ncu captures
+                ncu = json.load(open(os.path.join(ROOT, "profiles", "ncu_kernels.json"))).get(name, {})
+            except (OSError, ValueError):
+                pass
+            for k in kernels:
+                if k in ncu:
+                    kernels[k]["ncu_us_per_launch"] = ncu[k].get("us")
+            top = next(iter(kernels))
+            tv = rep[top]
+            rec["roofline"] = {"kernel": top, "bound": "hbm", "achieved": tv["bytes"] / (tv["ms"] * 1e-3) / 1e9,
+                               "peak": hbm, "unit": "GB/s", "frac": tv["bytes"] / (tv["ms"] * 1e-3) / 1e9 / hbm,
+                               "traffic": ncu.get(top, {}).get("dram_bytes"), "bytes_per_launch": tv["bytes"] / tv["launches"],
+                               "us_per_launch": 1e3 * tv["ms"] / tv["launches"], "share_of_step": tv["ms"] / tot,
+                               "ncu_us_per_launch": ncu.get(top, {}).get("us"), "peak_source": peak_src}
+            rec["kernels"] = kernels
+    eng.close()
+    del eng, flush, mem_dev
+    torch.cuda.empty_cache()
+    return rec
+
+
+def run_b200_arm(args) -> None:
+    import torch
+    import torch.distributed as dist
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: there is no CPU path for the product arm")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    name = pick_workload(args.workload, world)
+    line = measure(name, args.precision, args.steps, args.warmup, world, rank, local, args.images,
+                   verify=not args.no_verify)
+
+    if not args.no_sub and args.workload == "auto":
+        sub = {}
+        sub_steps = max(3, args.steps // 2)
+        for sname in (("cfg2", "cfg5") if world == 1 else ("cfg5", "cfg2")):
+            r = measure(sname, args.precision, sub_steps, args.warmup, world, rank, local)
+            sub[sname if sname != "cfg5" else "cfg5_per_gpu_1024"] = r
+        if world == 1:
+            r = measure(name, "fp32", 3, 3, world, rank, local, profile=False)
+            sub[f"{name}_fp32"] = r
+            if rank == 0:
+                sub[f"torch_eager_gpu_{name}"] = torch_eager_gpu(name, 1, 1, local)
+        line["sub"] = sub
+    if rank == 0:
         if world == 1 and not args.no_cpu:
-            r = cpu_reference(args.workload, 1, 0, args.cpu_sample)
+            r = cpu_reference(name, 3, 1, args.cpu_sample or CPU_SAMPLE[name])
             line["cpu_baseline"] = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")}
         print(json.dumps(line), flush=True)
-    eng.close()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -332,12 +457,13 @@ def main() -> None:
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference", "torch_gpu"])
-    ap.add_argument("--workload", default="cfg2", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default="auto", choices=["auto"] + sorted(WORKLOADS))
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
-    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
-    ap.add_argument("--images", type=int, default=0, help="override images per GPU")
-    ap.add_argument("--cpu-sample", type=int, default=8, help="images in the bounded CPU-baseline sample")
+    ap.add_argument("--images", type=int, default=0, help="override the workload's image count")
+    ap.add_argument("--cpu-sample", type=int, default=0, help="images in the bounded CPU-baseline sample (0 = per workload)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-sub", action="store_true", help="skip the sub-records of the default workload")
+    ap.add_argument("--no-verify", action="store_true", help="N > 1: skip the sharded == unsharded check")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "b200":
         args.warmup = 3

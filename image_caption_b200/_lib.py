@@ -11,7 +11,7 @@ LIB_PATH = os.environ.get("CAPDEC_LIB") or os.path.join(_HERE, "libcapdec.so")  
 ABI_VERSION = 1
 MAX_LAYERS = 12
 PREC_FP32, PREC_BF16 = 0, 1
-FLAG_NO_GRAPH, FLAG_NO_UMMA, FLAG_V1_STEP, FLAG_NO_PDL, FLAG_NO_CLUSTER_ROLLOUT = 1, 2, 4, 8, 16
+FLAG_NO_GRAPH, FLAG_NO_UMMA, FLAG_V1_STEP, FLAG_NO_PDL = 1, 2, 4, 8
 DECODE_NO_EARLY_STOP = 1
 DECODE_TEACHER_FORCED = 2
 BEAM_STOP_GRID = 1

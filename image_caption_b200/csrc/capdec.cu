@@ -17,7 +17,6 @@
 #include "cross_attn_tma.cuh"
 #include "attention.cuh"
 #include "pointwise.cuh"
-#include "rollout_cluster.cuh"
 
 using namespace capdec;
 
@@ -405,6 +404,9 @@ static void free_all(capdec_handle h) {
   h->graphs.clear();
   for (void* p : h->allocs) cudaFree(p);
   h->allocs.clear();
+  if (h->copy_stream) { cudaStreamDestroy(h->copy_stream); h->copy_stream = nullptr; }
+  for (auto& e : h->copy_ev) if (e) { cudaEventDestroy(e); e = nullptr; }
+  if (h->copy_start) { cudaEventDestroy(h->copy_start); h->copy_start = nullptr; }
 }
 
 extern "C" int capdec_destroy(capdec_handle h) {
@@ -430,14 +432,6 @@ extern "C" int capdec_destroy(capdec_handle h) {
                   r[8] - r[3], r[9] - r[3], r[10] - r[3], r[4] - r[3]);
         prev_exit = r[6];
       }
-    }
-  }
-  if (h->trace) {  // tuning aid: phase stamps of the cluster rollout kernel (cycles since the layer started)
-    long long t[64];
-    if (cudaMemcpy(t, h->trace, sizeof t, cudaMemcpyDeviceToHost) == cudaSuccess) {
-      fprintf(stderr, "capdec trace (cycles since layer start):");
-      for (int i = 1; i < 64 && t[i]; ++i) fprintf(stderr, " [%d]%lld", i, t[i] - t[0]);
-      fprintf(stderr, "\n");
     }
   }
   free_all(h);
@@ -504,13 +498,6 @@ static int create_impl(capdec_handle h) {
     CUDA_TRY(h, cudaMemset(h->tickets, 0, 64 * sizeof(unsigned)));
     CUDA_TRY(h, configure_fast_kernels());
   }
-  if (h->mega) {
-    TRY(dev_alloc(h, &h->wstream, (size_t)kRcCluster * (L * kRcUnitsPerLayer + kRcUnitsHead) * kRcUnitBytes));
-    TRY(dev_alloc(h, &h->counters, (size_t)c.max_len * 4));
-    if (getenv("CAPDEC_TRACE")) { TRY(dev_alloc(h, &h->trace, 64)); CUDA_TRY(h, cudaMemset(h->trace, 0, 64 * sizeof(long long))); }
-    CUDA_TRY(h, cudaFuncSetAttribute(rollout_cluster_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem));
-    CUDA_TRY(h, cudaFuncSetAttribute(rollout_cluster_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem));
-  }
   return 0;
 }
 
@@ -548,9 +535,6 @@ extern "C" int capdec_create(const capdec_config* cfg, int device, capdec_handle
   h->t_pad = cfg->max_len <= 64 ? 64 : 128;
   h->fast = h->use_umma && !(cfg->flags & CAPDEC_FLAG_V1_STEP);
   h->use_pdl = h->fast && !(cfg->flags & CAPDEC_FLAG_NO_PDL);
-  h->mega = h->fast && !(cfg->flags & CAPDEC_FLAG_NO_CLUSTER_ROLLOUT) && cfg->d_ff == 2048 && h->t_pad == 64;
-  if (const char* e = getenv("CAPDEC_RB")) h->mega_rb = atoi(e) == 32 ? 32 : 16;
-  if (const char* e = getenv("CAPDEC_CHUNK")) h->mega_chunk = std::max(1, atoi(e));
   if (getenv("CAPDEC_TRACE_GEMM")) {
     long long* buf = nullptr;
     if (cudaMalloc(&buf, 256 * 12 * sizeof(long long)) == cudaSuccess) {
@@ -651,20 +635,6 @@ extern "C" int capdec_set_weights(capdec_handle h, const capdec_weights* w, void
     }
   }
   if (h->use_umma) TRY(make_weight_maps(h, &h->m_ckv, h->w_ckv, L * 2 * kD, kD));
-  if (h->mega) {
-    RcPackSrc src{};
-    src.n_layer = L;
-    src.vocab = V;
-    src.fc_w = w->fc_out_w;
-    for (int l = 0; l < L; ++l) {
-      const capdec_layer_weights& lw = w->layer[l];
-      src.layer[l] = RcPackLayer{lw.self_in_w, lw.self_out_w, lw.cross_in_w, lw.cross_out_w, lw.lin1_w, lw.lin2_w};
-    }
-    const long long total = (long long)kRcCluster * (L * kRcUnitsPerLayer + kRcUnitsHead) * 512;
-    pack_wstream_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(src, h->wstream);
-    CUDA_TRY(h, cudaGetLastError());
-    h->launches++;
-  }
   h->have_weights = true;
   return CAPDEC_OK;
 }
@@ -683,32 +653,46 @@ static int finish_prefill(capdec_handle h, int n_images, int mem_len) {
   return CAPDEC_OK;
 }
 
-extern "C" int capdec_prefill(capdec_handle h, const float* memory, int32_t n_images, int32_t mem_len, void* stream) {
-  if (!h || !memory) return fail(h, CAPDEC_ERR_INVALID, "null argument");
-  if (!h->have_weights) return fail(h, CAPDEC_ERR_STATE, "capdec_prefill before capdec_set_weights");
-  if (n_images < 1 || mem_len < 1) return fail(h, CAPDEC_ERR_INVALID, "n_images and mem_len must be positive");
-  if (n_images > h->cfg.max_images || mem_len > h->cfg.max_mem)
-    return fail(h, CAPDEC_ERR_CAPACITY, "prefill of %d images x %d exceeds capacity %d x %d", n_images, mem_len,
-                h->cfg.max_images, h->cfg.max_mem);
-  cudaStream_t s = (cudaStream_t)stream;
-  CUDA_TRY(h, cudaSetDevice(h->device));
-  h->prefilled = false;
-  h->launches_this_enqueue = 0;
-  const int M = n_images * mem_len, N = h->cfg.n_layer * 2 * kD;
+// Images [img0, img0 + n_chunk) of a prefill over n_images: operand conversion (bf16 mode) + ONE projection GEMM into the
+// cross cache.  capdec_prefill runs it once over everything; capdec_generate_host once per host-copy chunk.
+static int prefill_chunk(capdec_handle h, cudaStream_t s, const float* memory_chunk, int img0, int n_chunk, int n_images,
+                         int mem_len) {
+  const int M = n_chunk * mem_len, N = h->cfg.n_layer * 2 * kD;
+  const size_t off = (size_t)img0 * mem_len * kD;  // element offset of the chunk inside the staged operand
   if (h->bf16) {
     const size_t n4 = (size_t)M * kD / 4;
     set_tag(h, "prefill_convert", (double)M * kD * 6);
     ProfScope ps(h, s);
-    convert_kernel<bf16><<<(unsigned)((n4 + 255) / 256), 256, 0, s>>>(memory, (bf16*)h->mem_b, n4);
+    convert_kernel<bf16><<<(unsigned)((n4 + 255) / 256), 256, 0, s>>>(memory_chunk, (bf16*)h->mem_b + off, n4);
     CUDA_TRY(h, cudaGetLastError());
     h->launches_this_enqueue++;
   }
-  EpiCrossKV<float> e32{(float*)h->cross_kv, h->b_ckv, n_images, mem_len};
-  EpiCrossKV<bf16> e16{(bf16*)h->cross_kv, h->b_ckv, n_images, mem_len};
+  EpiCrossKV<float> e32{(float*)h->cross_kv, h->b_ckv, n_images, mem_len, img0};
+  EpiCrossKV<bf16> e16{(bf16*)h->cross_kv, h->b_ckv, n_images, mem_len, img0};
   CUtensorMap tm_mem;
-  if (h->use_umma) TRY(make_map(h, &tm_mem, h->mem_b, M, kD, kUmmaBM));
+  if (h->use_umma) TRY(make_map(h, &tm_mem, (bf16*)h->mem_b + off, M, kD, kUmmaBM));
   set_tag(h, "prefill_gemm_cross_kv", gemm_bytes(M, N, kD, h->esz, h->esz, h->esz));
-  TRY(gemm(h, s, h->bf16 ? h->mem_b : (const void*)memory, &tm_mem, h->w_ckv, &h->m_ckv, M, N, kD, e32, e16, nullptr));
+  return gemm(h, s, h->bf16 ? (const void*)((bf16*)h->mem_b + off) : (const void*)memory_chunk, &tm_mem, h->w_ckv, &h->m_ckv, M, N,
+              kD, e32, e16, nullptr);
+}
+
+static int check_prefill_args(capdec_handle h, const void* memory, int n_images, int mem_len) {
+  if (!h || !memory) return fail(h, CAPDEC_ERR_INVALID, "null argument");
+  if (!h->have_weights) return fail(h, CAPDEC_ERR_STATE, "prefill before capdec_set_weights");
+  if (n_images < 1 || mem_len < 1) return fail(h, CAPDEC_ERR_INVALID, "n_images and mem_len must be positive");
+  if (n_images > h->cfg.max_images || mem_len > h->cfg.max_mem)
+    return fail(h, CAPDEC_ERR_CAPACITY, "prefill of %d images x %d exceeds capacity %d x %d", n_images, mem_len,
+                h->cfg.max_images, h->cfg.max_mem);
+  return 0;
+}
+
+extern "C" int capdec_prefill(capdec_handle h, const float* memory, int32_t n_images, int32_t mem_len, void* stream) {
+  TRY(check_prefill_args(h, memory, n_images, mem_len));
+  cudaStream_t s = (cudaStream_t)stream;
+  CUDA_TRY(h, cudaSetDevice(h->device));
+  h->prefilled = false;
+  h->launches_this_enqueue = 0;
+  TRY(prefill_chunk(h, s, memory, 0, n_images, n_images, mem_len));
   return finish_prefill(h, n_images, mem_len);
 }
 
@@ -1124,57 +1108,7 @@ static int get_step_graph(capdec_handle h, int n_images, int S, int group, int n
   return 0;
 }
 
-// ------------------------------------------------------------------ v3: whole-rollout cluster kernel
-static bool mega_applicable(capdec_handle h, int n_images, int S, int group) {
-  return h->mega && S <= 64 && group <= h->mega_rb && h->mega_rb % group == 0;
-}
-
-static int enqueue_cluster_rollout(capdec_handle h, cudaStream_t s, int n_images, int S, int group, int T) {
-  const int M = n_images * group, L = h->cfg.n_layer, RB = h->mega_rb;
-  RcParams P{};
-  for (int l = 0; l < L; ++l) {
-    const LayerParams& lp = h->layer[l];
-    RcLayer& r = P.layer[l];
-    r.b_qkv = lp.b_qkv; r.b_so = lp.b_so; r.b_cq = lp.b_cq; r.b_co = lp.b_co; r.b_1 = lp.b_1; r.b_2 = lp.b_2;
-    for (int j = 0; j < 3; ++j) { r.ln_w[j] = lp.ln_w[j]; r.ln_b[j] = lp.ln_b[j]; }
-    r.kcache = (bf16*)h->self_k + (size_t)l * h->self_layer_elems;
-    r.vcache = (bf16*)h->self_v + (size_t)l * h->self_layer_elems;
-  }
-  P.wstream = h->wstream;
-  P.emb = h->emb; P.pe = h->pe; P.fc_b = h->fc_b;
-  P.cp = h->cp; P.fin = h->fin; P.counters = h->counters; P.st = h->st; P.trace = h->trace;
-  P.n_layer = L; P.M = M; P.group = group; P.S = S; P.t_pad = h->t_pad; P.vocab = h->cfg.vocab; P.n_images = n_images;
-  const int blocks = (M + RB - 1) / RB;
-  const int ring0 = RB == 16 ? RcSmem<16>::kRing : RcSmem<32>::kRing;
-  int stages = std::min(16, (kMaxDynSmem - 1024 - ring0) / kRcUnitBytes);
-  if (h->force_stages > 0) stages = std::min(stages, h->force_stages);
-  if (stages < 2) return fail(h, CAPDEC_ERR_INVALID, "cluster rollout: no room for the weight ring (RB=%d)", RB);
-  const size_t smem = RB == 16 ? RcSmem<16>::bytes(stages) : RcSmem<32>::bytes(stages);
-  // algorithmic bytes of the chunk for the profile report: SURVEY 8d per-step terms
-  for (int n0 = 0; n0 < T; n0 += h->mega_chunk) {
-    const int n1 = std::min(T, n0 + h->mega_chunk);
-    P.step_begin = n0;
-    P.step_end = n1;
-    double bytes = 0;
-    for (int n = n0 + 1; n <= n1; ++n)
-      bytes += 22128237.0 * 2 + (double)n_images * 2 * L * S * kD * 2 + (double)M * (2.0 * L * n * kD * 2 + 2.0 * L * kD * 2) +
-               (double)M * (kD * 2 + 12);
-    set_tag(h, "rollout_cluster", bytes);
-    {
-      ProfScope ps(h, s);
-      if (RB == 16) rollout_cluster_kernel<16><<<blocks * kRcCluster, kRcThreads, smem, s>>>(h->tm_ckv, P, stages);
-      else rollout_cluster_kernel<32><<<blocks * kRcCluster, kRcThreads, smem, s>>>(h->tm_ckv, P, stages);
-      CUDA_TRY(h, cudaGetLastError());
-    }
-    rollout_check_kernel<<<1, 256, 0, s>>>(h->st, h->cp, h->counters, M, n0, n1);
-    CUDA_TRY(h, cudaGetLastError());
-    h->launches += 2;
-  }
-  return 0;
-}
-
 // ------------------------------------------------------------------ decode
-static bool mega_applicable(capdec_handle h, int n_images, int S, int group);
 static int validate_decode(capdec_handle h, const capdec_decode_args* a) {
   if (!h->prefilled) return fail(h, CAPDEC_ERR_STATE, "capdec_decode before capdec_prefill");
   if (a->group < 1 || a->n_sample < 0 || a->n_sample > a->group) return fail(h, CAPDEC_ERR_INVALID, "bad group/n_sample (%d/%d)", a->group, a->n_sample);
@@ -1183,8 +1117,8 @@ static int validate_decode(capdec_handle h, const capdec_decode_args* a) {
   if (a->max_len - 1 > h->cfg.pe_rows)  // the reference fails at vit:32 (prefix longer than the pe table)
     return fail(h, CAPDEC_ERR_INVALID, "max_len %d needs %d positional rows, table has %d", a->max_len, a->max_len - 1, h->cfg.pe_rows);
   const int V = h->cfg.vocab;
-  if (a->start_token < 0 || a->start_token >= V || a->end_token < 0 || a->end_token >= V)
-    return fail(h, CAPDEC_ERR_INVALID, "start/end token outside the vocabulary");
+  if (a->start_token < 0 || a->start_token >= V || a->end_token < 0 || a->end_token >= V || a->pad_token < 0 || a->pad_token >= V)
+    return fail(h, CAPDEC_ERR_INVALID, "start/end/pad token outside the vocabulary");
   if (!a->ids_out) return fail(h, CAPDEC_ERR_INVALID, "ids_out is null");
   return 0;
 }
@@ -1212,18 +1146,16 @@ extern "C" int capdec_decode(capdec_handle h, const capdec_decode_args* a, void*
   cp.no_early_stop = (a->flags & CAPDEC_DECODE_NO_EARLY_STOP) ? 1 : 0;
   cp.vocab = h->cfg.vocab;
   cp.forced = (a->flags & CAPDEC_DECODE_TEACHER_FORCED) ? 1 : 0;
-  if (cp.forced && mega_applicable(h, n_images, S, group))
-    return fail(h, CAPDEC_ERR_INVALID, "teacher forcing is not built into the cluster rollout (step_impl v3)");
   cp.n_sample_rows = n_images * a->n_sample;
   cp.n_greedy_rows = M - cp.n_sample_rows;
   // pageable source: the runtime stages it before returning, so `cp` may die with this frame
   CUDA_TRY(h, cudaMemcpyAsync(h->cp, &cp, sizeof cp, cudaMemcpyHostToDevice, s));
-  init_rollout_kernel<<<std::min((M * a->max_len + 255) / 256, 1024), 256, 0, s>>>(h->st, h->cp, h->fin, M, h->counters);
+  init_rollout_kernel<<<std::min((M * a->max_len + 255) / 256, 1024), 256, 0, s>>>(h->st, h->cp, h->fin, M);
   CUDA_TRY(h, cudaGetLastError());
   h->launches++;
 
   const int T = a->max_len - 1;
-  if (h->fast && !mega_applicable(h, n_images, S, group)) {
+  if (h->fast) {
     // input of step 0; later steps get theirs from the head kernel of the step before
     set_tag(h, "embed_pe", (double)M * kD * (4 + 4 + 2));
     ProfScope ps(h, s);
@@ -1231,9 +1163,7 @@ extern "C" int capdec_decode(capdec_handle h, const capdec_decode_args* a, void*
     CUDA_TRY(h, cudaGetLastError());
     h->launches++;
   }
-  if (mega_applicable(h, n_images, S, group)) {
-    TRY(enqueue_cluster_rollout(h, s, n_images, S, group, T));
-  } else if (h->use_graph && !h->profiling) {
+  if (h->use_graph && !h->profiling) {
     StepGraph* g = nullptr;
     const int per = std::max(1, std::min(h->graph_steps, T));
     if (T / per > 0) {
@@ -1306,7 +1236,7 @@ extern "C" int capdec_beam_search(capdec_handle h, const capdec_beam_args* a, vo
   cp.n_greedy_rows = M;
   cp.vocab = V;
   CUDA_TRY(h, cudaMemcpyAsync(h->cp, &cp, sizeof cp, cudaMemcpyHostToDevice, s));
-  init_rollout_kernel<<<std::min((M * a->max_len + 255) / 256, 1024), 256, 0, s>>>(h->st, h->cp, h->fin, M, h->counters);
+  init_rollout_kernel<<<std::min((M * a->max_len + 255) / 256, 1024), 256, 0, s>>>(h->st, h->cp, h->fin, M);
   beam_init_kernel<<<std::min((2 * M * h->t_pad + 255) / 256, 1024), 256, 0, s>>>(h->beam, h->cp, n_images, beam, h->t_pad);
   CUDA_TRY(h, cudaGetLastError());
   h->launches += 2;
@@ -1355,13 +1285,16 @@ extern "C" int capdec_beam_search(capdec_handle h, const capdec_beam_args* a, vo
   return CAPDEC_OK;
 }
 
+// Host buffers in, host buffers out (what generate() / SCSTLoss see when their tensors live on the CPU).
+// The memory is copied in up to 8 image chunks on a private copy stream; each chunk's K/V projection starts as soon
+// as its copy has landed, so the host link and the prefill overlap instead of running back to back.
 extern "C" int capdec_generate_host(capdec_handle h, const float* memory_host, int32_t n_images, int32_t mem_len,
                                     const capdec_decode_args* ah, void* stream) {
   if (!h || !memory_host || !ah) return fail(h, CAPDEC_ERR_INVALID, "null argument");
+  if (!ah->ids_out) return fail(h, CAPDEC_ERR_INVALID, "ids_out is null");
   if (ah->logits_out) return fail(h, CAPDEC_ERR_INVALID, "logits_out is not supported by capdec_generate_host");
   if (ah->flags & CAPDEC_DECODE_TEACHER_FORCED) return fail(h, CAPDEC_ERR_INVALID, "teacher forcing needs device buffers (capdec_decode)");
-  if (n_images < 1 || mem_len < 1 || n_images > h->cfg.max_images || mem_len > h->cfg.max_mem)
-    return fail(h, CAPDEC_ERR_CAPACITY, "%d images x %d exceeds capacity %d x %d", n_images, mem_len, h->cfg.max_images, h->cfg.max_mem);
+  TRY(check_prefill_args(h, memory_host, n_images, mem_len));
   if (ah->group < 1 || ah->group > h->cfg.max_group || ah->max_len < 2 || ah->max_len > h->cfg.max_len)
     return fail(h, CAPDEC_ERR_CAPACITY, "group/max_len outside capacity");
   cudaStream_t s = (cudaStream_t)stream;
@@ -1371,10 +1304,28 @@ extern "C" int capdec_generate_host(capdec_handle h, const float* memory_host, i
     TRY(dev_alloc(h, &h->stage_mem, (size_t)h->cfg.max_images * h->cfg.max_mem * kD));
     TRY(dev_alloc(h, &h->stage_ids, Mmax * h->cfg.max_len));
     TRY(dev_alloc(h, &h->stage_logp, Mmax * h->cfg.max_len));
+    CUDA_TRY(h, cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+    for (auto& e : h->copy_ev) CUDA_TRY(h, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    CUDA_TRY(h, cudaEventCreateWithFlags(&h->copy_start, cudaEventDisableTiming));
   }
   const size_t M = (size_t)n_images * ah->group;
-  CUDA_TRY(h, cudaMemcpyAsync(h->stage_mem, memory_host, (size_t)n_images * mem_len * kD * sizeof(float), cudaMemcpyHostToDevice, s));
-  TRY(capdec_prefill(h, h->stage_mem, n_images, mem_len, stream));
+  // the copy stream starts after whatever the caller's stream still does with the staging buffer
+  CUDA_TRY(h, cudaEventRecord(h->copy_start, s));
+  CUDA_TRY(h, cudaStreamWaitEvent(h->copy_stream, h->copy_start, 0));
+  h->prefilled = false;
+  h->launches_this_enqueue = 0;
+  const int n_chunks = std::min<int>(kHostCopyChunks, n_images);
+  const int per = (n_images + n_chunks - 1) / n_chunks;
+  for (int c = 0, img0 = 0; img0 < n_images; ++c, img0 += per) {
+    const int n = std::min(per, n_images - img0);
+    const size_t off = (size_t)img0 * mem_len * kD;
+    CUDA_TRY(h, cudaMemcpyAsync(h->stage_mem + off, memory_host + off, (size_t)n * mem_len * kD * sizeof(float),
+                                cudaMemcpyHostToDevice, h->copy_stream));
+    CUDA_TRY(h, cudaEventRecord(h->copy_ev[c], h->copy_stream));
+    CUDA_TRY(h, cudaStreamWaitEvent(s, h->copy_ev[c], 0));
+    TRY(prefill_chunk(h, s, h->stage_mem + off, img0, n, n_images, mem_len));
+  }
+  TRY(finish_prefill(h, n_images, mem_len));
   capdec_decode_args ad = *ah;
   ad.ids_out = (int64_t*)h->stage_ids;
   ad.logp_out = ah->logp_out ? h->stage_logp : nullptr;
@@ -1452,8 +1403,11 @@ extern "C" int capdec_debug_gemm(capdec_handle h, const float* a, const float* w
     else { EpiLinear<float, false> e{c, bias, n}; rc = launch_simt<float, float, EpiLinear<float, false>>(h, s, a, k, w, k, m, n, k, e, nullptr); }
   } else {
     bf16 *ab = nullptr, *wb = nullptr;
-    CUDA_TRY(h, cudaMalloc(&ab, (size_t)m * k * 2));
-    CUDA_TRY(h, cudaMalloc(&wb, (size_t)n * k * 2));
+    if (cudaMalloc(&ab, (size_t)m * k * 2) != cudaSuccess || cudaMalloc(&wb, (size_t)n * k * 2) != cudaSuccess) {
+      cudaFree(ab);  // (cudaFree(nullptr) is a no-op)
+      cudaGetLastError();
+      return fail(h, CAPDEC_ERR_CUDA, "debug gemm: cudaMalloc of the bf16 operands failed");
+    }
     pack_rows_kernel<bf16><<<(unsigned)(((size_t)m * k + 255) / 256), 256, 0, s>>>(a, ab, m, k, m);
     pack_rows_kernel<bf16><<<(unsigned)(((size_t)n * k + 255) / 256), 256, 0, s>>>(w, wb, n, k, n);
     if (h->use_umma) {

@@ -12,6 +12,8 @@
 
 namespace capdec {
 
+constexpr int kHostCopyChunks = 8;  // capdec_generate_host: image chunks of the host copy
+
 // W operand tensor maps for the three N-tile widths the tcgen05 GEMM is instantiated for.
 struct WeightMaps {
   CUtensorMap bn[3];  // 32, 64, 128
@@ -100,18 +102,13 @@ struct capdec_engine {
   unsigned* tickets = nullptr;     // [row tiles] last-CTA election of the self-closing split-K FFN2 (SwapPartialLN)
   bool no_ffn2_fuse = true;        // env CAPDEC_FFN2_FUSE=1 clears it: the split-K FFN2 closes itself (no sum_ln launch)
 
-  // ---- v3: whole-rollout cluster kernel (rollout_cluster.cuh), used when the shape allows
-  bool mega = false;               // enabled (bf16 + tcgen05, not CAPDEC_FLAG_NO_CLUSTER_ROLLOUT)
-  unsigned char* wstream = nullptr;  // [8][L*112+8][8192] per-CTA weight units in streaming order
-  int* counters = nullptr;         // [max_len][4] per-step stop-rule counters
-  long long* trace = nullptr;      // 32 clock stamps (env CAPDEC_TRACE=1)
-  int mega_rb = 16;                // sequences per cluster
-  int mega_chunk = 8;              // decode steps per kernel launch (stop rule evaluated between chunks)
-
   // ---- host-buffer entry point staging (device side)
   float* stage_mem = nullptr;
   long long* stage_ids = nullptr;
   float* stage_logp = nullptr;
+  cudaStream_t copy_stream = nullptr;          // host -> device chunks of the memory, overlapped with the prefill
+  cudaEvent_t copy_ev[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  cudaEvent_t copy_start = nullptr;
 
   // ---- current rollout
   int n_images = 0, mem_len = 0;

@@ -65,11 +65,12 @@ template <typename Elem>
 struct EpiCrossKV {
   Elem* out;
   const float* bias;  // [L*1024]
-  int n_images;
+  int n_images;       // images of the whole prefill (the cache's image stride)
   int mem_len;
+  int img0 = 0;       // first image of this launch (chunked prefill: host copies pipelined with the projection)
   template <int NV>
   __device__ __forceinline__ void store(int row, int col0, const float* v) const {
-    const int img = row / mem_len, s = row - img * mem_len;
+    const int il = row / mem_len, s = row - il * mem_len, img = img0 + il;
 #pragma unroll
     for (int i = 0; i < NV; i += 4) {
       const int col = col0 + i;

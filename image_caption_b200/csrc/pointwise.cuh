@@ -13,7 +13,7 @@ namespace capdec {
 // teacher forcing reads caller-supplied token ids: an id outside the vocabulary must not become an out-of-bounds read
 __device__ __forceinline__ int clamp_token(long long t, int vocab) { return t < 0 ? 0 : (t >= vocab ? vocab - 1 : (int)t); }
 
-__global__ void init_rollout_kernel(DecState* st, const CallParams* cp, unsigned char* fin, int M, int* counters) {
+__global__ void init_rollout_kernel(DecState* st, const CallParams* cp, unsigned char* fin, int M) {
   const CallParams p = *cp;
   const int tid = blockIdx.x * blockDim.x + threadIdx.x;
   if (tid == 0) {
@@ -28,8 +28,6 @@ __global__ void init_rollout_kernel(DecState* st, const CallParams* cp, unsigned
     if (p.logp != nullptr && i < M * (p.max_len - 1)) p.logp[i] = 0.f;
   }
   if (tid < M) fin[tid] = 0;
-  if (counters != nullptr)
-    for (int i = tid; i < p.max_len * 4; i += gridDim.x * blockDim.x) counters[i] = 0;
 }
 
 // x[m,:] = emb[tok]*sqrt(512) + pe[n,:]; separate multiply and add (no FMA contraction) so the

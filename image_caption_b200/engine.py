@@ -79,11 +79,10 @@ class CaptionDecodeEngine:
         if precision not in ("bf16", "fp32"):
             raise ValueError(f"precision must be 'bf16' or 'fp32', got {precision!r}")
         self.precision = precision
-        if step_impl not in ("v1", "v2", "v3"):
-            raise ValueError(f"step_impl must be 'v1', 'v2' or 'v3', got {step_impl!r}")
+        if step_impl not in ("v1", "v2"):
+            raise ValueError(f"step_impl must be 'v1' or 'v2', got {step_impl!r}")
         self._flags = ((0 if use_graph else _lib.FLAG_NO_GRAPH) | (0 if use_umma else _lib.FLAG_NO_UMMA)
-                       | (_lib.FLAG_V1_STEP if step_impl == "v1" else 0) | (0 if pdl else _lib.FLAG_NO_PDL)
-                       | (0 if step_impl == "v3" else _lib.FLAG_NO_CLUSTER_ROLLOUT))
+                       | (_lib.FLAG_V1_STEP if step_impl == "v1" else 0) | (0 if pdl else _lib.FLAG_NO_PDL))
         self._cap = dict(max_images=max_images, max_group=max_group, max_mem=max_mem, max_len=max_len)
         self._h = C.c_void_p()
         self._weights_sig = None
@@ -418,13 +417,22 @@ class CaptionDecodeEngine:
         The rollout samples from the eval-mode distribution on the engine.  When autograd is
         enabled the returned log-probs are recomputed by ONE teacher-forced pass of the reference
         decoder over the sampled ids (row k of that pass is the step-k distribution), so
-        ``loss.backward()`` reaches decoder and encoder exactly as scst:183-191 expects."""
+        ``loss.backward()`` reaches decoder and encoder exactly as scst:183-191 expects.
+
+        Stated deviation: the reference runs this loop under ``model.train()``
+        (scst:161), i.e. it samples from and scores with a distribution whose prefix activations are
+        re-dropped at every step.  A KV-cached engine cannot reproduce that; tokens come from the
+        eval-mode distribution, and the differentiable scoring pass runs in whatever mode the caller
+        left the model in (one dropout draw if it is in train mode; in ``eval()`` it reproduces the
+        engine's own log-probs to the precision tolerance, which the GPU tests assert).  ``device`` is
+        where the reference creates its token tensor (scst:216); results are returned there."""
         memory = model.encoder(images)  # scst:213
         if seed is None:
             seed = int(torch.randint(0, 2 ** 62, (1,)).item())  # follows torch's global generator
         out = self.decode_from_memory(memory, start_token, end_token, max_len, group=1, n_sample=1, seed=seed)
+        dst = torch.device(device) if device is not None else out.ids.device
         if not torch.is_grad_enabled():
-            return out.ids, out.logp
+            return out.ids.to(dst), out.logp.to(dst)
         ids = out.ids
         t = ids.size(1) - 1
         mask = model.decoder.generate_square_subsequent_mask(t, ids.device)
@@ -432,7 +440,7 @@ class CaptionDecodeEngine:
         lp = torch.log_softmax(logits, dim=-1).gather(2, ids[:, 1:, None]).squeeze(2)
         ended = ids[:, 1:] == end_token
         finished_before = (ended.cumsum(1) - ended.long()) > 0  # finished strictly before this step
-        return ids, lp.masked_fill(finished_before, 0.0)
+        return ids.to(dst), lp.masked_fill(finished_before, 0.0).to(dst)
 
     # ------------------------------------------------------------------ diagnostics
     def profile(self, on: bool) -> None:

@@ -17,31 +17,38 @@ from .engine import CaptionDecodeEngine
 
 
 def engine_for(model: torch.nn.Module, **engine_kwargs) -> CaptionDecodeEngine:
-    """One engine per model instance, created on first use from ``model.decoder``."""
+    """One engine per model instance, created on first use from ``model.decoder`` (which must then be on a CUDA
+    device: there is no CPU path, ``CaptionDecodeEngine`` raises)."""
     eng: Optional[CaptionDecodeEngine] = getattr(model, "_capdec_engine", None)
     if eng is None:
-        eng = CaptionDecodeEngine(model.decoder, **engine_kwargs)
+        kw = dict(getattr(model, "_capdec_engine_kwargs", {}))
+        kw.update(engine_kwargs)
+        eng = CaptionDecodeEngine(model.decoder, **kw)
         object.__setattr__(model, "_capdec_engine", eng)  # not a submodule / parameter
     return eng
 
 
-def install(model: torch.nn.Module, **engine_kwargs) -> CaptionDecodeEngine:
-    if getattr(model, "_capdec_reference_generate", None) is not None:
-        return engine_for(model)
-    eng = engine_for(model, **engine_kwargs)
-    object.__setattr__(model, "_capdec_reference_generate", model.generate)
+def install(model: torch.nn.Module, **engine_kwargs) -> Optional[CaptionDecodeEngine]:
+    """Rebind ``model.generate`` (vit:276 / grid:222; same positional order, same defaults; the ViT model's
+    signature has no ``beam_size`` and ignores it, vit:291).  The engine is created now when the decoder already
+    lives on a CUDA device, else on the first call (scripts move the model with ``.to(device)`` after building it)."""
+    if getattr(model, "_capdec_reference_generate", None) is None:
+        object.__setattr__(model, "_capdec_engine_kwargs", dict(engine_kwargs))
+        object.__setattr__(model, "_capdec_reference_generate", model.generate)
 
-    def generate(self, images, start_token, end_token, max_len=50, method="greedy", beam_size=5):
-        return self._capdec_engine.generate(self, images, start_token, end_token, max_len, method, beam_size)
+        def generate(self, images, start_token, end_token, max_len=50, method="greedy", beam_size=5):
+            return engine_for(self).generate(self, images, start_token, end_token, max_len, method, beam_size)
 
-    object.__setattr__(model, "generate", types.MethodType(generate, model))
-    return eng
+        object.__setattr__(model, "generate", types.MethodType(generate, model))
+    on_cuda = any(p.is_cuda for p in model.decoder.parameters())
+    return engine_for(model) if on_cuda else None
 
 
 def uninstall(model: torch.nn.Module) -> None:
     if getattr(model, "_capdec_reference_generate", None) is not None:
         object.__delattr__(model, "generate")
         object.__delattr__(model, "_capdec_reference_generate")
+        object.__delattr__(model, "_capdec_engine_kwargs")
     eng = getattr(model, "_capdec_engine", None)
     if eng is not None:
         eng.close()

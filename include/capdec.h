@@ -57,16 +57,20 @@ typedef enum {
 } capdec_precision;
 
 typedef struct {
-  int32_t vocab;       /* V   (data/vocab.json: 109)                          */
+  /* Hard shape limits of this build (capdec_create returns CAPDEC_ERR_INVALID outside them):
+   * vocab in [2,128], d_model == 512, n_head == 8, d_ff a multiple of 128, max_len in [2,128],
+   * memory length <= 256 on the bf16 tensor-core path.  Every shipped reference config
+   * (d_model 512 / nhead 8 / ffn 2048 / vocab 109 / max_len <= 64, S = 196 or 49) is inside them. */
+  int32_t vocab;       /* V   (data/vocab.json: 109); 2..128                  */
   int32_t d_model;     /* must be 512                                          */
   int32_t n_head;      /* must be 8 (head dim 64)                              */
   int32_t n_layer;     /* 1..CAPDEC_MAX_LAYERS                                 */
-  int32_t d_ff;        /* multiple of 64                                       */
+  int32_t d_ff;        /* multiple of 128                                      */
   int32_t pe_rows;     /* rows of pos_encoder.pe (the model's max_len)         */
   int32_t max_mem;     /* largest memory length S (196 ViT, 49 grid)           */
   int32_t max_images;  /* largest number of images per call                    */
   int32_t max_group;   /* largest sequences-per-image                          */
-  int32_t max_len;     /* largest generate(max_len=...)                        */
+  int32_t max_len;     /* largest generate(max_len=...); 2..128               */
   int32_t precision;   /* capdec_precision                                     */
   int32_t flags;       /* CAPDEC_FLAG_*                                        */
 } capdec_config;
@@ -76,7 +80,6 @@ typedef struct {
 #define CAPDEC_FLAG_V1_STEP 4    /* bf16 mode: the first-generation step kernels (one GEMM tile per CTA,
                                     separate LayerNorm / vocabulary / head kernels); kept for A/B runs */
 #define CAPDEC_FLAG_NO_PDL 8     /* do not chain the step's kernels with programmatic dependent launch */
-#define CAPDEC_FLAG_NO_CLUSTER_ROLLOUT 16 /* never use the whole-rollout cluster kernel (per-step kernels only) */
 
 /* fp32 DEVICE pointers, borrowed for the duration of capdec_set_weights only. */
 typedef struct {

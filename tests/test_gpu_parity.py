@@ -3,10 +3,11 @@
 
 Tolerances (stated once, used everywhere):
   fp32 mode  max |logit - oracle| <= 2e-4   (summation-order differences only; measured ~1e-5)
-  bf16 mode  max |logit - oracle| <= 1e-1   (weights, KV and GEMM inputs rounded to bf16, fp32
-             accumulate; weight rounding alone moves logits by 2.2e-2)
+  bf16 mode  max |logit - oracle| <= 4e-2   (weights, KV and GEMM inputs rounded to bf16, fp32
+             accumulate; weight rounding alone moves logits by 2.2e-2; the largest
+             error measured over this suite on B200 is ~2e-2, the tolerance is twice that)
 Greedy ids must equal argmax of the oracle's logits wherever the oracle's top-2 gap exceeds
-twice the mode's tolerance; sampled log-probs must equal log_softmax(oracle logits)[id] within the
+the mode's tolerance; sampled log-probs must equal log_softmax(oracle logits)[id] within the
 tolerance and be exactly 0 after a row's <end>.  All checks are teacher-forced on the engine's own
 ids so that one legitimate near-tie cannot cascade.
 """
@@ -19,7 +20,13 @@ from oracle import decoder_np, philox, torch_port
 
 pytestmark = pytest.mark.gpu
 
-TOL = {"fp32": 2e-4, "bf16": 1e-1}
+TOL = {"fp32": 2e-4, "bf16": 4e-2}
+MEASURED = {}  # largest |logit - oracle| seen per tolerance class, written to gpurun_out/parity_errors.json by the last test
+
+
+def _record(tol, err):
+    key = "fp32" if tol <= 1e-3 else "bf16"
+    MEASURED[key] = max(MEASURED.get(key, 0.0), float(err))
 
 
 @pytest.fixture(scope="module")
@@ -51,6 +58,7 @@ def check_rollout(out, w, mem, group, n_sample, tol, seed=0, seq_id_base=0):
     ref = oracle_logits(w, ids, mem, group)
     if out.logits is not None:
         err = np.abs(out.logits.cpu().numpy() - ref).max()
+        _record(tol, err)
         assert err <= tol, f"logits differ by {err}"
     is_sample = (np.arange(m) % group) < n_sample
     # greedy rows: argmax of the oracle's logits unless the oracle's top-2 gap is inside the tolerance
@@ -58,7 +66,7 @@ def check_rollout(out, w, mem, group, n_sample, tol, seed=0, seq_id_base=0):
     gap = srt[..., -1] - srt[..., -2]
     want = ref.argmax(-1)
     g = ~is_sample
-    bad = (ids[g, 1:] != want[g]) & (gap[g] > 2 * tol)
+    bad = (ids[g, 1:] != want[g]) & (gap[g] > tol)
     assert not bad.any(), f"{bad.sum()} greedy tokens differ outside the tie tolerance"
     if n_sample:
         lp = out.logp.cpu().numpy()
@@ -359,48 +367,6 @@ def test_v2_step_matches_v1_step(dev, pdl):
     same = (res[0][0] == res[1][0]).all(1)
     assert same.float().mean() > 0.8
     assert (res[0][1][same] - res[1][1][same]).abs().max() < 3e-2
-
-
-# ------------------------------------------------------------------ v3: whole-rollout cluster kernel
-@pytest.mark.parametrize("rb", [16])
-@pytest.mark.parametrize("n_img,group,n_sample,mem_len", [(40, 1, 0, 49), (21, 2, 1, 49), (9, 4, 3, 33), (3, 16, 15, 64), (1, 1, 0, 7)])
-def test_v3_cluster_rollout(dev, monkeypatch, rb, n_img, group, n_sample, mem_len):
-    """One cluster of 8 CTAs per block of sequences runs every layer of every step (rollout_cluster.cuh):
-    several blocks, ragged last block, groups sharing an image's K/V tile, chunked steps (3 per launch)."""
-    monkeypatch.setenv("CAPDEC_RB", str(rb))
-    monkeypatch.setenv("CAPDEC_CHUNK", "3")
-    dec = small_decoder(layers=2, end_bias=1.0)
-    w = torch_port.weights_to_numpy(dec)
-    mem = torch_port.synthetic_memory(n_img, mem_len)
-    eng = make_engine(dec.to(dev), "bf16", step_impl="v3", max_images=n_img, max_group=group, max_mem=mem_len, max_len=12)
-    out = eng.decode_from_memory(mem.to(dev), START, END, max_len=12, group=group, n_sample=n_sample, seed=21,
-                                 seq_id_base=500, return_logits=True)
-    check_rollout(out, w, mem.numpy(), group, n_sample, TOL["bf16"], seed=21, seq_id_base=500)
-    eng.close()
-
-
-def test_v3_matches_v2_and_stops_like_v2(dev):
-    """Same rollout through the per-step kernels and the cluster kernel: same stop step (the stop rule is
-    applied to per-step counters after each chunk), same padding after it, near-identical logits."""
-    dec = small_decoder(layers=3, end_bias=6.0).to(dev)
-    mem = torch_port.synthetic_memory(13, 49).to(dev)
-    res = []
-    for impl in ("v2", "v3"):
-        eng = make_engine(dec, "bf16", step_impl=impl, max_images=13, max_group=2, max_mem=49, max_len=24)
-        o = eng.decode_from_memory(mem, START, END, max_len=24, group=2, n_sample=2, seed=7, return_logits=True, trim=False)
-        res.append(o)
-        eng.close()
-    a, b = res
-    assert a.steps < 23 and b.steps < 23, "with end_bias=6 every sampled row finishes early"
-    assert (a.ids.cpu()[:, a.steps + 1:] == PAD).all() and (b.ids.cpu()[:, b.steps + 1:] == PAD).all()
-    assert (b.logp.cpu()[:, b.steps:] == 0).all()
-    k = min(a.steps, b.steps)
-    same = (a.ids.cpu()[:, :k + 1] == b.ids.cpu()[:, :k + 1]).all(1)
-    assert same.float().mean() > 0.7
-    if bool(same.all()):
-        assert a.steps == b.steps
-    d = (a.logits.cpu()[same][:, :k] - b.logits.cpu()[same][:, :k]).abs().max()
-    assert d < 3e-2, d
 
 
 def test_weight_updates_are_picked_up(dev):
@@ -770,6 +736,9 @@ def test_teacher_forced_grouped_and_v1(dev):
 FULL_SIZE = {  # images, memory length, rollouts per image, sampled rollouts, max_len (bench.py WORKLOADS)
     "cfg2": (256, 49, 1, 0, 50),
     "cfg3": (512, 196, 6, 5, 50),
+    "cfg4_per_gpu_n2": (256, 196, 6, 5, 50),   # cfg3's 512 images over 2 / 4 / 8 GPUs
+    "cfg4_per_gpu_n4": (128, 196, 6, 5, 50),
+    "cfg4_per_gpu_n8": (64, 196, 6, 5, 50),
     "cfg5_per_gpu": (1024, 49, 1, 0, 64),
 }
 
@@ -780,16 +749,18 @@ def test_full_size_rollout_properties(dev, name):
     of its step's logits; (2) sampled log-probs are log_softmax(logits)[id], exactly 0 after a row's <end> and for
     greedy rows; (3) a teacher-forced replay of the produced ids returns the rollout's logits and log-probs bit for
     bit (KV caches, step state and graph replay hold no hidden state); (4) permuting the images permutes the results
-    (rows do not interact; a row's arithmetic does not depend on its tile position); (5) rows at tile boundaries
-    against the CPU oracle within the bf16 tolerance."""
+    (rows do not interact; a row's arithmetic does not depend on its tile position); (5) at least 64 rows -- the tile
+    boundaries plus rows spread over every 128-row tile -- against the CPU oracle within the bf16 tolerance, greedy ids
+    equal to the oracle's argmax outside the tie tolerance."""
     from image_caption_b200.synthetic import random_decoder, random_memory
     n_img, S, G, ns, max_len = FULL_SIZE[name]
     M = n_img * G
-    dec = random_decoder(0, pe_rows=max(52, max_len))
-    w = torch_port.weights_to_numpy(dec)
+    dec = torch_port.build_decoder(0, max_len=max(52, max_len), perturb=0.02)  # == synthetic.random_decoder(0), with a forward
+    assert all(torch.equal(a, b) for a, b in zip(dec.state_dict().values(), random_decoder(0, pe_rows=max(52, max_len)).state_dict().values()))
     mem = random_memory(n_img, S)
     memd = mem.to(dev)
-    eng = make_engine(dec.to(dev), "bf16", max_images=n_img, max_group=G, max_mem=S, max_len=max_len)
+    import copy
+    eng = make_engine(copy.deepcopy(dec).to(dev), "bf16", max_images=n_img, max_group=G, max_mem=S, max_len=max_len)
     run = lambda m: eng.decode_from_memory(m, START, END, max_len=max_len, group=G, n_sample=ns, seed=2024,
                                            return_logits=True, early_stop=False, trim=False)
     out = run(memd)
@@ -820,7 +791,174 @@ def test_full_size_rollout_properties(dev, name):
     assert torch.equal(outp.ids[~sample], ids[rows][~sample])
     assert torch.equal(outp.logits[~sample], logits[rows][~sample])
     # (5)
-    R = sorted({0, 31, 32, 127, 128, M // 2 + 1, M - 129, M - 33, M - 1})
-    ref = decoder_np.decoder_forward(w, ids[R, :-1].cpu().numpy(), mem.numpy()[[r // G for r in R]])
-    assert np.abs(logits[R].cpu().numpy() - ref).max() < TOL["bf16"]
+    R = {0, 31, 32, 63, 64, 127, 128, M // 2 + 1, M - 129, M - 65, M - 33, M - 1}
+    n_tiles = (M + 127) // 128
+    per_tile = max(1, -(-56 // n_tiles))
+    rg = np.random.default_rng(5)
+    for t in range(n_tiles):
+        R.update(int(r) for r in rg.integers(t * 128, min(M, (t + 1) * 128), size=per_tile))
+    R = sorted(r for r in R if 0 <= r < M)
+    assert len(R) >= min(64, M)
+    with torch.no_grad():  # oracle = the torch.nn re-assembly pinned to the reference by tests/golden
+        ref = torch_port.teacher_forced_logits(dec, ids[R].cpu(), mem[[r // G for r in R]]).numpy()
+    got = logits[R].cpu().numpy()
+    _record(TOL["bf16"], np.abs(got - ref).max())
+    assert np.abs(got - ref).max() < TOL["bf16"]
+    srt = np.sort(ref, -1)
+    gap = srt[..., -1] - srt[..., -2]
+    gr = np.array([(r % G) >= ns for r in R])
+    tokR = ids[R, 1:].cpu().numpy()
+    bad = (tokR[gr] != ref.argmax(-1)[gr]) & (gap[gr] > TOL["bf16"])
+    assert not bad.any()
     eng.close()
+
+
+# ---------------------------------------------------------------- SCST drop-in boundary (scst:202-254 through patch.install_scst)
+class _RefLikeDecoder(torch_port.PortDecoder):
+    """PortDecoder plus the reference decoder's mask helper (vit:149-153), which the shim's autograd pass calls."""
+
+    def generate_square_subsequent_mask(self, sz, device):
+        return torch_port.PortDecoder.causal_mask(sz, device)
+
+
+class _ScstModel(torch.nn.Module):
+    def __init__(self, decoder):
+        super().__init__()
+        self.encoder = torch.nn.Linear(512, 512)  # a trainable stand-in for the image encoder: memory = encoder(images)
+        self.decoder = decoder
+
+    def generate(self, *a, **k):
+        raise AssertionError("the reference path must not run")
+
+
+class _ScstLoss(torch.nn.Module):
+    """Stands in for utils/scst_loss.py:SCSTLoss (its import needs pycocoevalcap): same method name and signature."""
+
+    def _sample_with_log_probs(self, model, images, start_token, end_token, max_len, device):
+        raise AssertionError("the reference loop must not run")
+
+
+def _scst_setup(dev, precision):
+    from image_caption_b200 import patch
+    torch.manual_seed(3)
+    dec = _RefLikeDecoder(VOCAB, 512, 8, 2, 2048, 0.1, 24)
+    with torch.no_grad():
+        for p_ in dec.parameters():
+            p_.add_(torch.randn_like(p_) * 0.02)
+        dec.fc_out.bias[END] += 2.0
+    model = _ScstModel(dec).to(dev)
+    loss = _ScstLoss()
+    patch.install(model, precision=precision, max_images=6, max_group=1, max_mem=49, max_len=14)
+    patch.install_scst(loss, precision=precision, max_images=6, max_group=1, max_mem=49, max_len=14)
+    feats = torch_port.synthetic_memory(6, 49, seed=21).to(dev)  # "images": the stand-in encoder maps them to memory
+    return patch, model, loss, feats
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_install_scst_no_grad_path_is_the_engine_rollout(dev, precision):
+    """SCSTLoss._sample_with_log_probs rebound by patch.install_scst: under no_grad it returns exactly what
+    decode_from_memory(group=1, n_sample=1) returns for the seed the shim drew from torch's global generator."""
+    patch, model, loss, feats = _scst_setup(dev, precision)
+    model.eval()
+    with torch.no_grad():
+        torch.manual_seed(99)
+        ids, lp = loss._sample_with_log_probs(model, feats, START, END, 14, dev)
+        torch.manual_seed(99)
+        seed = int(torch.randint(0, 2 ** 62, (1,)).item())
+        ref = model._capdec_engine.decode_from_memory(model.encoder(feats), START, END, 14, group=1, n_sample=1, seed=seed)
+    assert ids.dtype == torch.int64 and ids.device.type == "cuda" and not lp.requires_grad
+    assert torch.equal(ids, ref.ids) and torch.equal(lp, ref.logp)
+    assert ids.shape[1] == lp.shape[1] + 1 and (ids[:, 0] == START).all()
+    patch.uninstall_scst(loss)
+    with pytest.raises(AssertionError):
+        loss._sample_with_log_probs(model, feats, START, END, 14, dev)
+    patch.uninstall(model)
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_install_scst_grad_path_rederives_the_log_probs(dev, precision):
+    """With autograd on (scst:164, model in eval mode here so that the scoring pass has no dropout): the returned
+    log-probs carry grad, equal log_softmax(decoder(ids[:, :-1]))[ids] masked as scst:236-239 (exact zeros once a row
+    has finished), equal the engine's own log-probs within the mode's tolerance, and the SCST loss (scst:183-191)
+    back-propagates into decoder AND encoder parameters."""
+    patch, model, loss, feats = _scst_setup(dev, precision)
+    model.eval()
+    torch.manual_seed(7)
+    ids, lp = loss._sample_with_log_probs(model, feats, START, END, 14, dev)
+    assert lp.requires_grad and lp.shape == (6, ids.shape[1] - 1)
+    with torch.no_grad():
+        torch.manual_seed(7)
+        seed = int(torch.randint(0, 2 ** 62, (1,)).item())
+        eng_out = model._capdec_engine.decode_from_memory(model.encoder(feats), START, END, 14, group=1, n_sample=1, seed=seed)
+        assert torch.equal(eng_out.ids, ids)
+        t = ids.shape[1] - 1
+        logits = model.decoder(ids[:, :-1], model.encoder(feats), tgt_mask=torch_port.PortDecoder.causal_mask(t, dev))
+        want = torch.log_softmax(logits, -1).gather(2, ids[:, 1:, None]).squeeze(2)
+        ended = ids[:, 1:] == END
+        after = (ended.cumsum(1) - ended.long()) > 0
+        want = want.masked_fill(after, 0.0)
+    assert after.any(), "with end_bias=2 some rows must finish before the rollout stops"
+    assert torch.equal(lp.detach() == 0, want == 0) and (lp.detach()[after] == 0).all()
+    assert (lp.detach() - want).abs().max() < 1e-5
+    assert (lp.detach() - eng_out.logp).abs().max() < TOL[precision]
+    adv = torch.linspace(-1, 1, 6, device=dev)
+    scst = -(adv * lp.sum(1)).mean()  # scst:183-191
+    scst.backward()
+    assert model.decoder.fc_out.weight.grad is not None and float(model.decoder.fc_out.weight.grad.abs().sum()) > 0
+    assert model.encoder.weight.grad is not None and float(model.encoder.weight.grad.abs().sum()) > 0
+    patch.uninstall_scst(loss)
+    patch.uninstall(model)
+
+
+# ---------------------------------------------------------------- sharding invariance on real GPUs (SURVEY 8e)
+def _nccl_worker(rank, world, port, out_path):
+    import os
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    from image_caption_b200 import CaptionDecodeEngine
+    from image_caption_b200.dist import sharded_rollout
+    dec = small_decoder(layers=2, end_bias=2.5).to(dev)
+    n_img, G, ns, max_len = 37, 3, 2, 16   # ragged shards: 19 + 18 images
+    mem = torch_port.synthetic_memory(n_img, 49).to(dev)
+    eng = CaptionDecodeEngine(dec, precision="bf16", max_images=n_img, max_group=G, max_mem=49, max_len=max_len)
+
+    def local(lo, hi, base):
+        o = eng.decode_from_memory(mem[lo:hi].contiguous(), START, END, max_len=max_len, group=G, n_sample=ns, seed=31,
+                                   seq_id_base=base, trim=False, early_stop=False)
+        return o.ids, o.logp
+
+    ids, lp = sharded_rollout(local, n_img, START, END, max_len, group=G, n_sample=ns, seed=31)
+    if rank == 0:
+        full = eng.decode_from_memory(mem, START, END, max_len=max_len, group=G, n_sample=ns, seed=31)
+        torch.save({"ids": ids.cpu(), "lp": lp.cpu(), "full_ids": full.ids.cpu(), "full_lp": full.logp.cpu()}, out_path)
+    eng.close()
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_sharded_rollout_two_gpus_equals_one_gpu(tmp_path):
+    """Two ranks over NCCL, ragged shards, global Philox sequence ids: the gathered, reference-width-trimmed result
+    is bit-equal to the single-GPU rollout of the same batch with its own early stop (dist.py's claims on hardware)."""
+    import socket
+    import torch.multiprocessing as mp
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    out = str(tmp_path / "r.pt")
+    mp.spawn(_nccl_worker, args=(2, port, out), nprocs=2, join=True)
+    r = torch.load(out)
+    assert r["ids"].shape == r["full_ids"].shape, (r["ids"].shape, r["full_ids"].shape)
+    assert torch.equal(r["ids"], r["full_ids"]) and torch.equal(r["lp"], r["full_lp"])
+
+
+def test_zz_report_measured_errors():
+    """Not a check: leaves the largest logit errors this run measured where the builder can read them."""
+    import json
+    import os
+    from conftest import ROOT
+    d = os.path.join(ROOT, "gpurun_out")
+    if os.path.isdir(d):
+        with open(os.path.join(d, "parity_errors.json"), "w") as f:
+            json.dump({"max_abs_logit_error": MEASURED, "tolerance": TOL}, f)

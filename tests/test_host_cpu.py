@@ -186,3 +186,93 @@ def test_vit_encoder_tokens_restates_the_reference_encoder():
         tok = vit_encoder_tokens(enc, images)
         assert tok.shape == (1, 197, 768)
         assert torch.equal(enc.projection(tok[:, 1:, :]), ref)
+
+
+# ------------------------------------------------------------------ installation onto the REAL reference classes
+REF = "/root/reference"
+
+
+def _load_reference_module(rel, name):
+    import importlib.util
+    spec = importlib.util.spec_from_file_location(name, os.path.join(REF, rel))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+def _load_reference_scst():
+    """utils/scst_loss.py imports pycocoevalcap at module level (scst:16-17), which is not installed: stub modules
+    are registered first; the reference file itself is loaded unmodified (same recipe as tests/golden/make_golden.py)."""
+    import types
+    for name in ("pycocoevalcap", "pycocoevalcap.cider", "pycocoevalcap.cider.cider", "pycocoevalcap.bleu",
+                 "pycocoevalcap.bleu.bleu"):
+        sys.modules.setdefault(name, types.ModuleType(name))
+    sys.modules["pycocoevalcap.cider.cider"].Cider = type("Cider", (), {})
+    sys.modules["pycocoevalcap.bleu.bleu"].Bleu = type("Bleu", (), {"__init__": lambda self, n=4: None})
+    return _load_reference_module("utils/scst_loss.py", "_ref_scst_loss")
+
+
+@pytest.mark.skipif(not os.path.exists(REF), reason="reference checkout not present")
+@pytest.mark.parametrize("which", ["vit", "grid"])
+def test_install_rebinds_the_real_reference_model(which):
+    """patch.install on ViTTransformerCaptioning / GridTransformerCaptioning (vit:276, grid:222): the rebound
+    ``generate`` takes the reference's positional order and keyword names with the same defaults, the engine reads
+    exactly the state-dict keys the real decoder has, there is no CPU fallback (the first call on a CPU model raises),
+    and ``uninstall`` restores the reference method."""
+    import inspect
+    from image_caption_b200 import patch
+    from image_caption_b200.engine import _LAYER_FIELDS
+    if which == "vit":
+        mod = _load_reference_module("models/vit_transformer_model.py", "_ref_vit")
+        cls, kw = mod.ViTTransformerCaptioning, dict(pretrained_vit=False)
+    else:
+        mod = _load_reference_module("models/grid_transformer_model.py", "_ref_grid")
+        cls, kw = mod.GridTransformerCaptioning, dict(pretrained_cnn=False)
+    torch.manual_seed(0)
+    model = cls(vocab_size=109, num_decoder_layers=2, num_encoder_layers=1, max_len=52, **kw)
+    ref_sig = inspect.signature(model.generate)
+    ref_generate = model.generate
+    assert patch.install(model) is None, "a CPU model gets no engine at install time (created on first CUDA use)"
+    new_sig = inspect.signature(model.generate)
+    assert model.generate.__func__ is not ref_generate.__func__
+    for name, p in ref_sig.parameters.items():  # every reference parameter: same name, same position, same default
+        q = new_sig.parameters[name]
+        assert list(new_sig.parameters).index(name) == list(ref_sig.parameters).index(name)
+        assert q.default == p.default, name
+    assert set(new_sig.parameters) - set(ref_sig.parameters) <= {"beam_size"}  # the Grid model's extra keyword (grid:222)
+    # the engine's weight table names exactly the real decoder's parameters
+    keys = set(model.decoder.state_dict().keys())
+    want = {"embedding.weight", "pos_encoder.pe", "fc_out.weight", "fc_out.bias"}
+    for i in range(2):
+        pre = f"transformer_decoder.layers.{i}."
+        want |= {pre + k for _, k in _LAYER_FIELDS}
+        want |= {f"{pre}norm{j}.{p}" for j in (1, 2, 3) for p in ("weight", "bias")}
+    assert want == keys
+    assert model.decoder.transformer_decoder.layers[0].norm_first is False
+    images = torch.zeros(1, 3, 224, 224)
+    with pytest.raises(RuntimeError, match="CUDA"):  # no CPU path: fails loudly instead of falling back
+        model.generate(images, 107, 108, max_len=5, method="greedy")
+    patch.uninstall(model)
+    assert model.generate.__func__ is ref_generate.__func__
+    with pytest.raises(ValueError):
+        model.generate(images, 107, 108, method="nucleus")  # the reference's own dispatcher again (vit:294)
+
+
+@pytest.mark.skipif(not os.path.exists(REF), reason="reference checkout not present")
+def test_install_scst_rebinds_the_real_scst_loss():
+    """patch.install_scst on the real SCSTLoss (scst:202): same method name, same parameter list; SCSTLoss.forward's
+    own call `self._sample_with_log_probs(model, images, start, end, max_len, device)` (scst:164-166) binds to it."""
+    import inspect
+    from image_caption_b200 import patch
+    scst = _load_reference_scst()
+    loss = scst.SCSTLoss.__new__(scst.SCSTLoss)
+    torch.nn.Module.__init__(loss)
+    ref_sig = inspect.signature(loss._sample_with_log_probs)
+    ref_func = loss._sample_with_log_probs.__func__
+    patch.install_scst(loss)
+    assert list(inspect.signature(loss._sample_with_log_probs).parameters) == list(ref_sig.parameters)
+    assert loss._sample_with_log_probs.__func__ is not ref_func
+    src = inspect.getsource(scst.SCSTLoss.forward)
+    assert "self._sample_with_log_probs(" in src and "model.generate(" in src  # the two call sites the shims serve
+    patch.uninstall_scst(loss)
+    assert loss._sample_with_log_probs.__func__ is ref_func

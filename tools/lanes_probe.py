@@ -16,7 +16,7 @@ ap.add_argument("--lanes", default="1,2,3,4")
 ap.add_argument("--reps", type=int, default=5)
 ap.add_argument("--prio", action="store_true", help="alternate stream priorities between lanes")
 a = ap.parse_args()
-desc, n_img, S, G, ns, max_len = WORKLOADS[a.workload]
+desc, n_img, S, G, ns, max_len, _ = WORKLOADS[a.workload]
 dev = torch.device("cuda:0")
 dec = random_decoder(0, pe_rows=max(52, max_len)).to(dev)
 mem = random_memory(n_img, S, seed=1234).to(dev)

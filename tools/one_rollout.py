@@ -9,7 +9,7 @@ from image_caption_b200 import CaptionDecodeEngine
 from image_caption_b200.synthetic import random_decoder, random_memory
 wl = sys.argv[1]; reps = int(sys.argv[2]) if len(sys.argv) > 2 else 1
 max_len_override = int(os.environ.get("MAXLEN", "0"))
-desc, n_img, S, G, ns, max_len = WORKLOADS[wl]
+desc, n_img, S, G, ns, max_len, _ = WORKLOADS[wl]
 if max_len_override: max_len = max_len_override
 dev = torch.device("cuda:0")
 dec = random_decoder(0, pe_rows=max(52, max_len)).to(dev)

@@ -11,13 +11,13 @@ from image_caption_b200.synthetic import random_decoder, random_memory
 
 ap = argparse.ArgumentParser()
 ap.add_argument("workload")
-ap.add_argument("--variants", default="v3,v2,v1")
+ap.add_argument("--variants", default="v2,v1")
 ap.add_argument("--bnb", default="")
 ap.add_argument("--stages", default="")
 ap.add_argument("--reps", type=int, default=5)
 ap.add_argument("--images", type=int, default=0)
 a = ap.parse_args()
-desc, n_img, S, G, ns, max_len = WORKLOADS[a.workload]
+desc, n_img, S, G, ns, max_len, _ = WORKLOADS[a.workload]
 if a.images: n_img = a.images
 dev = torch.device("cuda:0")
 dec = random_decoder(0, pe_rows=max(52, max_len)).to(dev)
