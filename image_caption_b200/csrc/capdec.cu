@@ -17,6 +17,7 @@
 #include "cross_attn_tma.cuh"
 #include "attention.cuh"
 #include "pointwise.cuh"
+#include "layer_chain.cuh"
 
 using namespace capdec;
 
@@ -222,6 +223,14 @@ static int gemm(capdec_handle h, cudaStream_t s, const void* a_ptr, const CUtens
 // All v2 step kernels begin with griddepcontrol.wait, so they may be chained with programmatic
 // dependent launch: the next kernel's prologue (barrier init, TMEM alloc, descriptor prefetch)
 // overlaps the tail of the current one.
+// INVARIANT the attention / sum_ln / head kernels rely on: they read DecState (st->step, st->done) BEFORE their wait.
+// DecState is written only by the head kernel, at the end of a step.  That is safe only because every kernel of the
+// chain executes griddepcontrol.wait in all of its CTAs before anything else of the step can have completed, and at
+// least one full kernel (the layer-0 in_proj) separates the head from the first early reader: a grid can start under
+// programmatic launch only after ALL CTAs of its predecessor have triggered, each of which waited for ITS predecessor
+// to complete -- so when kernel k+2 starts, kernel k has completed and flushed.  A new kernel placed directly after the
+// head must therefore read DecState after its wait (the projection chains in layer_chain.cuh do).  The PDL on/off
+// parity test (test_v2_step_matches_v1_step) guards the ordering.
 template <typename... KArgs, typename... Args>
 static cudaError_t launch_ex(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, int cluster_x,
                              bool pdl, Args&&... args) {
@@ -368,6 +377,68 @@ static cudaError_t configure_fast_kernels() {
   return e;
 }
 
+// ------------------------------------------------------------------ cluster-resident projection chains (layer_chain.cuh)
+template <int BNB, int CS>
+static int chain_stages() {
+  return std::min(10, (kMaxDynSmem - 1024 - ChSmem<BNB, CS>::kRing) / kChSlot);
+}
+
+template <int BNB, int CS, int KIND>
+static int launch_chain_t(capdec_handle h, cudaStream_t s, const CUtensorMap& tm_b, const ChainParams& P, int M) {
+  const int stages = chain_stages<BNB, CS>();
+  const int tiles = (M + BNB - 1) / BNB;
+  ProfScope ps(h, s);
+  cudaError_t e = launch_ex(chain_kernel<BNB, CS, KIND>, dim3(CS * tiles), dim3(kChThreads), ChSmem<BNB, CS>::bytes(stages), s, CS,
+                            h->use_pdl, tm_b, P, stages);
+  if (e != cudaSuccess)
+    return fail(h, CAPDEC_ERR_CUDA, "chain kernel launch failed: %s (BNB=%d CS=%d kind=%d stages=%d)", cudaGetErrorString(e), BNB, CS,
+                KIND, stages);
+  h->launches_this_enqueue++;
+  return 0;
+}
+
+template <int KIND>
+static int launch_chain(capdec_handle h, cudaStream_t s, const CUtensorMap& tm_b, const ChainParams& P, int M) {
+  if (h->chain_cs == 8) {
+    if (h->chain_bnb == 32) return launch_chain_t<32, 8, KIND>(h, s, tm_b, P, M);
+    return launch_chain_t<64, 8, KIND>(h, s, tm_b, P, M);
+  }
+  if (h->chain_bnb == 32) return launch_chain_t<32, 4, KIND>(h, s, tm_b, P, M);
+  return launch_chain_t<64, 4, KIND>(h, s, tm_b, P, M);
+}
+
+template <int BNB, int CS>
+static cudaError_t configure_chain_t(int* max_clusters) {
+  cudaError_t e = cudaSuccess;
+  auto set = [&](auto kern) {
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
+  };
+  set(chain_kernel<BNB, CS, kChainQKV>);
+  set(chain_kernel<BNB, CS, kChainAttnOut>);
+  set(chain_kernel<BNB, CS, kChainFFN>);
+  if (e != cudaSuccess) return e;
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(CS * 64);
+  cfg.blockDim = dim3(kChThreads);
+  cfg.dynamicSmemBytes = ChSmem<BNB, CS>::bytes(chain_stages<BNB, CS>());
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = CS; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  int n = 0;
+  e = cudaOccupancyMaxActiveClusters(&n, chain_kernel<BNB, CS, kChainFFN>, &cfg);
+  *max_clusters = n;
+  return e;
+}
+
+// Units of the packed stream before the first unit of (layer l, kind): [rank][layer][in_proj | attn-out | ffn]
+template <int CS>
+static size_t chain_unit_offset(int l, int kind) {
+  using SH = ChainShape<CS>;
+  return (size_t)l * SH::UL + (kind == kChainQKV ? 0 : (kind == kChainAttnOut ? SH::UQ : SH::UQ + SH::UC));
+}
+
 // ------------------------------------------------------------------ allocation helpers
 template <typename T>
 static int dev_alloc(capdec_handle h, T** out, size_t count) {
@@ -431,6 +502,27 @@ extern "C" int capdec_destroy(capdec_handle h) {
           fprintf(stderr, "          mainloop, cycles since the pdl wait returned: activation tiles requested %lld, first tile landed %lld, all mma issued %lld, accumulator seen %lld\n",
                   r[8] - r[3], r[9] - r[3], r[10] - r[3], r[4] - r[3]);
         prev_exit = r[6];
+      }
+    }
+  }
+  if (getenv("CAPDEC_TRACE_CHAIN")) {  // tuning aid: stamps of the last projection-chain launches (layer_chain.cuh)
+    long long* dptr = nullptr;
+    unsigned n = 0;
+    cudaMemcpyFromSymbol(&dptr, g_chain_trace, sizeof dptr);
+    cudaMemcpyFromSymbol(&n, g_chain_trace_n, sizeof n);
+    if (dptr) {
+      static long long t[256 * 64];
+      cudaMemcpy(t, dptr, sizeof t, cudaMemcpyDeviceToHost);
+      const unsigned first = n > 30 ? n - 30 : 0;
+      long long prev_exit = 0;
+      for (unsigned i = first; i < n; ++i) {
+        const long long* r = t + (i & 255u) * 64;
+        fprintf(stderr, "chain#%u kind=%lld gap_ns=%lld in-kernel ns %lld | epilogue cycles since entry:", i, r[1], prev_exit ? r[0] - prev_exit : 0, r[62] - r[0]);
+        for (int j = 3; j < 40 && r[j]; ++j) fprintf(stderr, " [%d]%lld", j, r[j] - r[2]);
+        fprintf(stderr, " end %lld | mma:", r[63] - r[2]);
+        for (int j = 40; j < 52 && r[j]; ++j) fprintf(stderr, " [%d]%lld", j - 40, r[j] - r[2]);
+        fprintf(stderr, "\n");
+        prev_exit = r[62];
       }
     }
   }
@@ -498,6 +590,22 @@ static int create_impl(capdec_handle h) {
     CUDA_TRY(h, cudaMemset(h->tickets, 0, 64 * sizeof(unsigned)));
     CUDA_TRY(h, configure_fast_kernels());
   }
+  if (h->chain) {
+    const size_t units = (size_t)h->cfg.n_layer * (h->chain_cs == 8 ? ChainShape<8>::UL : ChainShape<4>::UL);
+    TRY(dev_alloc(h, &h->chain_w, (size_t)h->chain_cs * units * kChUnit));
+    const size_t Mpad = (M + 63) / 64 * 64;
+    TRY(dev_alloc(h, &h->chain_part, (size_t)h->chain_cs * Mpad * kD));
+    if (h->chain_cs == 8) {
+      CUDA_TRY(h, (configure_chain_t<32, 8>(&h->chain_clusters[0])));
+      CUDA_TRY(h, (configure_chain_t<64, 8>(&h->chain_clusters[1])));
+    } else {
+      CUDA_TRY(h, (configure_chain_t<32, 4>(&h->chain_clusters[0])));
+      CUDA_TRY(h, (configure_chain_t<64, 4>(&h->chain_clusters[1])));
+    }
+    if (getenv("CAPDEC_CHAIN_INFO"))
+      fprintf(stderr, "capdec: projection chains, %d CTAs per cluster, co-resident clusters: %d (32 rows) / %d (64 rows)\n", h->chain_cs,
+              h->chain_clusters[0], h->chain_clusters[1]);
+  }
   return 0;
 }
 
@@ -535,11 +643,22 @@ extern "C" int capdec_create(const capdec_config* cfg, int device, capdec_handle
   h->t_pad = cfg->max_len <= 64 ? 64 : 128;
   h->fast = h->use_umma && !(cfg->flags & CAPDEC_FLAG_V1_STEP);
   h->use_pdl = h->fast && !(cfg->flags & CAPDEC_FLAG_NO_PDL);
+  h->chain = h->fast && cfg->d_ff == kChFF;
+  if (const char* e = getenv("CAPDEC_CHAIN")) { if (atoi(e) == 0) h->chain = false; }
+  if (const char* e = getenv("CAPDEC_CHAIN_CS")) h->chain_cs = atoi(e) == 4 ? 4 : 8;
+  if (const char* e = getenv("CAPDEC_CHAIN_BNB")) h->force_chain_bnb = atoi(e) == 64 ? 64 : (atoi(e) == 32 ? 32 : 0);
   if (getenv("CAPDEC_TRACE_GEMM")) {
     long long* buf = nullptr;
     if (cudaMalloc(&buf, 256 * 12 * sizeof(long long)) == cudaSuccess) {
       cudaMemset(buf, 0, 256 * 12 * sizeof(long long));
       cudaMemcpyToSymbol(g_swap_trace, &buf, sizeof buf);
+    }
+  }
+  if (getenv("CAPDEC_TRACE_CHAIN")) {
+    long long* buf = nullptr;
+    if (cudaMalloc(&buf, 256 * 64 * sizeof(long long)) == cudaSuccess) {
+      cudaMemset(buf, 0, 256 * 64 * sizeof(long long));
+      cudaMemcpyToSymbol(g_chain_trace, &buf, sizeof buf);
     }
   }
   if (const char* e = getenv("CAPDEC_LN_TMA_STORE")) h->force_ln_tma_store = atoi(e) != 0 ? 1 : 0;
@@ -635,6 +754,19 @@ extern "C" int capdec_set_weights(capdec_handle h, const capdec_weights* w, void
     }
   }
   if (h->use_umma) TRY(make_weight_maps(h, &h->m_ckv, h->w_ckv, L * 2 * kD, kD));
+  if (h->chain) {
+    ChainPackSrc src{};
+    src.n_layer = L;
+    for (int l = 0; l < L; ++l) {
+      const capdec_layer_weights& lw = w->layer[l];
+      src.layer[l] = ChainPackLayer{lw.self_in_w, lw.self_out_w, lw.cross_in_w, lw.cross_out_w, lw.lin1_w, lw.lin2_w};
+    }
+    const long long total = (long long)h->chain_cs * L * (h->chain_cs == 8 ? ChainShape<8>::UL : ChainShape<4>::UL) * 1024;
+    if (h->chain_cs == 8) pack_chain_kernel<8><<<(unsigned)((total + 255) / 256), 256, 0, s>>>(src, h->chain_w);
+    else pack_chain_kernel<4><<<(unsigned)((total + 255) / 256), 256, 0, s>>>(src, h->chain_w);
+    CUDA_TRY(h, cudaGetLastError());
+    h->launches++;
+  }
   h->have_weights = true;
   return CAPDEC_OK;
 }
@@ -905,100 +1037,62 @@ static int enqueue_step_t(capdec_handle h, cudaStream_t s, int n_images, int S, 
   return 0;
 }
 
-// v2 step (bf16 + tcgen05): 8 kernels per layer instead of 11, no separate LayerNorm / vocabulary / head passes.
-static int enqueue_step_fast(capdec_handle h, cudaStream_t s, int n_images, int S, int group) {
-  const int M = n_images * group, L = h->cfg.n_layer, F = h->cfg.d_ff;
+// ---- v2 step (bf16 + tcgen05)
+static int fast_self_attn(capdec_handle h, cudaStream_t s, int l, int M) {
   const DecState* st = h->st;
-  const SwapLNParams no_ln{};
+  bf16* kc = (bf16*)h->self_k + (size_t)l * h->self_layer_elems;
+  bf16* vc = (bf16*)h->self_v + (size_t)l * h->self_layer_elems;
+  set_tag(h, "self_attn", (double)M * kD * 2 * 2 + (double)M * 2 * kD * 2 * h->prof_step_n);
+  const int blocks = (M * kH + kAttnWarps - 1) / kAttnWarps;
   cudaError_t e;
-  const double ln_extra = (double)M * kD * (4 + 4 + 2);  // residual read, x and xb written
-  for (int l = 0; l < L; ++l) {
-    LayerParams& lp = h->layer[l];
-    bf16* kc = (bf16*)h->self_k + (size_t)l * h->self_layer_elems;
-    bf16* vc = (bf16*)h->self_v + (size_t)l * h->self_layer_elems;
-    {  // self-attention block
-      SwapQKV<bf16> eq{(bf16*)h->q, kc, vc, lp.b_qkv, st, h->t_pad};
-      set_tag(h, "gemm_qkv", gemm_bytes(M, 3 * kD, kD, 2, 2, 2));
-      TRY((launch_swap<false>(h, s, lp.m_qkv, h->tx_xb, M, 3 * kD, kD, eq, no_ln, st)));
-      set_tag(h, "self_attn", (double)M * kD * 2 * 2 + (double)M * 2 * kD * 2 * h->prof_step_n);
-      {
-        const int blocks = (M * kH + kAttnWarps - 1) / kAttnWarps;
-        ProfScope ps(h, s);
-        if (h->beam_mode)
-          e = launch_ex(self_attn_stream_kernel<true>, dim3(blocks), dim3(kAttnWarps * 32), 0, s, 1, h->use_pdl, (const bf16*)h->q,
-                        (const bf16*)kc, (const bf16*)vc, (bf16*)h->a, M, h->t_pad, st, (const int*)h->beam.anc);
-        else
-          e = launch_ex(self_attn_stream_kernel<false>, dim3(blocks), dim3(kAttnWarps * 32), 0, s, 1, h->use_pdl, (const bf16*)h->q,
-                        (const bf16*)kc, (const bf16*)vc, (bf16*)h->a, M, h->t_pad, st, (const int*)nullptr);
-      }
-      CUDA_TRY(h, e);
-      h->launches_this_enqueue++;
-      SwapLNParams ln{h->x, (bf16*)h->xb, lp.b_so, lp.ln_w[0], lp.ln_b[0], h->ts_x, h->ts_xb, h->ln_tma_store};
-      set_tag(h, "gemm_self_out_ln", gemm_bytes(M, kD, kD, 2, 2, 0) + ln_extra);
-      TRY((launch_swap<true>(h, s, lp.m_so, h->tx_a, M, kD, kD, SwapNoLN{}, ln, st)));
-    }
-    {  // cross-attention block
-      SwapLinear<bf16, false> eq{(bf16*)h->q, lp.b_cq, kD};
-      set_tag(h, "gemm_cross_q", gemm_bytes(M, kD, kD, 2, 2, 2));
-      TRY((launch_swap<false>(h, s, lp.m_cq, h->tx_xb, M, kD, kD, eq, no_ln, st)));
-      set_tag(h, "cross_attn", (double)n_images * S * 2 * kD * 2 + (double)M * kD * 2 * 2);
-      {
-        const int KT = ca_key_rows(S) / 16;
-        const int per_warp = (KT + 3) / 4;
-        ProfScope ps(h, s);
-        // one query per (image, head) and a short memory: streaming warps, all resident at once (B200: cfg2 335 -> 321
-        // us/step, cfg5 592 -> 532; at S = 196 the tensor-core kernel is level, 561 vs 565)
-        if (group == 1 && S <= 128 && !h->no_cross_stream)
-          e = launch_ex(cross_attn_stream_kernel, dim3((n_images * kH + kAttnWarps - 1) / kAttnWarps), dim3(kAttnWarps * 32), 0,
-                        s, 1, h->use_pdl, (const bf16*)h->q, (const bf16*)h->cross_kv, (bf16*)h->a, l, n_images, S, st);
-        else if (per_warp <= 1)
-          e = launch_ex(cross_attn_tma_kernel<1>, dim3(n_images * kH), dim3(kCaThreads), ca_smem_bytes(S, group), s, 1, h->use_pdl,
-                        h->tm_ckv, (const bf16*)h->q, (bf16*)h->a, l, n_images, group, S, st);
-        else if (per_warp <= 2)
-          e = launch_ex(cross_attn_tma_kernel<2>, dim3(n_images * kH), dim3(kCaThreads), ca_smem_bytes(S, group), s, 1, h->use_pdl,
-                        h->tm_ckv, (const bf16*)h->q, (bf16*)h->a, l, n_images, group, S, st);
-        else
-          e = launch_ex(cross_attn_tma_kernel<4>, dim3(n_images * kH), dim3(kCaThreads), ca_smem_bytes(S, group), s, 1, h->use_pdl,
-                        h->tm_ckv, (const bf16*)h->q, (bf16*)h->a, l, n_images, group, S, st);
-      }
-      CUDA_TRY(h, e);
-      h->launches_this_enqueue++;
-      SwapLNParams ln{h->x, (bf16*)h->xb, lp.b_co, lp.ln_w[1], lp.ln_b[1], h->ts_x, h->ts_xb, h->ln_tma_store};
-      set_tag(h, "gemm_cross_out_ln", gemm_bytes(M, kD, kD, 2, 2, 0) + ln_extra);
-      TRY((launch_swap<true>(h, s, lp.m_co, h->tx_a, M, kD, kD, SwapNoLN{}, ln, st)));
-    }
-    {  // feed-forward block
-      SwapLinear<bf16, true> e1{(bf16*)h->hbuf, lp.b_1, F};
-      set_tag(h, "gemm_ffn1", gemm_bytes(M, F, kD, 2, 2, 2));
-      TRY((launch_swap<false>(h, s, lp.m_1, h->tx_xb, M, F, kD, e1, no_ln, st)));
-      const int row_tiles = (M + h->bnb - 1) / h->bnb;
-      if (M <= h->part_rows && 16 * row_tiles <= 148 && F % (4 * kSwapBK) == 0 && !h->no_ffn2_split) {
-        // small batch: K = d_ff divided over 4 CTAs per tile (fp32 partial products), closed by a separate sum_ln launch.
-        // CAPDEC_FFN2_FUSE=1: closed by the last CTA of each row tile instead (SwapPartialLN) -- one launch fewer, but
-        // measured slower on B200 (cfg2 320 vs 293 us/step): 8 CTAs x 7 warps walk 256 rows five at a time behind two
-        // fences and an atomic, where sum_ln's 256 warps take one row each inside a launch that is mostly floor.
-        if (!h->no_ffn2_fuse) {
-          SwapPartialLN ep{h->part, (long long)M * kD, h->x, (bf16*)h->xb, lp.b_2, lp.ln_w[2], lp.ln_b[2], h->tickets};
-          set_tag(h, "gemm_ffn2_sumln", gemm_bytes(M, kD, F, 2, 2, 0) + 2 * 4.0 * M * kD * 4 + (double)M * kD * (4 + 4 + 2));
-          TRY((launch_swap<false>(h, s, lp.m_2, h->tx_h, M, kD, F, ep, no_ln, st, 4)));
-          continue;
-        }
-        SwapLinear<float, false> ep{h->part, nullptr, kD, (long long)M * kD};
-        set_tag(h, "gemm_ffn2_part", gemm_bytes(M, kD, F, 2, 2, 0) + 4.0 * M * kD * 4);
-        TRY((launch_swap<false>(h, s, lp.m_2, h->tx_h, M, kD, F, ep, no_ln, st, 4)));
-        set_tag(h, "sum_ln", (double)M * kD * (4 * 4 + 4 + 4 + 2));
-        ProfScope ps(h, s);
-        e = launch_ex(sum_ln_kernel<4>, dim3((M + 3) / 4), dim3(128), 0, s, 1, h->use_pdl, h->x, (const float*)h->part,
-                      (const float*)lp.b_2, (const float*)lp.ln_w[2], (const float*)lp.ln_b[2], (bf16*)h->xb, M, st);
-        CUDA_TRY(h, e);
-        h->launches_this_enqueue++;
-      } else {
-        SwapLNParams ln{h->x, (bf16*)h->xb, lp.b_2, lp.ln_w[2], lp.ln_b[2], h->ts_x, h->ts_xb, h->ln_tma_store};
-        set_tag(h, "gemm_ffn2_ln", gemm_bytes(M, kD, F, 2, 2, 0) + ln_extra);
-        TRY((launch_swap<true>(h, s, lp.m_2, h->tx_h, M, kD, F, SwapNoLN{}, ln, st)));
-      }
-    }
+  {
+    ProfScope ps(h, s);
+    if (h->beam_mode)
+      e = launch_ex(self_attn_stream_kernel<true>, dim3(blocks), dim3(kAttnWarps * 32), 0, s, 1, h->use_pdl, (const bf16*)h->q,
+                    (const bf16*)kc, (const bf16*)vc, (bf16*)h->a, M, h->t_pad, st, (const int*)h->beam.anc);
+    else
+      e = launch_ex(self_attn_stream_kernel<false>, dim3(blocks), dim3(kAttnWarps * 32), 0, s, 1, h->use_pdl, (const bf16*)h->q,
+                    (const bf16*)kc, (const bf16*)vc, (bf16*)h->a, M, h->t_pad, st, (const int*)nullptr);
   }
+  CUDA_TRY(h, e);
+  h->launches_this_enqueue++;
+  return 0;
+}
+
+static int fast_cross_attn(capdec_handle h, cudaStream_t s, int l, int n_images, int group, int S) {
+  const DecState* st = h->st;
+  const int M = n_images * group;
+  set_tag(h, "cross_attn", (double)n_images * S * 2 * kD * 2 + (double)M * kD * 2 * 2);
+  const int KT = ca_key_rows(S) / 16;
+  const int per_warp = (KT + 3) / 4;
+  cudaError_t e;
+  {
+    ProfScope ps(h, s);
+    // one query per (image, head) and a short memory: streaming warps, all resident at once (B200: cfg2 335 -> 321
+    // us/step, cfg5 592 -> 532; at S = 196 the tensor-core kernel is level, 561 vs 565)
+    if (group == 1 && S <= 128 && !h->no_cross_stream)
+      e = launch_ex(cross_attn_stream_kernel, dim3((n_images * kH + kAttnWarps - 1) / kAttnWarps), dim3(kAttnWarps * 32), 0,
+                    s, 1, h->use_pdl, (const bf16*)h->q, (const bf16*)h->cross_kv, (bf16*)h->a, l, n_images, S, st);
+    else if (per_warp <= 1)
+      e = launch_ex(cross_attn_tma_kernel<1>, dim3(n_images * kH), dim3(kCaThreads), ca_smem_bytes(S, group), s, 1, h->use_pdl,
+                    h->tm_ckv, (const bf16*)h->q, (bf16*)h->a, l, n_images, group, S, st);
+    else if (per_warp <= 2)
+      e = launch_ex(cross_attn_tma_kernel<2>, dim3(n_images * kH), dim3(kCaThreads), ca_smem_bytes(S, group), s, 1, h->use_pdl,
+                    h->tm_ckv, (const bf16*)h->q, (bf16*)h->a, l, n_images, group, S, st);
+    else
+      e = launch_ex(cross_attn_tma_kernel<4>, dim3(n_images * kH), dim3(kCaThreads), ca_smem_bytes(S, group), s, 1, h->use_pdl,
+                    h->tm_ckv, (const bf16*)h->q, (bf16*)h->a, l, n_images, group, S, st);
+  }
+  CUDA_TRY(h, e);
+  h->launches_this_enqueue++;
+  return 0;
+}
+
+// vocabulary projection + pick + next step's embedding (plain rollouts), or logits + per-image top-k + embedding (beam search)
+static int fast_head(capdec_handle h, cudaStream_t s, int n_images, int group) {
+  const int M = n_images * group;
+  const DecState* st = h->st;
+  cudaError_t e;
   if (h->beam_mode) {
     // beam search: logits to memory (fp32, as in the v1 step), per-image top-k head, then the next step's embedding
     EpiLinear<float, false> ev{h->logits, h->fc_b, kVPad};
@@ -1042,6 +1136,120 @@ static int enqueue_step_fast(capdec_handle h, cudaStream_t s, int n_images, int 
   return 0;
 }
 
+// The step as projection chains: in_proj(0), then per layer self-attention | out_proj+LN1+cross-q | cross-attention |
+// out_proj+LN2+FFN+LN3[+in_proj of the next layer], then the head: 2 + 4 L kernels instead of 1 + 9 L.
+template <int CS>
+static int enqueue_step_chain(capdec_handle h, cudaStream_t s, int n_images, int S, int group) {
+  using SH = ChainShape<CS>;
+  const int M = n_images * group, L = h->cfg.n_layer;
+  const long long rank_stride = (long long)L * SH::UL * kChUnit;
+  auto base = [&](int l, int kind) { return (const uint8_t*)h->chain_w + chain_unit_offset<CS>(l, kind) * kChUnit; };
+  auto caches = [&](ChainParams& P, int l) {
+    P.kcache = (bf16*)h->self_k + (size_t)l * h->self_layer_elems;
+    P.vcache = (bf16*)h->self_v + (size_t)l * h->self_layer_elems;
+    P.b_qkv = h->layer[l].b_qkv;
+  };
+  ChainParams P0{};
+  P0.rank_stride = rank_stride; P0.st = h->st; P0.M = M; P0.t_pad = h->t_pad;
+  P0.x = h->x; P0.q = (bf16*)h->q; P0.part = h->chain_part;
+  {
+    ChainParams P = P0;
+    P.wstream = base(0, kChainQKV);
+    caches(P, 0);
+    set_tag(h, "chain_in_proj", gemm_bytes(M, 3 * kD, kD, 2, 2, 2));
+    TRY(launch_chain<kChainQKV>(h, s, h->tc_xb, P, M));
+  }
+  for (int l = 0; l < L; ++l) {
+    LayerParams& lp = h->layer[l];
+    TRY(fast_self_attn(h, s, l, M));
+    {
+      ChainParams P = P0;
+      P.wstream = base(l, kChainAttnOut);
+      P.b_proj = lp.b_so; P.ln_g = lp.ln_w[0]; P.ln_b = lp.ln_b[0]; P.b_cq = lp.b_cq;
+      set_tag(h, "chain_attn_out", gemm_bytes(M, kD, kD, 2, 2, 0) + gemm_bytes(M, kD, kD, 2, 0, 2) + (double)M * kD * 8);
+      TRY(launch_chain<kChainAttnOut>(h, s, h->tc_a, P, M));
+    }
+    TRY(fast_cross_attn(h, s, l, n_images, group, S));
+    {
+      ChainParams P = P0;
+      P.wstream = base(l, kChainFFN);  // the next layer's in_proj units follow in the stream
+      P.b_proj = lp.b_co; P.ln_g = lp.ln_w[1]; P.ln_b = lp.ln_b[1];
+      P.b_1 = lp.b_1; P.b_2 = lp.b_2; P.ln3_g = lp.ln_w[2]; P.ln3_b = lp.ln_b[2];
+      P.has_qkv = l + 1 < L ? 1 : 0;
+      if (P.has_qkv) caches(P, l + 1);
+      set_tag(h, "chain_ffn", gemm_bytes(M, kD, kD, 2, 2, 0) + 2.0 * kD * kChFF * 2 + (double)M * kD * 8 +
+                                  (P.has_qkv ? gemm_bytes(M, 3 * kD, kD, 2, 0, 2) : 0.0));
+      TRY(launch_chain<kChainFFN>(h, s, h->tc_a, P, M));
+    }
+  }
+  return fast_head(h, s, n_images, group);
+}
+
+// One kernel per projection (9 per layer); in use when the chains are off (CAPDEC_CHAIN=0) or d_ff != 2048.
+static int enqueue_step_fast(capdec_handle h, cudaStream_t s, int n_images, int S, int group) {
+  if (h->chain) return h->chain_cs == 8 ? enqueue_step_chain<8>(h, s, n_images, S, group) : enqueue_step_chain<4>(h, s, n_images, S, group);
+  const int M = n_images * group, L = h->cfg.n_layer, F = h->cfg.d_ff;
+  const DecState* st = h->st;
+  const SwapLNParams no_ln{};
+  cudaError_t e;
+  const double ln_extra = (double)M * kD * (4 + 4 + 2);  // residual read, x and xb written
+  for (int l = 0; l < L; ++l) {
+    LayerParams& lp = h->layer[l];
+    bf16* kc = (bf16*)h->self_k + (size_t)l * h->self_layer_elems;
+    bf16* vc = (bf16*)h->self_v + (size_t)l * h->self_layer_elems;
+    {  // self-attention block
+      SwapQKV<bf16> eq{(bf16*)h->q, kc, vc, lp.b_qkv, st, h->t_pad};
+      set_tag(h, "gemm_qkv", gemm_bytes(M, 3 * kD, kD, 2, 2, 2));
+      TRY((launch_swap<false>(h, s, lp.m_qkv, h->tx_xb, M, 3 * kD, kD, eq, no_ln, st)));
+      TRY(fast_self_attn(h, s, l, M));
+      SwapLNParams ln{h->x, (bf16*)h->xb, lp.b_so, lp.ln_w[0], lp.ln_b[0], h->ts_x, h->ts_xb, h->ln_tma_store};
+      set_tag(h, "gemm_self_out_ln", gemm_bytes(M, kD, kD, 2, 2, 0) + ln_extra);
+      TRY((launch_swap<true>(h, s, lp.m_so, h->tx_a, M, kD, kD, SwapNoLN{}, ln, st)));
+    }
+    {  // cross-attention block
+      SwapLinear<bf16, false> eq{(bf16*)h->q, lp.b_cq, kD};
+      set_tag(h, "gemm_cross_q", gemm_bytes(M, kD, kD, 2, 2, 2));
+      TRY((launch_swap<false>(h, s, lp.m_cq, h->tx_xb, M, kD, kD, eq, no_ln, st)));
+      TRY(fast_cross_attn(h, s, l, n_images, group, S));
+      SwapLNParams ln{h->x, (bf16*)h->xb, lp.b_co, lp.ln_w[1], lp.ln_b[1], h->ts_x, h->ts_xb, h->ln_tma_store};
+      set_tag(h, "gemm_cross_out_ln", gemm_bytes(M, kD, kD, 2, 2, 0) + ln_extra);
+      TRY((launch_swap<true>(h, s, lp.m_co, h->tx_a, M, kD, kD, SwapNoLN{}, ln, st)));
+    }
+    {  // feed-forward block
+      SwapLinear<bf16, true> e1{(bf16*)h->hbuf, lp.b_1, F};
+      set_tag(h, "gemm_ffn1", gemm_bytes(M, F, kD, 2, 2, 2));
+      TRY((launch_swap<false>(h, s, lp.m_1, h->tx_xb, M, F, kD, e1, no_ln, st)));
+      const int row_tiles = (M + h->bnb - 1) / h->bnb;
+      if (M <= h->part_rows && 16 * row_tiles <= 148 && F % (4 * kSwapBK) == 0 && !h->no_ffn2_split) {
+        // small batch: K = d_ff divided over 4 CTAs per tile (fp32 partial products), closed by a separate sum_ln launch.
+        // CAPDEC_FFN2_FUSE=1: closed by the last CTA of each row tile instead (SwapPartialLN) -- one launch fewer, but
+        // measured slower on B200 (cfg2 320 vs 293 us/step): 8 CTAs x 7 warps walk 256 rows five at a time behind two
+        // fences and an atomic, where sum_ln's 256 warps take one row each inside a launch that is mostly floor.
+        if (!h->no_ffn2_fuse) {
+          SwapPartialLN ep{h->part, (long long)M * kD, h->x, (bf16*)h->xb, lp.b_2, lp.ln_w[2], lp.ln_b[2], h->tickets};
+          set_tag(h, "gemm_ffn2_sumln", gemm_bytes(M, kD, F, 2, 2, 0) + 2 * 4.0 * M * kD * 4 + (double)M * kD * (4 + 4 + 2));
+          TRY((launch_swap<false>(h, s, lp.m_2, h->tx_h, M, kD, F, ep, no_ln, st, 4)));
+          continue;
+        }
+        SwapLinear<float, false> ep{h->part, nullptr, kD, (long long)M * kD};
+        set_tag(h, "gemm_ffn2_part", gemm_bytes(M, kD, F, 2, 2, 0) + 4.0 * M * kD * 4);
+        TRY((launch_swap<false>(h, s, lp.m_2, h->tx_h, M, kD, F, ep, no_ln, st, 4)));
+        set_tag(h, "sum_ln", (double)M * kD * (4 * 4 + 4 + 4 + 2));
+        ProfScope ps(h, s);
+        e = launch_ex(sum_ln_kernel<4>, dim3((M + 3) / 4), dim3(128), 0, s, 1, h->use_pdl, h->x, (const float*)h->part,
+                      (const float*)lp.b_2, (const float*)lp.ln_w[2], (const float*)lp.ln_b[2], (bf16*)h->xb, M, st);
+        CUDA_TRY(h, e);
+        h->launches_this_enqueue++;
+      } else {
+        SwapLNParams ln{h->x, (bf16*)h->xb, lp.b_2, lp.ln_w[2], lp.ln_b[2], h->ts_x, h->ts_xb, h->ln_tma_store};
+        set_tag(h, "gemm_ffn2_ln", gemm_bytes(M, kD, F, 2, 2, 0) + ln_extra);
+        TRY((launch_swap<true>(h, s, lp.m_2, h->tx_h, M, kD, F, SwapNoLN{}, ln, st)));
+      }
+    }
+  }
+  return fast_head(h, s, n_images, group);
+}
+
 static int enqueue_step(capdec_handle h, cudaStream_t s, int n_images, int S, int group) {
   h->launches_this_enqueue = 0;
   if (h->fast && !(h->beam_mode && h->beam_v1)) return enqueue_step_fast(h, s, n_images, S, group);
@@ -1068,6 +1276,12 @@ static int ensure_activation_maps(capdec_handle h, int M) {
     h->ln_tma_store = h->force_ln_tma_store >= 0 ? h->force_ln_tma_store : (h->bnb == 32 ? 1 : 0);
     TRY(make_store_map(h, &h->ts_x, h->x, M, kD, h->bnb, true));
     TRY(make_store_map(h, &h->ts_xb, h->xb, M, kD, h->bnb, false));
+    if (h->chain) {
+      // 32 rows per cluster while all clusters of a launch are co-resident, else 64 (half the weight traffic per row)
+      h->chain_bnb = h->force_chain_bnb ? h->force_chain_bnb : ((M + 31) / 32 <= std::max(1, h->chain_clusters[0]) ? 32 : 64);
+      TRY(make_map3(h, &h->tc_xb, h->xb, M, kD, h->chain_bnb, 8));
+      TRY(make_map3(h, &h->tc_a, h->a, M, kD, h->chain_bnb, 8));
+    }
   }
   h->maps_for_m = M;
   return 0;

@@ -102,6 +102,17 @@ struct capdec_engine {
   unsigned* tickets = nullptr;     // [row tiles] last-CTA election of the self-closing split-K FFN2 (SwapPartialLN)
   bool no_ffn2_fuse = true;        // env CAPDEC_FFN2_FUSE=1 clears it: the split-K FFN2 closes itself (no sum_ln launch)
 
+  // ---- cluster-resident projection chains (layer_chain.cuh): in_proj | out_proj+LN+cross-q | out_proj+LN+FFN+LN[+in_proj]
+  bool chain = false;              // in use (bf16 + tcgen05 v2 step, d_ff == 2048; env CAPDEC_CHAIN=0 turns it off)
+  int chain_cs = 8;                // CTAs per cluster (env CAPDEC_CHAIN_CS: 4 or 8)
+  int chain_bnb = 32;              // sequence rows per cluster for the current M (env CAPDEC_CHAIN_BNB)
+  int force_chain_bnb = 0;
+  int chain_max_clusters = 0;      // co-resident clusters of the FFN chain kernel (cudaOccupancyMaxActiveClusters), per BNB below
+  int chain_clusters[2] = {0, 0};  // [BNB 32, BNB 64]
+  unsigned char* chain_w = nullptr;  // [CS][L][UL][16 KB] per-CTA weight units in consumption order
+  float* chain_part = nullptr;     // [row tiles][CS][BNB][512] fp32 linear2 partial products
+  CUtensorMap tc_xb, tc_a;         // [64, M, 8] views of xb / a, box = 64 x chain_bnb x 8
+
   // ---- host-buffer entry point staging (device side)
   float* stage_mem = nullptr;
   long long* stage_ids = nullptr;

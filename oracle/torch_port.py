@@ -6,9 +6,10 @@ so this port constructs the SAME third-party modules the reference constructs, i
 order (vit:111-147: Embedding, sinusoid buffer, one nn.TransformerDecoderLayer cloned
 ``num_layers`` times by nn.TransformerDecoder, Linear, then the U(-0.1,0.1) re-init of
 vit:142-147), so that under the same ``torch.manual_seed`` it yields bit-identical
-parameters with identical state-dict keys.  ``tests/test_oracle_vs_reference.py`` checks
-both claims against the real reference whenever ``/root/reference`` is present, and
-``tests/golden`` pins them when it is not.
+parameters with identical state-dict keys.  ``tests/golden/make_golden.py`` asserts both claims
+against the real reference when it generates the fixtures (it needs ``/root/reference``), and
+``tests/test_oracle_golden.py`` re-checks them everywhere through the per-tensor checksums and
+the reference outputs stored in ``tests/golden/*.npz``.
 
 The loops below restate vit:296-325 (greedy) and scst:202-254 (sampling) in the reference's
 own no-KV-cache form: the whole prefix is re-decoded at every step.

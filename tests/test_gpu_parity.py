@@ -797,6 +797,8 @@ def test_full_size_rollout_properties(dev, name):
     rg = np.random.default_rng(5)
     for t in range(n_tiles):
         R.update(int(r) for r in rg.integers(t * 128, min(M, (t + 1) * 128), size=per_tile))
+    while len(R) < min(64, M):
+        R.add(int(rg.integers(0, M)))
     R = sorted(r for r in R if 0 <= r < M)
     assert len(R) >= min(64, M)
     with torch.no_grad():  # oracle = the torch.nn re-assembly pinned to the reference by tests/golden
