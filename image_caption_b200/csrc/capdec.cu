@@ -644,7 +644,7 @@ extern "C" int capdec_create(const capdec_config* cfg, int device, capdec_handle
   h->fast = h->use_umma && !(cfg->flags & CAPDEC_FLAG_V1_STEP);
   h->use_pdl = h->fast && !(cfg->flags & CAPDEC_FLAG_NO_PDL);
   h->chain = h->fast && cfg->d_ff == kChFF;
-  if (const char* e = getenv("CAPDEC_CHAIN")) { if (atoi(e) == 0) h->chain = false; }
+  if (const char* e = getenv("CAPDEC_CHAIN")) { if (atoi(e) == 0) h->chain = false; h->chain_always = atoi(e) == 2; }
   if (const char* e = getenv("CAPDEC_CHAIN_CS")) h->chain_cs = atoi(e) == 4 ? 4 : 8;
   if (const char* e = getenv("CAPDEC_CHAIN_BNB")) h->force_chain_bnb = atoi(e) == 64 ? 64 : (atoi(e) == 32 ? 32 : 0);
   if (getenv("CAPDEC_TRACE_GEMM")) {
@@ -1187,7 +1187,7 @@ static int enqueue_step_chain(capdec_handle h, cudaStream_t s, int n_images, int
 
 // One kernel per projection (9 per layer); in use when the chains are off (CAPDEC_CHAIN=0) or d_ff != 2048.
 static int enqueue_step_fast(capdec_handle h, cudaStream_t s, int n_images, int S, int group) {
-  if (h->chain) return h->chain_cs == 8 ? enqueue_step_chain<8>(h, s, n_images, S, group) : enqueue_step_chain<4>(h, s, n_images, S, group);
+  if (h->chain_now) return h->chain_cs == 8 ? enqueue_step_chain<8>(h, s, n_images, S, group) : enqueue_step_chain<4>(h, s, n_images, S, group);
   const int M = n_images * group, L = h->cfg.n_layer, F = h->cfg.d_ff;
   const DecState* st = h->st;
   const SwapLNParams no_ln{};
@@ -1276,7 +1276,13 @@ static int ensure_activation_maps(capdec_handle h, int M) {
     h->ln_tma_store = h->force_ln_tma_store >= 0 ? h->force_ln_tma_store : (h->bnb == 32 ? 1 : 0);
     TRY(make_store_map(h, &h->ts_x, h->x, M, kD, h->bnb, true));
     TRY(make_store_map(h, &h->ts_xb, h->xb, M, kD, h->bnb, false));
-    if (h->chain) {
+    // Measured on B200 (tools/chain_ab.sh, same box): the chains win only while every cluster of a launch is
+    // co-resident (8 CTAs x <= 15 clusters): cfg2 (256 rows) 269.6 -> 266.3 us/step.  Beyond that each CTA still streams
+    // its whole 768 KB weight share per 32-row tile through one TMA ring (~60 B/clk) and the row tiles queue up:
+    // cfg5 (1024 rows) 489 -> 505 us/step with 4-CTA clusters, cfg3 (3072 rows) 860 -> 1290.  So larger batches keep one
+    // kernel per projection; CAPDEC_CHAIN=2 forces the chains for any batch (tests, A/B), CAPDEC_CHAIN=0 turns them off.
+    h->chain_now = h->chain && (h->chain_always || (M + 31) / 32 <= h->chain_clusters[0]);
+    if (h->chain_now) {
       // 32 rows per cluster while all clusters of a launch are co-resident, else 64 (half the weight traffic per row)
       h->chain_bnb = h->force_chain_bnb ? h->force_chain_bnb : ((M + 31) / 32 <= std::max(1, h->chain_clusters[0]) ? 32 : 64);
       TRY(make_map3(h, &h->tc_xb, h->xb, M, kD, h->chain_bnb, 8));

@@ -104,6 +104,8 @@ struct capdec_engine {
 
   // ---- cluster-resident projection chains (layer_chain.cuh): in_proj | out_proj+LN+cross-q | out_proj+LN+FFN+LN[+in_proj]
   bool chain = false;              // in use (bf16 + tcgen05 v2 step, d_ff == 2048; env CAPDEC_CHAIN=0 turns it off)
+  bool chain_now = false;          // chains used for the current batch size (all clusters co-resident, or forced)
+  bool chain_always = false;       // env CAPDEC_CHAIN=2
   int chain_cs = 8;                // CTAs per cluster (env CAPDEC_CHAIN_CS: 4 or 8)
   int chain_bnb = 32;              // sequence rows per cluster for the current M (env CAPDEC_CHAIN_BNB)
   int force_chain_bnb = 0;

@@ -275,6 +275,7 @@ def test_v2_step_tile_widths(dev, monkeypatch, bnb, mem_len, group, n_sample):
     """swap-AB GEMMs at every sequences-per-CTA width (ragged last tile), TMA cross-attention at both
     memory lengths, fused LayerNorm epilogue (cluster of 4) and fused vocabulary head."""
     monkeypatch.setenv("CAPDEC_BNB", str(bnb))
+    monkeypatch.setenv("CAPDEC_CHAIN", "0")  # this test targets the one-kernel-per-projection step
     dec = small_decoder(layers=2, end_bias=1.0)
     w = torch_port.weights_to_numpy(dec)
     n_img = 150 // group
@@ -286,11 +287,37 @@ def test_v2_step_tile_widths(dev, monkeypatch, bnb, mem_len, group, n_sample):
     eng.close()
 
 
+@pytest.mark.parametrize("cs,bnb", [(8, 32), (8, 64), (4, 32), (4, 64)])
+@pytest.mark.parametrize("mem_len,group,n_sample", [(196, 6, 5), (49, 1, 0)])
+def test_v2_projection_chains(dev, monkeypatch, cs, bnb, mem_len, group, n_sample):
+    """The cluster-resident projection chains (layer_chain.cuh: in_proj | out_proj+LN1+cross-q | out_proj+LN2+FFN+LN3
+    [+ next in_proj]) forced on (CAPDEC_CHAIN=2) at both cluster sizes and both row-tile widths, several row tiles with
+    a ragged last one, against the oracle; and the same rollout with the chains off (one kernel per projection)."""
+    monkeypatch.setenv("CAPDEC_CHAIN_CS", str(cs))
+    monkeypatch.setenv("CAPDEC_CHAIN_BNB", str(bnb))
+    dec = small_decoder(layers=3, end_bias=1.0)
+    w = torch_port.weights_to_numpy(dec)
+    n_img = 150 // group
+    mem = torch_port.synthetic_memory(n_img, mem_len)
+    outs = []
+    for chain in ("2", "0"):
+        monkeypatch.setenv("CAPDEC_CHAIN", chain)
+        eng = make_engine(dec.to(dev), "bf16", step_impl="v2", max_images=n_img, max_group=group, max_mem=mem_len, max_len=10)
+        out = eng.decode_from_memory(mem.to(dev), START, END, max_len=10, group=group, n_sample=n_sample, seed=13,
+                                     return_logits=True, early_stop=False, trim=False)
+        check_rollout(out, w, mem.numpy(), group, n_sample, TOL["bf16"], seed=13)
+        outs.append((out.logits.cpu(), eng.launch_count()))
+        eng.close()
+    assert (outs[0][0][:, 0] - outs[1][0][:, 0]).abs().max() < 2e-2  # same roundings, different summation order
+    assert outs[0][1] < outs[1][1]  # 2 + 4 L kernels per step instead of 1 + 9 L
+
+
 @pytest.mark.parametrize("ksplit", [1, 2, 4])
 def test_v2_layernorm_gemm_split_k(dev, monkeypatch, ksplit):
     """LayerNorm GEMMs with K divided over 1/2/4 CTAs per feature tile (clusters of 4/8/16 CTAs, partial
     accumulators added through distributed shared memory)."""
     monkeypatch.setenv("CAPDEC_KSPLIT", str(ksplit))
+    monkeypatch.setenv("CAPDEC_CHAIN", "0")  # this test targets the one-kernel-per-projection step
     monkeypatch.setenv("CAPDEC_NO_FFN2_SPLIT", "1")  # FFN2 through the LayerNorm GEMM too (large-batch route)
     dec = small_decoder(layers=2, end_bias=1.0)
     w = torch_port.weights_to_numpy(dec)
@@ -325,6 +352,7 @@ def test_v2_ffn2_split_k_closes_itself(dev, monkeypatch, n_img):
     """Small batches run FFN2 as 4 k-slices whose last CTA per row tile (ticket counter) sums the slices and applies
     residual + LayerNorm (SwapPartialLN) when CAPDEC_FFN2_FUSE=1; the default is the separate sum_ln launch.  Same arithmetic
     (sum_ln_row) on the same partial products: identical results, ragged last row tile included."""
+    monkeypatch.setenv("CAPDEC_CHAIN", "0")  # this test targets the one-kernel-per-projection step
     dec = small_decoder(layers=2, end_bias=1.0)
     w = torch_port.weights_to_numpy(dec)
     mem = torch_port.synthetic_memory(n_img, 49)
