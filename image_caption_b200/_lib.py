@@ -20,7 +20,7 @@ EXPORTS = (
     "capdec_abi_version", "capdec_last_error", "capdec_create", "capdec_destroy", "capdec_set_weights",
     "capdec_prefill", "capdec_decode", "capdec_generate_host", "capdec_sample_logits", "capdec_launch_count",
     "capdec_debug_gemm", "capdec_debug_cross_kv", "capdec_profile_enable", "capdec_profile_report",
-    "capdec_beam_search", "capdec_set_memory_projection", "capdec_prefill_tokens",
+    "capdec_beam_search", "capdec_set_memory_projection", "capdec_prefill_tokens", "capdec_gemm_static",
 )
 
 
@@ -102,6 +102,9 @@ def load() -> C.CDLL:
     lib.capdec_launch_count.argtypes = [H]
     lib.capdec_debug_gemm.argtypes = [H, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32,
                                       C.c_int32, C.c_int32, C.c_void_p]
+    if hasattr(lib, "capdec_gemm_static"):
+        lib.capdec_gemm_static.argtypes = [H, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32,
+                                           C.c_int32, C.c_int32, C.c_void_p]
     lib.capdec_debug_cross_kv.argtypes = [H, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]
     lib.capdec_profile_enable.argtypes = [H, C.c_int32]
     lib.capdec_profile_report.argtypes = [H, C.c_char_p, C.c_int32]

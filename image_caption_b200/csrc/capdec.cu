@@ -1667,3 +1667,71 @@ extern "C" int capdec_debug_cross_kv(capdec_handle h, int32_t layer, int32_t whi
   h->launches++;
   return CAPDEC_OK;
 }
+
+// ------------------------------------------------------------------ allocation-free projection (capdec_gemm_static)
+// capdec_debug_gemm converts its fp32 operands to bf16 in scratch buffers it cudaMalloc's and frees per call.  Callers
+// that may not allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid it) get the same
+// kernels with that scratch in a file-scope device array: 4 MiB, held by every GPU that loads the library until exit.
+// In host code `g_static_scratch` is only a stand-in for the symbol, not a device address: the address is looked up once
+// per device with cudaGetSymbolAddress (that device current) and handed to the kernels.
+constexpr size_t kStaticScratchElems = (size_t)2 << 20;  // bf16 elements: operand rows of A plus rows of W, 4 MiB in all
+static __device__ __align__(256) unsigned short g_static_scratch[kStaticScratchElems];
+
+static int static_scratch_address(capdec_handle h, bf16** out) {
+  static std::mutex mu;
+  static void* addr[64] = {};
+  if (h->device < 0 || h->device >= 64) return fail(h, CAPDEC_ERR_INVALID, "device index %d outside the scratch table", h->device);
+  std::lock_guard<std::mutex> lock(mu);
+  if (!addr[h->device]) {
+    void* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch);  // caller has made h->device current
+    if (e != cudaSuccess || !p)
+      return fail(h, CAPDEC_ERR_CUDA, "cudaGetSymbolAddress(g_static_scratch) failed on device %d: %s", h->device, cudaGetErrorString(e));
+    addr[h->device] = p;
+  }
+  *out = static_cast<bf16*>(addr[h->device]);
+  return 0;
+}
+
+extern "C" int capdec_gemm_static(capdec_handle h, const float* a, const float* w, const float* bias, float* c, int32_t m,
+                                  int32_t n, int32_t k, int32_t relu, void* stream) {
+  if (!h || !a || !w || !c || m < 1 || n < 1 || k < 1) return fail(h, CAPDEC_ERR_INVALID, "bad argument");
+  if (h->profiling) return fail(h, CAPDEC_ERR_STATE, "capdec_gemm_static while per-launch profiling is on (the event pairs are allocations)");
+  const size_t a_elems = ((size_t)m * k + 127) / 128 * 128, w_elems = (size_t)n * k;
+  if (h->bf16 && a_elems + w_elems > kStaticScratchElems)
+    return fail(h, CAPDEC_ERR_CAPACITY, "capdec_gemm_static: (m + n) * k = %zu operand elements exceed the static scratch of %zu (4 MiB); "
+                "use capdec_debug_gemm or a smaller tile", (size_t)m * k + w_elems, kStaticScratchElems);
+  cudaStream_t s = (cudaStream_t)stream;
+  CUDA_TRY(h, cudaSetDevice(h->device));
+  h->launches_this_enqueue = 0;
+  int rc = 0;
+  if (!h->bf16) {  // fp32 engine: the CUDA-core GEMM reads the operands in place, no scratch at all
+    if (relu) { EpiLinear<float, true> e{c, bias, n}; rc = launch_simt<float, float, EpiLinear<float, true>>(h, s, a, k, w, k, m, n, k, e, nullptr); }
+    else { EpiLinear<float, false> e{c, bias, n}; rc = launch_simt<float, float, EpiLinear<float, false>>(h, s, a, k, w, k, m, n, k, e, nullptr); }
+    h->launches += h->launches_this_enqueue;
+    return rc;
+  }
+  bf16* scratch = nullptr;
+  TRY(static_scratch_address(h, &scratch));
+  bf16 *ab = scratch, *wb = scratch + a_elems;
+  // every element the GEMM reads is written here first (rows beyond m / n are filled by the TMA unit, not read from
+  // memory), so nothing of an earlier call's contents can reach the result and nothing needs clearing
+  pack_rows_kernel<bf16><<<(unsigned)(((size_t)m * k + 255) / 256), 256, 0, s>>>(a, ab, m, k, m);
+  pack_rows_kernel<bf16><<<(unsigned)((w_elems + 255) / 256), 256, 0, s>>>(w, wb, n, k, n);
+  CUDA_TRY(h, cudaGetLastError());
+  if (h->use_umma) {
+    CUtensorMap ta;
+    WeightMaps wm;  // (tensor maps are encoded on the host: no device memory involved)
+    rc = make_map(h, &ta, ab, m, k, kUmmaBM);
+    if (!rc) rc = make_weight_maps(h, &wm, wb, n, k);
+    if (!rc) {
+      if (relu) { EpiLinear<float, true> e{c, bias, n}; rc = launch_umma(h, s, ta, wm, m, n, k, e, nullptr); }
+      else { EpiLinear<float, false> e{c, bias, n}; rc = launch_umma(h, s, ta, wm, m, n, k, e, nullptr); }
+    }
+  } else {
+    if (relu) { EpiLinear<float, true> e{c, bias, n}; rc = launch_simt<bf16, bf16, EpiLinear<float, true>>(h, s, ab, k, wb, k, m, n, k, e, nullptr); }
+    else { EpiLinear<float, false> e{c, bias, n}; rc = launch_simt<bf16, bf16, EpiLinear<float, false>>(h, s, ab, k, wb, k, m, n, k, e, nullptr); }
+  }
+  h->launches += h->launches_this_enqueue + 2;
+  return rc;
+}

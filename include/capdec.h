@@ -220,6 +220,22 @@ int capdec_debug_gemm(capdec_handle h, const float* a, const float* w, const flo
  * [n_images, mem_len, D] (the reference's memory @ W^T + b layout). */
 int capdec_debug_cross_kv(capdec_handle h, int32_t layer, int32_t which, float* out, void* cuda_stream);
 
+/* Allocation-free projection: C[m,n] = act(A[m,k] W[n,k]^T + bias), fp32 DEVICE pointers, the computation of
+ * capdec_debug_gemm (same kernels, same rounding: bf16 operands / fp32 accumulate on a bf16 engine) with the bf16 operand
+ * scratch in a file-scope device array instead of cudaMalloc'd buffers.  It has NO counterpart in the reference: it was
+ * added for callers that cannot call cudaMalloc (CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  It calls no cudaMalloc / cudaFree / allocating library routine and does not
+ * synchronise: the work is enqueued on `cuda_stream`.
+ *   limit   bf16 engine: (m rounded so that m*k is a multiple of 128) * k + n * k <= 2 Mi elements (4 MiB of scratch, held
+ *           by every GPU that loads the library until exit); beyond it CAPDEC_ERR_CAPACITY.  Shapes as capdec_debug_gemm:
+ *           k % 64 == 0 and n % 128 == 0 on the tensor-core route.  fp32 engine: no scratch, no limit.
+ *   sharing every call on a device uses the SAME array, which keeps the previous call's contents; each call overwrites
+ *           all it reads, so nothing needs clearing -- but two calls that overlap on the GPU (different streams, or a
+ *           graph replayed concurrently) RACE on it.  Serialise them on one stream.
+ *   state   CAPDEC_ERR_STATE while capdec_profile_enable(h, 1) is in effect (its event pairs are allocations). */
+int capdec_gemm_static(capdec_handle h, const float* a, const float* w, const float* bias, float* c, int32_t m, int32_t n,
+                       int32_t k, int32_t relu, void* cuda_stream);
+
 #ifdef __cplusplus
 }
 #endif
