@@ -79,7 +79,11 @@ def workload_config(name: str, world: int, precision: str, images_override: int 
     return {"workload": f"{name}: {desc}", "images_global": n_global, "images_per_gpu": n_global // world, "mem_len": S,
             "group": G, "n_sample": ns, "max_len": max_len, "sequences_global": n_global * G, "decode_steps": max_len - 1,
             "n_gpus": world, "scaling": scaling, "weights": "random init, torch.manual_seed(0)",
-            "memory": "randn(images, S, 512), torch.Generator().manual_seed(1234)"}
+            "memory": "randn(images, S, 512), torch.Generator().manual_seed(1234)",
+            # (the same object in the product arm and in the reference arm: statements about the GPU arm say so)
+            "l2": "GPU arm: flushed between timed steps (512 MiB memset outside the event pairs)",
+            "collective": ("GPU arm: all-gather ids+logp (NCCL), trimmed to the reference's global width" if world > 1 else "none"),
+            "engine": "GPU arm: v2 step kernels (projection chains at <= 480 rows), 7 decode steps per CUDA graph, programmatic dependent launch"}
 
 
 def algorithmic_bytes(n_img: int, S: int, G: int, max_len: int, e: int) -> dict:
@@ -339,9 +343,6 @@ def measure(name: str, precision: str, steps: int, warmup: int, world: int, rank
                    if world == 1 else "per rank: H2D of the shard, decode, all-gather on the device, one D2H of the gathered result"}
 
     cfg = workload_config(name, world, precision, images_override)
-    cfg.update({"l2": "flushed between timed steps (512 MiB memset outside the event pairs)",
-                "collective": "all-gather ids+logp (NCCL), trimmed to the reference's global width" if world > 1 else "none",
-                "engine": os.environ.get("CAPDEC_ENGINE_NOTE", "v2 step kernels, 7 decode steps per CUDA graph, programmatic dependent launch")})
     rec = {"metric": "captions/s", "value": value, "unit": "captions/s", "n_gpus": world, "steps": steps,
            "warmup": warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": scaling,
            "vs_baseline": None, "dtype": precision, "data": "synthetic", "config": cfg,

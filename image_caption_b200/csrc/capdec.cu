@@ -13,6 +13,7 @@
 #include "gemm_simt.cuh"
 #include "gemm_umma.cuh"
 #include "gemm_swap.cuh"
+#include "gemm_ws.cuh"
 #include "beam.cuh"
 #include "cross_attn_tma.cuh"
 #include "attention.cuh"
@@ -136,6 +137,7 @@ static int make_map3(capdec_handle h, CUtensorMap* m, const void* ptr, int rows,
 }
 
 static int make_weight_maps(capdec_handle h, WeightMaps* wm, const void* ptr, int n, int k) {
+  wm->raw = ptr; wm->rows = n; wm->k = k;
   const int bns[3] = {32, 64, 128};
   for (int i = 0; i < 3; ++i) {
     int rc = make_map(h, &wm->bn[i], ptr, n, k, bns[i]);
@@ -327,6 +329,41 @@ static int launch_swap_bnb(capdec_handle h, cudaStream_t s, const WeightMaps& tw
   return 0;
 }
 
+// Large batches, K = 512, no LayerNorm: persistent weight-stationary GEMM (gemm_ws.cuh), one wave of CTAs.
+template <typename Epi>
+static int launch_ws(capdec_handle h, cudaStream_t s, const WeightMaps& tw, const ActMaps& tx, int M, int n_out, const Epi& epi,
+                     const DecState* st) {
+  constexpr int BNB = 128;
+  const int f_tiles = n_out / kSwapBF, n_tiles = (M + BNB - 1) / BNB;
+  const int groups = std::max(1, std::min(n_tiles, 148 / f_tiles));
+  ProfScope ps(h, s);
+  cudaError_t e = launch_ex(gemm_ws_kernel<BNB, Epi>, dim3(f_tiles, groups), dim3(kWsThreads), ws_smem_bytes(BNB), s, 1, h->use_pdl,
+                            tw.bn[2], tx.tile, M, epi, st, h->ws_dbg);
+  if (e != cudaSuccess) return fail(h, CAPDEC_ERR_CUDA, "gemm_ws launch failed: %s (n_out=%d M=%d)", cudaGetErrorString(e), n_out, M);
+  h->launches_this_enqueue++;
+  return 0;
+}
+template <typename Epi>
+static cudaError_t configure_ws_epi() {
+  return cudaFuncSetAttribute(gemm_ws_kernel<128, Epi>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
+}
+static bool use_ws(capdec_handle h, int n_out) { return h->bnb == 128 && !h->no_ws && n_out / kSwapBF <= 148 && h->cfg.d_model == kWsK; }
+
+// bf16 [rows][H][t_pad][64] self K/V cache of one layer as a 4-D tensor for the in_proj epilogue's bulk store:
+// box = {64, 1 position, 2 heads, 128 rows} (shared-memory image: [128 rows][128 features] bf16)
+static int make_cache_store_map(capdec_handle h, CUtensorMap* m, const void* ptr, size_t rows, int t_pad) {
+  EncodeTiledFn fn = encode_tiled_fn();
+  if (!fn) return fail(h, CAPDEC_ERR_CUDA, "cuTensorMapEncodeTiled entry point unavailable");
+  cuuint64_t dims[4] = {(cuuint64_t)kHD, (cuuint64_t)t_pad, (cuuint64_t)kH, (cuuint64_t)rows};
+  cuuint64_t strides[3] = {(cuuint64_t)kHD * 2, (cuuint64_t)t_pad * kHD * 2, (cuuint64_t)kH * t_pad * kHD * 2};
+  cuuint32_t box[4] = {(cuuint32_t)kHD, 1, 2, 128};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(h, CAPDEC_ERR_CUDA, "cuTensorMapEncodeTiled (cache store view) failed (%d)", (int)r);
+  return 0;
+}
+
 template <bool kLN, typename Epi>
 static int launch_swap(capdec_handle h, cudaStream_t s, const WeightMaps& tw, const ActMaps& tx, int M, int n_out, int K,
                        const Epi& epi, const SwapLNParams& ln, const DecState* st, int zsplit = 1) {
@@ -361,6 +398,9 @@ static cudaError_t configure_fast_kernels() {
   if (e == cudaSuccess) e = configure_swap_epi<false, SwapQKV<bf16>>();
   if (e == cudaSuccess) e = configure_swap_epi<false, SwapPartialLN>();
   if (e == cudaSuccess) e = configure_swap_epi<true, SwapNoLN>();
+  if (e == cudaSuccess) e = configure_ws_epi<WsLinear<false>>();
+  if (e == cudaSuccess) e = configure_ws_epi<WsLinear<true>>();
+  if (e == cudaSuccess) e = configure_ws_epi<WsQKV>();
   if (e == cudaSuccess) e = configure_swap_ln_ks<32, 2>();
   if (e == cudaSuccess) e = configure_swap_ln_ks<64, 2>();
   if (e == cudaSuccess) e = configure_swap_ln_ks<128, 2>();
@@ -567,6 +607,11 @@ static int create_impl(capdec_handle h) {
   TRY(dev_alloc_bytes(h, &h->self_v, (size_t)L * h->self_layer_elems * es));
   TRY(dev_alloc_bytes(h, &h->cross_kv, (size_t)L * 2 * c.max_images * c.max_mem * kD * es));
 
+  if (h->fast)
+    for (int l = 0; l < L; ++l) {
+      TRY(make_cache_store_map(h, &lp[l].ts_k, (char*)h->self_k + (size_t)l * h->self_layer_elems * es, M, h->t_pad));
+      TRY(make_cache_store_map(h, &lp[l].ts_v, (char*)h->self_v + (size_t)l * h->self_layer_elems * es, M, h->t_pad));
+    }
   TRY(dev_alloc(h, &h->x, M * kD));
   TRY(dev_alloc(h, &h->t, M * kD));
   TRY(dev_alloc(h, &h->logits, M * kVPad));
@@ -663,6 +708,8 @@ extern "C" int capdec_create(const capdec_config* cfg, int device, capdec_handle
   }
   if (const char* e = getenv("CAPDEC_LN_TMA_STORE")) h->force_ln_tma_store = atoi(e) != 0 ? 1 : 0;
   if (const char* e = getenv("CAPDEC_NO_CROSS_STREAM")) h->no_cross_stream = atoi(e) != 0;
+  if (const char* e = getenv("CAPDEC_NO_WS")) h->no_ws = atoi(e) != 0;
+  if (const char* e = getenv("CAPDEC_WS_DBG")) h->ws_dbg = atoi(e);  // tuning aid: 1 = skip the output stores, 2 = skip the weight load (wrong results)
   if (const char* e = getenv("CAPDEC_NO_WHOLE_K")) h->no_whole_k = atoi(e) != 0;
   if (const char* e = getenv("CAPDEC_FFN2_FUSE")) h->no_ffn2_fuse = atoi(e) == 0;
   if (const char* e = getenv("CAPDEC_HEAD_RW")) { const int v = atoi(e); h->force_head_rw = (v == 1 || v == 2 || v == 4 || v == 6) ? v : 0; }
@@ -1200,7 +1247,8 @@ static int enqueue_step_fast(capdec_handle h, cudaStream_t s, int n_images, int 
     {  // self-attention block
       SwapQKV<bf16> eq{(bf16*)h->q, kc, vc, lp.b_qkv, st, h->t_pad};
       set_tag(h, "gemm_qkv", gemm_bytes(M, 3 * kD, kD, 2, 2, 2));
-      TRY((launch_swap<false>(h, s, lp.m_qkv, h->tx_xb, M, 3 * kD, kD, eq, no_ln, st)));
+      if (use_ws(h, 3 * kD)) TRY(launch_ws(h, s, lp.m_qkv, h->tx_xb, M, 3 * kD, WsQKV{h->ts_q, lp.ts_k, lp.ts_v, lp.b_qkv, st}, st));
+      else TRY((launch_swap<false>(h, s, lp.m_qkv, h->tx_xb, M, 3 * kD, kD, eq, no_ln, st)));
       TRY(fast_self_attn(h, s, l, M));
       SwapLNParams ln{h->x, (bf16*)h->xb, lp.b_so, lp.ln_w[0], lp.ln_b[0], h->ts_x, h->ts_xb, h->ln_tma_store};
       set_tag(h, "gemm_self_out_ln", gemm_bytes(M, kD, kD, 2, 2, 0) + ln_extra);
@@ -1209,7 +1257,8 @@ static int enqueue_step_fast(capdec_handle h, cudaStream_t s, int n_images, int 
     {  // cross-attention block
       SwapLinear<bf16, false> eq{(bf16*)h->q, lp.b_cq, kD};
       set_tag(h, "gemm_cross_q", gemm_bytes(M, kD, kD, 2, 2, 2));
-      TRY((launch_swap<false>(h, s, lp.m_cq, h->tx_xb, M, kD, kD, eq, no_ln, st)));
+      if (use_ws(h, kD)) TRY(launch_ws(h, s, lp.m_cq, h->tx_xb, M, kD, WsLinear<false>{h->ts_q, lp.b_cq}, st));
+      else TRY((launch_swap<false>(h, s, lp.m_cq, h->tx_xb, M, kD, kD, eq, no_ln, st)));
       TRY(fast_cross_attn(h, s, l, n_images, group, S));
       SwapLNParams ln{h->x, (bf16*)h->xb, lp.b_co, lp.ln_w[1], lp.ln_b[1], h->ts_x, h->ts_xb, h->ln_tma_store};
       set_tag(h, "gemm_cross_out_ln", gemm_bytes(M, kD, kD, 2, 2, 0) + ln_extra);
@@ -1218,7 +1267,8 @@ static int enqueue_step_fast(capdec_handle h, cudaStream_t s, int n_images, int 
     {  // feed-forward block
       SwapLinear<bf16, true> e1{(bf16*)h->hbuf, lp.b_1, F};
       set_tag(h, "gemm_ffn1", gemm_bytes(M, F, kD, 2, 2, 2));
-      TRY((launch_swap<false>(h, s, lp.m_1, h->tx_xb, M, F, kD, e1, no_ln, st)));
+      if (use_ws(h, F)) TRY(launch_ws(h, s, lp.m_1, h->tx_xb, M, F, WsLinear<true>{h->ts_h, lp.b_1}, st));
+      else TRY((launch_swap<false>(h, s, lp.m_1, h->tx_xb, M, F, kD, e1, no_ln, st)));
       const int row_tiles = (M + h->bnb - 1) / h->bnb;
       if (M <= h->part_rows && 16 * row_tiles <= 148 && F % (4 * kSwapBK) == 0 && !h->no_ffn2_split) {
         // small batch: K = d_ff divided over 4 CTAs per tile (fp32 partial products), closed by a separate sum_ln launch.
@@ -1276,6 +1326,10 @@ static int ensure_activation_maps(capdec_handle h, int M) {
     h->ln_tma_store = h->force_ln_tma_store >= 0 ? h->force_ln_tma_store : (h->bnb == 32 ? 1 : 0);
     TRY(make_store_map(h, &h->ts_x, h->x, M, kD, h->bnb, true));
     TRY(make_store_map(h, &h->ts_xb, h->xb, M, kD, h->bnb, false));
+    if (h->bnb == 128) {  // output views of the weight-stationary GEMM's bulk stores
+      TRY(make_store_map(h, &h->ts_q, h->q, M, kD, 128, false));
+      TRY(make_store_map(h, &h->ts_h, h->hbuf, M, h->cfg.d_ff, 128, false));
+    }
     // Measured on B200 (tools/chain_ab.sh, same box): the chains win only while every cluster of a launch is
     // co-resident (8 CTAs x <= 15 clusters): cfg2 (256 rows) 269.6 -> 266.3 us/step.  Beyond that each CTA still streams
     // its whole 768 KB weight share per 32-row tile through one TMA ring (~60 B/clk) and the row tiles queue up:

@@ -17,6 +17,8 @@ constexpr int kHostCopyChunks = 8;  // capdec_generate_host: image chunks of the
 // W operand tensor maps for the three N-tile widths the tcgen05 GEMM is instantiated for.
 struct WeightMaps {
   CUtensorMap bn[3];  // 32, 64, 128
+  const void* raw = nullptr;  // the packed matrix itself ([rows, K] row-major, engine element type)
+  int rows = 0, k = 0;
   CUtensorMap w3;     // [64, rows, K/64] view, box = 64 x 128 rows x 4 k-blocks: half of a K = 512 weight slice per copy
 };
 // TMA views of one activation matrix for the v2 GEMMs
@@ -31,6 +33,7 @@ struct LayerParams {
   float *b_qkv, *b_so, *b_cq, *b_co, *b_1, *b_2;
   float *ln_w[3], *ln_b[3];
   WeightMaps m_qkv, m_so, m_cq, m_co, m_1, m_2;
+  CUtensorMap ts_k, ts_v;  // this layer's self K / V cache as a 4-D store view (gemm_ws.cuh, in_proj epilogue)
 };
 
 struct StepGraph {
@@ -89,10 +92,13 @@ struct capdec_engine {
   int force_bnb = 0, force_stages = 0, force_ksplit = 0;
   bool no_ffn2_split = false;  // tuning overrides (env CAPDEC_BNB / CAPDEC_STAGES)
   capdec::ActMaps tx_xb, tx_a, tx_h;  // activation maps with box rows = bnb
+  CUtensorMap ts_q, ts_h;          // bf16 store views of q [M,512] and the FFN hidden [M,d_ff], box = 128 x 128 (gemm_ws.cuh)
   CUtensorMap ts_x, ts_xb;         // store views of the residual stream (fp32 / bf16), box = 128 x bnb
   int ln_tma_store = 1;            // LayerNorm epilogue leaves through bulk tensor stores
   int force_ln_tma_store = -1;     // env CAPDEC_LN_TMA_STORE
   int force_head_rw = 0;           // env CAPDEC_HEAD_RW: rows per warp of the vocabulary head (1, 2, 4, 6)
+  int ws_dbg = 0;
+  bool no_ws = false;              // env CAPDEC_NO_WS: never use the weight-stationary persistent GEMM (gemm_ws.cuh)
   bool no_whole_k = false;         // env CAPDEC_NO_WHOLE_K: one TMA copy per k-block instead of whole-K copies
   bool no_cross_stream = false;    // env CAPDEC_NO_CROSS_STREAM: keep the tensor-core cross-attention for group == 1
   CUtensorMap tm_ckv;              // whole cross cache as [rows,64], box = 64 x ca_key_rows(S)
