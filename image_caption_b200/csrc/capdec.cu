@@ -331,14 +331,14 @@ static int launch_swap_bnb(capdec_handle h, cudaStream_t s, const WeightMaps& tw
 
 // Large batches, K = 512, no LayerNorm: persistent weight-stationary GEMM (gemm_ws.cuh), one wave of CTAs.
 template <typename Epi>
-static int launch_ws(capdec_handle h, cudaStream_t s, const WeightMaps& tw, const ActMaps& tx, int M, int n_out, const Epi& epi,
+static int launch_ws(capdec_handle h, cudaStream_t s, const WeightMaps& tw, const CUtensorMap& tx, int M, int n_out, const Epi& epi,
                      const DecState* st) {
   constexpr int BNB = 128;
   const int f_tiles = n_out / kSwapBF, n_tiles = (M + BNB - 1) / BNB;
   const int groups = std::max(1, std::min(n_tiles, 148 / f_tiles));
   ProfScope ps(h, s);
   cudaError_t e = launch_ex(gemm_ws_kernel<BNB, Epi>, dim3(f_tiles, groups), dim3(kWsThreads), ws_smem_bytes(BNB), s, 1, h->use_pdl,
-                            tw.bn[2], tx.tile, M, epi, st, h->ws_dbg);
+                            tw.bn[2], tx, M, epi, st, h->ws_dbg);
   if (e != cudaSuccess) return fail(h, CAPDEC_ERR_CUDA, "gemm_ws launch failed: %s (n_out=%d M=%d)", cudaGetErrorString(e), n_out, M);
   h->launches_this_enqueue++;
   return 0;
@@ -347,7 +347,12 @@ template <typename Epi>
 static cudaError_t configure_ws_epi() {
   return cudaFuncSetAttribute(gemm_ws_kernel<128, Epi>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
 }
-static bool use_ws(capdec_handle h, int n_out) { return h->bnb == 128 && !h->no_ws && n_out / kSwapBF <= 148 && h->cfg.d_model == kWsK; }
+// In use when the batch gives a full wave of CTAs: (feature tiles) x (row groups) >= 96
+static bool use_ws(capdec_handle h, int n_out, int M) {
+  const int f_tiles = n_out / kSwapBF, n_tiles = (M + 127) / 128;
+  if (h->no_ws || M < h->ws_min_m || f_tiles > 148) return false;
+  return f_tiles * std::min(n_tiles, 148 / f_tiles) >= 96;
+}
 
 // bf16 [rows][H][t_pad][64] self K/V cache of one layer as a 4-D tensor for the in_proj epilogue's bulk store:
 // box = {64, 1 position, 2 heads, 128 rows} (shared-memory image: [128 rows][128 features] bf16)
@@ -709,6 +714,7 @@ extern "C" int capdec_create(const capdec_config* cfg, int device, capdec_handle
   if (const char* e = getenv("CAPDEC_LN_TMA_STORE")) h->force_ln_tma_store = atoi(e) != 0 ? 1 : 0;
   if (const char* e = getenv("CAPDEC_NO_CROSS_STREAM")) h->no_cross_stream = atoi(e) != 0;
   if (const char* e = getenv("CAPDEC_NO_WS")) h->no_ws = atoi(e) != 0;
+  if (const char* e = getenv("CAPDEC_WS_MIN_M")) h->ws_min_m = std::max(128, atoi(e));
   if (const char* e = getenv("CAPDEC_WS_DBG")) h->ws_dbg = atoi(e);  // tuning aid: 1 = skip the output stores, 2 = skip the weight load (wrong results)
   if (const char* e = getenv("CAPDEC_NO_WHOLE_K")) h->no_whole_k = atoi(e) != 0;
   if (const char* e = getenv("CAPDEC_FFN2_FUSE")) h->no_ffn2_fuse = atoi(e) == 0;
@@ -1247,7 +1253,7 @@ static int enqueue_step_fast(capdec_handle h, cudaStream_t s, int n_images, int 
     {  // self-attention block
       SwapQKV<bf16> eq{(bf16*)h->q, kc, vc, lp.b_qkv, st, h->t_pad};
       set_tag(h, "gemm_qkv", gemm_bytes(M, 3 * kD, kD, 2, 2, 2));
-      if (use_ws(h, 3 * kD)) TRY(launch_ws(h, s, lp.m_qkv, h->tx_xb, M, 3 * kD, WsQKV{h->ts_q, lp.ts_k, lp.ts_v, lp.b_qkv, st}, st));
+      if (use_ws(h, 3 * kD, M)) TRY(launch_ws(h, s, lp.m_qkv, h->tx_ws, M, 3 * kD, WsQKV{h->ts_q, lp.ts_k, lp.ts_v, lp.b_qkv, st}, st));
       else TRY((launch_swap<false>(h, s, lp.m_qkv, h->tx_xb, M, 3 * kD, kD, eq, no_ln, st)));
       TRY(fast_self_attn(h, s, l, M));
       SwapLNParams ln{h->x, (bf16*)h->xb, lp.b_so, lp.ln_w[0], lp.ln_b[0], h->ts_x, h->ts_xb, h->ln_tma_store};
@@ -1257,7 +1263,7 @@ static int enqueue_step_fast(capdec_handle h, cudaStream_t s, int n_images, int 
     {  // cross-attention block
       SwapLinear<bf16, false> eq{(bf16*)h->q, lp.b_cq, kD};
       set_tag(h, "gemm_cross_q", gemm_bytes(M, kD, kD, 2, 2, 2));
-      if (use_ws(h, kD)) TRY(launch_ws(h, s, lp.m_cq, h->tx_xb, M, kD, WsLinear<false>{h->ts_q, lp.b_cq}, st));
+      if (use_ws(h, kD, M)) TRY(launch_ws(h, s, lp.m_cq, h->tx_ws, M, kD, WsLinear<false>{h->ts_q, lp.b_cq}, st));
       else TRY((launch_swap<false>(h, s, lp.m_cq, h->tx_xb, M, kD, kD, eq, no_ln, st)));
       TRY(fast_cross_attn(h, s, l, n_images, group, S));
       SwapLNParams ln{h->x, (bf16*)h->xb, lp.b_co, lp.ln_w[1], lp.ln_b[1], h->ts_x, h->ts_xb, h->ln_tma_store};
@@ -1267,7 +1273,7 @@ static int enqueue_step_fast(capdec_handle h, cudaStream_t s, int n_images, int 
     {  // feed-forward block
       SwapLinear<bf16, true> e1{(bf16*)h->hbuf, lp.b_1, F};
       set_tag(h, "gemm_ffn1", gemm_bytes(M, F, kD, 2, 2, 2));
-      if (use_ws(h, F)) TRY(launch_ws(h, s, lp.m_1, h->tx_xb, M, F, WsLinear<true>{h->ts_h, lp.b_1}, st));
+      if (use_ws(h, F, M)) TRY(launch_ws(h, s, lp.m_1, h->tx_ws, M, F, WsLinear<true>{h->ts_h, lp.b_1}, st));
       else TRY((launch_swap<false>(h, s, lp.m_1, h->tx_xb, M, F, kD, e1, no_ln, st)));
       const int row_tiles = (M + h->bnb - 1) / h->bnb;
       if (M <= h->part_rows && 16 * row_tiles <= 148 && F % (4 * kSwapBK) == 0 && !h->no_ffn2_split) {
@@ -1326,9 +1332,10 @@ static int ensure_activation_maps(capdec_handle h, int M) {
     h->ln_tma_store = h->force_ln_tma_store >= 0 ? h->force_ln_tma_store : (h->bnb == 32 ? 1 : 0);
     TRY(make_store_map(h, &h->ts_x, h->x, M, kD, h->bnb, true));
     TRY(make_store_map(h, &h->ts_xb, h->xb, M, kD, h->bnb, false));
-    if (h->bnb == 128) {  // output views of the weight-stationary GEMM's bulk stores
+    if (M >= h->ws_min_m) {  // output views of the weight-stationary GEMM's bulk stores; its X tiles are always 128 rows
       TRY(make_store_map(h, &h->ts_q, h->q, M, kD, 128, false));
       TRY(make_store_map(h, &h->ts_h, h->hbuf, M, h->cfg.d_ff, 128, false));
+      TRY(make_map(h, &h->tx_ws, h->xb, M, kD, 128));
     }
     // Measured on B200 (tools/chain_ab.sh, same box): the chains win only while every cluster of a launch is
     // co-resident (8 CTAs x <= 15 clusters): cfg2 (256 rows) 269.6 -> 266.3 us/step.  Beyond that each CTA still streams
