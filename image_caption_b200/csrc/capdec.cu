@@ -351,7 +351,7 @@ static cudaError_t configure_ws_epi() {
 static bool use_ws(capdec_handle h, int n_out, int M) {
   const int f_tiles = n_out / kSwapBF, n_tiles = (M + 127) / 128;
   if (h->no_ws || M < h->ws_min_m || f_tiles > 148) return false;
-  return f_tiles * std::min(n_tiles, 148 / f_tiles) >= 96;
+  return f_tiles * std::min(n_tiles, 148 / f_tiles) >= h->ws_min_ctas;
 }
 
 // bf16 [rows][H][t_pad][64] self K/V cache of one layer as a 4-D tensor for the in_proj epilogue's bulk store:
@@ -714,6 +714,7 @@ extern "C" int capdec_create(const capdec_config* cfg, int device, capdec_handle
   if (const char* e = getenv("CAPDEC_LN_TMA_STORE")) h->force_ln_tma_store = atoi(e) != 0 ? 1 : 0;
   if (const char* e = getenv("CAPDEC_NO_CROSS_STREAM")) h->no_cross_stream = atoi(e) != 0;
   if (const char* e = getenv("CAPDEC_NO_WS")) h->no_ws = atoi(e) != 0;
+  if (const char* e = getenv("CAPDEC_WS_MIN_CTAS")) h->ws_min_ctas = atoi(e);
   if (const char* e = getenv("CAPDEC_WS_MIN_M")) h->ws_min_m = std::max(128, atoi(e));
   if (const char* e = getenv("CAPDEC_WS_DBG")) h->ws_dbg = atoi(e);  // tuning aid: 1 = skip the output stores, 2 = skip the weight load (wrong results)
   if (const char* e = getenv("CAPDEC_NO_WHOLE_K")) h->no_whole_k = atoi(e) != 0;

@@ -98,7 +98,8 @@ struct capdec_engine {
   int force_ln_tma_store = -1;     // env CAPDEC_LN_TMA_STORE
   int force_head_rw = 0;           // env CAPDEC_HEAD_RW: rows per warp of the vocabulary head (1, 2, 4, 6)
   int ws_dbg = 0;
-  int ws_min_m = 1024;             // smallest batch that takes the weight-stationary GEMM (env CAPDEC_WS_MIN_M)
+  int ws_min_ctas = 96;
+  int ws_min_m = 512;             // smallest batch that takes the weight-stationary GEMM (env CAPDEC_WS_MIN_M)
   CUtensorMap tx_ws;               // xb as [M,512], box = 64 x 128 rows
   bool no_ws = false;              // env CAPDEC_NO_WS: never use the weight-stationary persistent GEMM (gemm_ws.cuh)
   bool no_whole_k = false;         // env CAPDEC_NO_WHOLE_K: one TMA copy per k-block instead of whole-K copies
