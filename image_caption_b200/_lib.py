@@ -20,7 +20,7 @@ EXPORTS = (
     "capdec_abi_version", "capdec_last_error", "capdec_create", "capdec_destroy", "capdec_set_weights",
     "capdec_prefill", "capdec_decode", "capdec_generate_host", "capdec_sample_logits", "capdec_launch_count",
     "capdec_debug_gemm", "capdec_debug_cross_kv", "capdec_profile_enable", "capdec_profile_report",
-    "capdec_beam_search", "capdec_set_memory_projection", "capdec_prefill_tokens", "capdec_gemm_static",
+    "capdec_beam_search", "capdec_set_memory_projection", "capdec_prefill_tokens", "capdec_gemm_static", "capdec_cider_d",
 )
 
 
@@ -64,6 +64,13 @@ class BeamArgs(C.Structure):
                 ("score_out", _fp), ("steps_out", C.POINTER(C.c_int32))]
 
 
+class CiderArgs(C.Structure):
+    _fields_ = [("hyp_ids", _fp), ("ref_ids", _fp), ("ref_offsets", C.POINTER(C.c_int32)),
+                ("n_images", C.c_int32), ("group", C.c_int32), ("hyp_len", C.c_int32), ("n_refs", C.c_int32),
+                ("ref_len", C.c_int32), ("start_token", C.c_int32), ("end_token", C.c_int32), ("pad_token", C.c_int32),
+                ("scores_out", _fp)]
+
+
 _lib = None
 
 
@@ -105,6 +112,8 @@ def load() -> C.CDLL:
     if hasattr(lib, "capdec_gemm_static"):
         lib.capdec_gemm_static.argtypes = [H, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32,
                                            C.c_int32, C.c_int32, C.c_void_p]
+    if hasattr(lib, "capdec_cider_d"):
+        lib.capdec_cider_d.argtypes = [H, C.POINTER(CiderArgs), C.c_void_p]
     lib.capdec_debug_cross_kv.argtypes = [H, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]
     lib.capdec_profile_enable.argtypes = [H, C.c_int32]
     lib.capdec_profile_report.argtypes = [H, C.c_char_p, C.c_int32]

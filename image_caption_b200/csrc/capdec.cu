@@ -19,6 +19,7 @@
 #include "attention.cuh"
 #include "pointwise.cuh"
 #include "layer_chain.cuh"
+#include "cider.cuh"
 
 using namespace capdec;
 
@@ -1727,6 +1728,47 @@ extern "C" int capdec_debug_cross_kv(capdec_handle h, int32_t layer, int32_t whi
     gather_cross_kernel<float><<<blocks, 256, 0, (cudaStream_t)stream>>>((const float*)h->cross_kv + (size_t)(2 * layer + which) * tile, out, h->n_images, h->mem_len);
   CUDA_TRY(h, cudaGetLastError());
   h->launches++;
+  return CAPDEC_OK;
+}
+
+// ------------------------------------------------------------------ CIDEr-D reward (cider.cuh)
+extern "C" int capdec_cider_d(capdec_handle h, const capdec_cider_args* a, void* stream) {
+  if (!h || !a || !a->hyp_ids || !a->ref_ids || !a->ref_offsets || !a->scores_out) return fail(h, CAPDEC_ERR_INVALID, "null argument");
+  if (a->n_images < 1 || a->group < 1 || a->hyp_len < 1 || a->ref_len < 1 || a->n_refs < 0)
+    return fail(h, CAPDEC_ERR_INVALID, "cider: sizes must be positive");
+  if (a->ref_offsets[0] != 0 || a->ref_offsets[a->n_images] != a->n_refs) return fail(h, CAPDEC_ERR_INVALID, "cider: ref_offsets must run from 0 to n_refs");
+  const int words = std::min<int>(a->ref_len, kCdMaxTok);
+  const int per_ref = words >= 4 ? 4 * words - 6 : words * (words + 1) / 2;
+  for (int i = 0; i < a->n_images; ++i) {
+    const int n = a->ref_offsets[i + 1] - a->ref_offsets[i];
+    if (n < 0) return fail(h, CAPDEC_ERR_INVALID, "cider: ref_offsets must not decrease");
+    if ((long long)n * per_ref > kCdImgKeys)
+      return fail(h, CAPDEC_ERR_CAPACITY, "cider: image %d has %d references of up to %d words: more than %d n-grams", i, n, words, kCdImgKeys);
+  }
+  cudaStream_t s = (cudaStream_t)stream;
+  CUDA_TRY(h, cudaSetDevice(h->device));
+  size_t want = 1024;
+  while (want < (size_t)2 * std::max(1, a->n_refs) * per_ref) want <<= 1;
+  if (want > h->cider_tab || a->n_images + 1 > h->cider_off_cap) {  // (grown on demand; earlier buffers stay until destroy)
+    h->cider_tab = std::max(want, h->cider_tab);
+    h->cider_off_cap = std::max(a->n_images + 1, h->cider_off_cap);
+    TRY(dev_alloc(h, &h->cider_keys, h->cider_tab));
+    TRY(dev_alloc(h, &h->cider_cnt, h->cider_tab));
+    TRY(dev_alloc(h, &h->cider_off, (size_t)h->cider_off_cap));
+  }
+  CUDA_TRY(h, cudaMemsetAsync(h->cider_keys, 0xff, h->cider_tab * sizeof(unsigned long long), s));
+  CUDA_TRY(h, cudaMemsetAsync(h->cider_cnt, 0, h->cider_tab * sizeof(unsigned int), s));
+  CUDA_TRY(h, cudaMemcpyAsync(h->cider_off, a->ref_offsets, (size_t)(a->n_images + 1) * sizeof(int), cudaMemcpyHostToDevice, s));
+  CiderArgs A{};
+  A.hyp = (const long long*)a->hyp_ids; A.refs = (const long long*)a->ref_ids; A.ref_offsets = h->cider_off;
+  A.n_images = a->n_images; A.group = a->group; A.hyp_len = a->hyp_len; A.ref_len = a->ref_len;
+  A.start_token = a->start_token; A.end_token = a->end_token; A.pad_token = a->pad_token;
+  A.tab_keys = h->cider_keys; A.tab_cnt = h->cider_cnt; A.tab_mask = (unsigned int)(h->cider_tab - 1);
+  A.scores = a->scores_out;
+  cider_df_kernel<<<a->n_images, kCdThreads, 0, s>>>(A);
+  cider_score_kernel<<<a->n_images * a->group, kCdThreads, 0, s>>>(A);
+  CUDA_TRY(h, cudaGetLastError());
+  h->launches += 2;
   return CAPDEC_OK;
 }
 

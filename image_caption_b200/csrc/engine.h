@@ -124,6 +124,13 @@ struct capdec_engine {
   float* chain_part = nullptr;     // [row tiles][CS][BNB][512] fp32 linear2 partial products
   CUtensorMap tc_xb, tc_a;         // [64, M, 8] views of xb / a, box = 64 x chain_bnb x 8
 
+  // ---- CIDEr-D reward workspace (cider.cuh), grown on demand
+  unsigned long long* cider_keys = nullptr;
+  unsigned int* cider_cnt = nullptr;
+  int* cider_off = nullptr;
+  size_t cider_tab = 0;
+  int cider_off_cap = 0;
+
   // ---- host-buffer entry point staging (device side)
   float* stage_mem = nullptr;
   long long* stage_ids = nullptr;

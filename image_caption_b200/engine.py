@@ -442,6 +442,30 @@ class CaptionDecodeEngine:
         finished_before = (ended.cumsum(1) - ended.long()) > 0  # finished strictly before this step
         return ids.to(dst), lp.masked_fill(finished_before, 0.0).to(dst)
 
+    # ------------------------------------------------------------------ reward
+    def cider_d(self, hyp_ids: torch.Tensor, ref_ids: torch.Tensor, ref_offsets, group: int = 1, start_token: int = -1,
+                end_token: int = -1, pad_token: int = -1) -> torch.Tensor:
+        """CIDEr-D of every hypothesis against its image's references on the device (C ABI ``capdec_cider_d``):
+        ``hyp_ids`` (n_images*group, L) int64 image-major, ``ref_ids`` (n_refs, Lr) int64, ``ref_offsets`` n_images+1
+        ints (host).  Sequences are read like scst:256-269 (stop at ``end_token``, skip ``start_token`` / ``pad_token``).
+        Returns float64 (n_images*group,), what ``CiderRewardCalculator.compute_reward`` (scst:29-54) returns."""
+        hyp = hyp_ids.to(self.device, torch.int64).contiguous()
+        refs = ref_ids.to(self.device, torch.int64).contiguous()
+        offs = [int(x) for x in ref_offsets]
+        n_images = len(offs) - 1
+        if hyp.dim() != 2 or hyp.shape[0] != n_images * group:
+            raise ValueError(f"hyp_ids must be ({n_images * group}, L), got {tuple(hyp.shape)}")
+        if refs.dim() != 2 or refs.shape[0] != offs[-1]:
+            raise ValueError(f"ref_ids must be ({offs[-1]}, Lr), got {tuple(refs.shape)}")
+        out = torch.empty(hyp.shape[0], dtype=torch.float64, device=self.device)
+        off_arr = (C.c_int32 * len(offs))(*offs)
+        args = _lib.CiderArgs(hyp_ids=hyp.data_ptr(), ref_ids=refs.data_ptr(), ref_offsets=off_arr, n_images=n_images,
+                              group=group, hyp_len=hyp.shape[1], n_refs=refs.shape[0], ref_len=refs.shape[1],
+                              start_token=start_token, end_token=end_token, pad_token=pad_token, scores_out=out.data_ptr())
+        _lib.check(self._h, self._lib.capdec_cider_d(self._h, C.byref(args), _stream_ptr(self.device)))
+        self._keep_cider = (hyp, refs)  # alive until the kernels have run (stream-ordered; replaced by the next call)
+        return out
+
     # ------------------------------------------------------------------ diagnostics
     def profile(self, on: bool) -> None:
         """Per-kernel CUDA-event timing of the following rollouts (direct launches, no graph)."""

@@ -220,6 +220,24 @@ int capdec_debug_gemm(capdec_handle h, const float* a, const float* w, const flo
  * [n_images, mem_len, D] (the reference's memory @ W^T + b layout). */
 int capdec_debug_cross_kv(capdec_handle h, int32_t layer, int32_t which, float* out, void* cuda_stream);
 
+/* CIDEr-D reward of an SCST step on the device: what CiderRewardCalculator.compute_reward
+ * (utils/scst_loss.py:20-54, called at scst:179-180 on the strings of scst:256-269) returns per prediction, computed from
+ * token ids.  The arithmetic lives in pycocoevalcap (not vendored by the reference, not installable here): this follows the
+ * published CIDEr-D algorithm as restated in oracle/cider_d.py; parity is against that restatement ("unpinned").
+ * Sequences are read as the reference reads them: stop at the first end_token, skip start_token and pad_token.
+ * Token ids must be < 32768; at most 128 words per sequence are used; all references of one image together may hold at
+ * most 4096 n-grams (about 8 references of 128 words), else CAPDEC_ERR_CAPACITY.  The scorer's corpus is THIS call's
+ * references (document frequencies and log N from the n_images reference sets), as in the reference's per-batch call. */
+typedef struct {
+  const int64_t* hyp_ids;      /* DEVICE [n_images * group, hyp_len]: hypotheses, image-major             */
+  const int64_t* ref_ids;      /* DEVICE [n_refs, ref_len]: reference captions as token ids                 */
+  const int32_t* ref_offsets;  /* HOST   [n_images + 1]: references of image i = rows ref_offsets[i] .. ref_offsets[i+1]-1 */
+  int32_t n_images, group, hyp_len, n_refs, ref_len;
+  int32_t start_token, end_token, pad_token;
+  double* scores_out;          /* DEVICE [n_images * group] fp64, as the reference's Python floats          */
+} capdec_cider_args;
+int capdec_cider_d(capdec_handle h, const capdec_cider_args* a, void* cuda_stream);
+
 /* Allocation-free projection: C[m,n] = act(A[m,k] W[n,k]^T + bias), fp32 DEVICE pointers, the computation of
  * capdec_debug_gemm (same kernels, same rounding: bf16 operands / fp32 accumulate on a bf16 engine) with the bf16 operand
  * scratch in a file-scope device array instead of cudaMalloc'd buffers.  It has NO counterpart in the reference: it was

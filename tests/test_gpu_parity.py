@@ -992,3 +992,73 @@ def test_zz_report_measured_errors():
     if os.path.isdir(d):
         with open(os.path.join(d, "parity_errors.json"), "w") as f:
             json.dump({"max_abs_logit_error": MEASURED, "tolerance": TOL}, f)
+
+
+# ---------------------------------------------------------------- CIDEr-D reward on the device (oracle unpinned)
+def _cider_case(seed, n_images, group, max_refs, hyp_len, ref_len, vocab=40):
+    g = np.random.default_rng(seed)
+    hyp = g.integers(1, vocab, size=(n_images * group, hyp_len))
+    hyp[:, 0] = START
+    for m in range(hyp.shape[0]):  # ragged: <end> somewhere, <pad> after it; some rows never end, some end at once
+        e = int(g.integers(1, hyp_len + 3))
+        if e < hyp_len:
+            hyp[m, e] = END
+            hyp[m, e + 1:] = PAD
+    offs, refs = [0], []
+    for i in range(n_images):
+        k = int(g.integers(1, max_refs + 1))
+        for _ in range(k):
+            r = g.integers(1, vocab, size=ref_len)
+            if g.random() < 0.5:  # half of the references are noisy copies of a hypothesis of the image: overlapping n-grams
+                src = hyp[i * group + int(g.integers(0, group))]
+                r[: min(ref_len, hyp_len)] = src[: min(ref_len, hyp_len)]
+                r[g.integers(0, ref_len, size=2)] = g.integers(1, vocab, size=2)
+            e = int(g.integers(2, ref_len + 2))
+            if e < ref_len:
+                r[e] = END
+                r[e + 1:] = PAD
+            refs.append(r)
+        offs.append(len(refs))
+    return hyp.astype(np.int64), np.stack(refs).astype(np.int64), offs
+
+
+@pytest.mark.parametrize("seed,n_images,group,max_refs,hyp_len,ref_len", [(0, 16, 1, 5, 20, 24), (1, 7, 6, 3, 50, 40), (2, 1, 2, 2, 12, 12),
+                                                                           (3, 64, 6, 8, 50, 128), (4, 3, 1, 1, 3, 2)])
+def test_cider_d_reward_against_the_restated_algorithm(dev, seed, n_images, group, max_refs, hyp_len, ref_len):
+    """capdec_cider_d against oracle/cider_d.py (the published CIDEr-D algorithm; pycocoevalcap itself is absent, so this is
+    parity with the restatement only): ragged hypotheses and references, empty hypotheses, several rollouts per image
+    sharing the references, a single image (log N = 0), sentences shorter than 4 words.  fp64 on both sides: 1e-9."""
+    from oracle import cider_d as oracle_cider
+    hyp, refs, offs = _cider_case(seed, n_images, group, max_refs, hyp_len, ref_len)
+    eng = make_engine(small_decoder(layers=1).to(dev), "bf16", max_images=1, max_mem=1, max_len=4)
+    got = eng.cider_d(torch.from_numpy(hyp), torch.from_numpy(refs), offs, group, START, END, PAD).cpu().numpy()
+    want = np.array(oracle_cider.cider_d_from_ids(hyp, refs, offs, group, START, END, PAD))
+    assert got.shape == want.shape and np.isfinite(got).all()
+    assert np.abs(got - want).max() <= 1e-9 * max(1.0, np.abs(want).max()), np.abs(got - want).max()
+    if n_images > 3:  # (tiny cases only check agreement; one image: log N = 0, every tf-idf weight is <= 0 and the score 0 -- the scorer's own behaviour)
+        assert want.max() > 0.5, "the case must contain overlapping n-grams"
+    again = eng.cider_d(torch.from_numpy(hyp), torch.from_numpy(refs), offs, group, START, END, PAD).cpu().numpy()
+    assert np.abs(again - got).max() <= 1e-12  # the table is cleared between calls
+    eng.close()
+
+
+def test_cider_d_string_front_end_and_limits(dev):
+    """DeviceCiderReward.compute_reward takes the reference calculator's arguments (scst:29-54: list of str, list of list of
+    str | str) and returns a list of floats; identical sentences score 10; too many references raise."""
+    from image_caption_b200 import _lib
+    from image_caption_b200.reward import DeviceCiderReward
+    from oracle import cider_d as oracle_cider
+    eng = make_engine(small_decoder(layers=1).to(dev), "bf16", max_images=1, max_mem=1, max_len=4)
+    calc = DeviceCiderReward(eng)
+    preds = ["a woman wears a long sleeve shirt", "the shirt has a round neckline", "", "pants"]
+    refs = [["a woman wears a long sleeve shirt", "this lady wears a long sleeve shirt with solid color patterns"],
+            "the shirt has a round neckline", ["a man wears shorts"], ["the pants are long", "pants pants"]]
+    got = calc.compute_reward(preds, refs)
+    want = oracle_cider.cider_d([p.split() for p in preds], [[r.split() for r in (rs if isinstance(rs, list) else [rs])] for rs in refs])
+    assert isinstance(got, list) and len(got) == 4
+    assert np.abs(np.array(got) - np.array(want)).max() <= 1e-9
+    assert abs(got[1] - 10.0) < 1e-9 and got[2] == 0.0
+    with pytest.raises(_lib.CapdecError) as ei:  # 40 references of 128 words for one image: more n-grams than the kernel sorts
+        eng.cider_d(torch.ones(1, 8, dtype=torch.int64), torch.ones(40, 128, dtype=torch.int64), [0, 40], 1, START, END, PAD)
+    assert ei.value.code == -4
+    eng.close()
