@@ -12,6 +12,7 @@ ABI_VERSION = 1
 MAX_LAYERS = 12
 PREC_FP32, PREC_BF16 = 0, 1
 FLAG_NO_GRAPH, FLAG_NO_UMMA, FLAG_V1_STEP, FLAG_NO_PDL = 1, 2, 4, 8
+FLAG_BATCH_INVARIANT = 32
 DECODE_NO_EARLY_STOP = 1
 DECODE_TEACHER_FORCED = 2
 BEAM_STOP_GRID = 1

@@ -728,6 +728,12 @@ extern "C" int capdec_create(const capdec_config* cfg, int device, capdec_handle
   if (const char* e = getenv("CAPDEC_KSPLIT")) h->force_ksplit = atoi(e);
   if (const char* e = getenv("CAPDEC_NO_FFN2_SPLIT")) h->no_ffn2_split = atoi(e) != 0;
   if (const char* e = getenv("CAPDEC_NO_PDL")) { if (atoi(e)) h->use_pdl = false; }
+  if (cfg->flags & CAPDEC_FLAG_BATCH_INVARIANT) {  // one route for every batch size (see capdec.h)
+    h->chain = false;
+    h->no_ws = true;
+    h->force_bnb = 64;
+    h->no_ffn2_split = true;
+  }
   int rc = create_impl(h);
   if (rc) {
     g_create_error = h->err;

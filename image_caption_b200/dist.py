@@ -7,7 +7,12 @@ computation that follows (utils/scst_loss.py:175-180).
 
 * contiguous blocks of images per rank, all ``group`` rollouts of an image on one rank;
 * Philox counters use the GLOBAL sequence id (``seq_id_base = first_image * group``), so the
-  tokens do not depend on the number of ranks;
+  draws do not depend on the number of ranks.  The TOKENS are bit-identical for every N when all
+  shards take the same kernel route: always in fp32 mode and with ``batch_invariant=True``
+  (CAPDEC_FLAG_BATCH_INVARIANT); in the default bf16 mode the engine picks the fastest route per
+  batch size (projection chains / swap-AB / weight-stationary GEMMs differ in fp32 summation
+  order), so shards of a different size class agree with the unsharded rollout within the bf16
+  tolerance only and a near-tie may flip a token (bench.py's ``verify`` reports both);
 * a rank cannot know the global stop step without a per-step collective, and the greedy rule
   (vit:322: ALL rows emit <end> on the SAME step) depends on what finished rows keep emitting,
   so ranks decode all ``max_len - 1`` steps (``early_stop=False``) and the gathered result is

@@ -60,7 +60,7 @@ def vit_encoder_tokens(encoder: torch.nn.Module, images: torch.Tensor) -> torch.
 class CaptionDecodeEngine:
     def __init__(self, decoder: torch.nn.Module, precision: str = "bf16", max_images: int = 64,
                  max_group: int = 1, max_mem: int = 196, max_len: int = 50, use_graph: bool = True,
-                 use_umma: bool = True, step_impl: str = "v2", pdl: bool = True):
+                 use_umma: bool = True, step_impl: str = "v2", pdl: bool = True, batch_invariant: bool = False):
         self._lib = _lib.load()
         self.decoder = decoder
         sd = dict(decoder.state_dict())
@@ -82,7 +82,8 @@ class CaptionDecodeEngine:
         if step_impl not in ("v1", "v2"):
             raise ValueError(f"step_impl must be 'v1' or 'v2', got {step_impl!r}")
         self._flags = ((0 if use_graph else _lib.FLAG_NO_GRAPH) | (0 if use_umma else _lib.FLAG_NO_UMMA)
-                       | (_lib.FLAG_V1_STEP if step_impl == "v1" else 0) | (0 if pdl else _lib.FLAG_NO_PDL))
+                       | (_lib.FLAG_V1_STEP if step_impl == "v1" else 0) | (0 if pdl else _lib.FLAG_NO_PDL)
+                       | (_lib.FLAG_BATCH_INVARIANT if batch_invariant else 0))
         self._cap = dict(max_images=max_images, max_group=max_group, max_mem=max_mem, max_len=max_len)
         self._h = C.c_void_p()
         self._weights_sig = None

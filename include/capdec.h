@@ -80,6 +80,12 @@ typedef struct {
 #define CAPDEC_FLAG_V1_STEP 4    /* bf16 mode: the first-generation step kernels (one GEMM tile per CTA,
                                     separate LayerNorm / vocabulary / head kernels); kept for A/B runs */
 #define CAPDEC_FLAG_NO_PDL 8     /* do not chain the step's kernels with programmatic dependent launch */
+#define CAPDEC_FLAG_BATCH_INVARIANT 32 /* bf16 mode: ONE kernel route whatever the batch size (64-row swap-AB tiles, no
+                                    projection chains, no weight-stationary GEMM, no split-K FFN2), so that a sequence's
+                                    tokens and log-probs are bit-identical however the batch is sharded or split.  The
+                                    default picks the fastest route per batch size; routes differ in fp32 summation
+                                    order, so results across DIFFERENT batch sizes then agree only within the bf16
+                                    tolerance (and a near-tie may flip a token). */
 
 /* fp32 DEVICE pointers, borrowed for the duration of capdec_set_weights only. */
 typedef struct {
