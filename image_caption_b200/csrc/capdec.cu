@@ -333,13 +333,13 @@ static int launch_swap_bnb(capdec_handle h, cudaStream_t s, const WeightMaps& tw
 // Large batches, K = 512, no LayerNorm: persistent weight-stationary GEMM (gemm_ws.cuh), one wave of CTAs.
 template <typename Epi>
 static int launch_ws(capdec_handle h, cudaStream_t s, const WeightMaps& tw, const CUtensorMap& tx, int M, int n_out, const Epi& epi,
-                     const DecState* st) {
+                     const DecState* st, int n_tiles_override = 0) {
   constexpr int BNB = 128;
-  const int f_tiles = n_out / kSwapBF, n_tiles = (M + BNB - 1) / BNB;
+  const int f_tiles = n_out / kSwapBF, n_tiles = n_tiles_override > 0 ? n_tiles_override : (M + BNB - 1) / BNB;
   const int groups = std::max(1, std::min(n_tiles, 148 / f_tiles));
   ProfScope ps(h, s);
   cudaError_t e = launch_ex(gemm_ws_kernel<BNB, Epi>, dim3(f_tiles, groups), dim3(kWsThreads), ws_smem_bytes(BNB), s, 1, h->use_pdl,
-                            tw.bn[2], tx, M, epi, st, h->ws_dbg);
+                            tw.bn[2], tx, n_tiles, epi, st, h->ws_dbg);
   if (e != cudaSuccess) return fail(h, CAPDEC_ERR_CUDA, "gemm_ws launch failed: %s (n_out=%d M=%d)", cudaGetErrorString(e), n_out, M);
   h->launches_this_enqueue++;
   return 0;
@@ -407,6 +407,7 @@ static cudaError_t configure_fast_kernels() {
   if (e == cudaSuccess) e = configure_ws_epi<WsLinear<false>>();
   if (e == cudaSuccess) e = configure_ws_epi<WsLinear<true>>();
   if (e == cudaSuccess) e = configure_ws_epi<WsQKV>();
+  if (e == cudaSuccess) e = configure_ws_epi<WsCrossKV>();
   if (e == cudaSuccess) e = configure_swap_ln_ks<32, 2>();
   if (e == cudaSuccess) e = configure_swap_ln_ks<64, 2>();
   if (e == cudaSuccess) e = configure_swap_ln_ks<128, 2>();
@@ -715,6 +716,7 @@ extern "C" int capdec_create(const capdec_config* cfg, int device, capdec_handle
   if (const char* e = getenv("CAPDEC_LN_TMA_STORE")) h->force_ln_tma_store = atoi(e) != 0 ? 1 : 0;
   if (const char* e = getenv("CAPDEC_NO_CROSS_STREAM")) h->no_cross_stream = atoi(e) != 0;
   if (const char* e = getenv("CAPDEC_NO_WS")) h->no_ws = atoi(e) != 0;
+  if (const char* e = getenv("CAPDEC_NO_WS_PREFILL")) h->no_ws_prefill = atoi(e) != 0;
   if (const char* e = getenv("CAPDEC_WS_MIN_CTAS")) h->ws_min_ctas = atoi(e);
   if (const char* e = getenv("CAPDEC_WS_MIN_M")) h->ws_min_m = std::max(128, atoi(e));
   if (const char* e = getenv("CAPDEC_WS_DBG")) h->ws_dbg = atoi(e);  // tuning aid: 1 = skip the output stores, 2 = skip the weight load (wrong results)
@@ -859,6 +861,33 @@ static int prefill_chunk(capdec_handle h, cudaStream_t s, const float* memory_ch
     convert_kernel<bf16><<<(unsigned)((n4 + 255) / 256), 256, 0, s>>>(memory_chunk, (bf16*)h->mem_b + off, n4);
     CUDA_TRY(h, cudaGetLastError());
     h->launches_this_enqueue++;
+  }
+  if (h->fast && !h->no_ws && !h->no_ws_prefill) {
+    // persistent weight-stationary GEMM (gemm_ws.cuh): 128-row tiles, per-image bulk tensor stores straight into the
+    // cross cache layout (WsCrossKV)
+    const int box_s = std::min(mem_len, 128);
+    WsCrossKV epi{};
+    {
+      EncodeTiledFn fn = encode_tiled_fn();
+      if (!fn) return fail(h, CAPDEC_ERR_CUDA, "cuTensorMapEncodeTiled entry point unavailable");
+      const cuuint64_t S = (cuuint64_t)mem_len;
+      cuuint64_t dims[5] = {(cuuint64_t)kHD, S, (cuuint64_t)kH, (cuuint64_t)n_images, (cuuint64_t)h->cfg.n_layer * 2};
+      cuuint64_t strides[4] = {(cuuint64_t)kHD * 2, S * kHD * 2, (cuuint64_t)kH * S * kHD * 2, (cuuint64_t)n_images * kH * S * kHD * 2};
+      cuuint32_t estr[5] = {1, 1, 1, 1, 1};
+      for (int k = -1; k < 7; ++k) {  // -1: the whole-box view; k: the box of 2^k positions (never used when 2^k > S)
+        cuuint32_t box[5] = {(cuuint32_t)kHD, (cuuint32_t)(k < 0 ? box_s : std::min(1 << k, mem_len)), 1, 1, 1};
+        CUresult r = fn(k < 0 ? &epi.ts : &epi.ts_p2[k], CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, h->cross_kv, dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS)
+          return fail(h, CAPDEC_ERR_CUDA, "cuTensorMapEncodeTiled (cross cache store view %d) failed (%d) S=%d images=%d", k, (int)r, mem_len, n_images);
+      }
+    }
+    epi.bias = h->b_ckv; epi.S = mem_len; epi.box = box_s; epi.img0 = img0; epi.rows = M;
+    CUtensorMap tm_x;
+    TRY(make_map(h, &tm_x, (bf16*)h->mem_b + off, M, kD, 128));
+    set_tag(h, "prefill_gemm_cross_kv", gemm_bytes(M, N, kD, h->esz, h->esz, h->esz));
+    return launch_ws(h, s, h->m_ckv, tm_x, M, N, epi, nullptr);
   }
   EpiCrossKV<float> e32{(float*)h->cross_kv, h->b_ckv, n_images, mem_len, img0};
   EpiCrossKV<bf16> e16{(bf16*)h->cross_kv, h->b_ckv, n_images, mem_len, img0};

@@ -98,6 +98,7 @@ struct capdec_engine {
   int force_ln_tma_store = -1;     // env CAPDEC_LN_TMA_STORE
   int force_head_rw = 0;           // env CAPDEC_HEAD_RW: rows per warp of the vocabulary head (1, 2, 4, 6)
   int ws_dbg = 0;
+  bool no_ws_prefill = false;      // env CAPDEC_NO_WS_PREFILL: prefill through the one-tile-per-CTA GEMM (gemm_umma.cuh)
   int ws_min_ctas = 96;
   int ws_min_m = 512;             // smallest batch that takes the weight-stationary GEMM (env CAPDEC_WS_MIN_M)
   CUtensorMap tx_ws;               // xb as [M,512], box = 64 x 128 rows

@@ -89,7 +89,9 @@ struct WsLinear {
     const float r = acc + pre.bias;
     return kRelu ? fmaxf(r, 0.f) : r;
   }
-  __device__ __forceinline__ void store(const void* stage, int f0, int b0, const SwapEpiPre&) const { ptx::tma_store_2d(&ts, stage, f0, b0); }
+  __device__ __forceinline__ int row0(int tile) const { return tile * 128; }
+  __device__ __forceinline__ int stage_index(int j, int fl) const { return j * kSwapBF + fl; }  // row-major [128 rows][128 features]
+  __device__ __forceinline__ void store(const void* stage, int f0, int tile, const SwapEpiPre&) const { ptx::tma_store_2d(&ts, stage, f0, tile * 128); }
 };
 // self-attention in_proj: features [0,512) -> q, [512,1024) -> K cache position st->step, [1024,1536) -> V cache.
 // ts_k / ts_v: this layer's cache [rows][H][t_pad][64] as a 4-D tensor, box = {64, 1 position, 2 heads, BNB rows}.
@@ -101,10 +103,51 @@ struct WsQKV {
   const DecState* st;
   __device__ __forceinline__ SwapEpiPre prepare(int f) const { return SwapEpiPre{__ldg(bias + f), st->step}; }
   __device__ __forceinline__ float value(float acc, const SwapEpiPre& pre) const { return acc + pre.bias; }
-  __device__ __forceinline__ void store(const void* stage, int f0, int b0, const SwapEpiPre& pre) const {
+  __device__ __forceinline__ int row0(int tile) const { return tile * 128; }
+  __device__ __forceinline__ int stage_index(int j, int fl) const { return j * kSwapBF + fl; }
+  __device__ __forceinline__ void store(const void* stage, int f0, int tile, const SwapEpiPre& pre) const {
+    const int b0 = tile * 128;
     const int which = f0 >> 9, c = f0 & (kD - 1);
     if (which == 0) ptx::tma_store_2d(&ts_q, stage, c, b0);
     else ptx::tma_store_4d(which == 1 ? &ts_k : &ts_v, stage, 0, pre.step, c >> 6, b0);
+  }
+};
+
+// Prefill: rows = (image, memory position), features = layer*1024 + kv*512 + head*64 + d; destination = the
+// cross cache [L*2][n_images][H][S][64], seen as a 5-D tensor {64, S, H, n_images, L*2}.  A tile is 128 consecutive rows,
+// staged as [head][128 rows][64]; it overlaps a few images, and each overlap (image i, positions [s_lo, s_lo + n)) is stored
+// per head with bulk tensor stores that fit it exactly: one box of min(S, 128) positions when n is that, else the binary
+// decomposition of n over the boxes of 64, 32, ... 1 positions (ts_p2[k] = box of 2^k positions).  Nothing relies on the
+// copy engine clipping a box: a store at a negative position faults on B200 (measured: illegal instruction).
+struct WsCrossKV {
+  alignas(64) CUtensorMap ts;
+  alignas(64) CUtensorMap ts_p2[7];
+  const float* bias;
+  int S, box, img0, rows;  // box = min(S, 128); img0 = first image of this chunk; rows = n_chunk * S rows of X
+  __device__ __forceinline__ SwapEpiPre prepare(int f) const { return SwapEpiPre{__ldg(bias + f), 0}; }
+  __device__ __forceinline__ float value(float acc, const SwapEpiPre& pre) const { return acc + pre.bias; }
+  __device__ __forceinline__ int row0(int tile) const { return tile * 128; }
+  __device__ __forceinline__ int stage_index(int j, int fl) const { return ((fl >> 6) * 128 + j) * 64 + (fl & 63); }
+  __device__ __forceinline__ void put(const CUtensorMap* m, uint32_t src, int jrow, int pos, int head0, int img, int lk) const {
+#pragma unroll
+    for (int hh = 0; hh < 2; ++hh)
+      asm volatile("cp.async.bulk.tensor.5d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5, %6}], [%1];"
+                   ::"l"(reinterpret_cast<uint64_t>(m)), "r"(src + (uint32_t)((hh * 128 + jrow) * 128)), "r"(0), "r"(pos),
+                     "r"(head0 + hh), "r"(img), "r"(lk)
+                   : "memory");
+  }
+  __device__ __forceinline__ void store(const void* stage, int f0, int tile, const SwapEpiPre&) const {
+    const int lk = f0 >> 9, head0 = (f0 & (kD - 1)) >> 6;
+    const int r0 = tile * 128, r1 = min(r0 + 128, rows);
+    const uint32_t src = ptx::smem_u32(stage);
+    for (int i = r0 / S; i * S < r1; ++i) {
+      const int a = max(i * S, r0), b = min((i + 1) * S, r1);  // rows [a, b) of the tile belong to image i
+      int n = b - a, pos = a - i * S, jrow = a - r0;
+      if (n == box) { put(&ts, src, jrow, pos, head0, img0 + i, lk); continue; }
+#pragma unroll 1
+      for (int k = 6; k >= 0; --k)
+        if (n & (1 << k)) { put(&ts_p2[k], src, jrow, pos, head0, img0 + i, lk); pos += 1 << k; jrow += 1 << k; }
+    }
   }
 };
 
@@ -112,7 +155,7 @@ struct WsQKV {
 // tm_w: the packed bf16 weight matrix [n_out, 512], box = 64 columns x 128 rows; tm_x: [M, 512] activations, box = 64 x BNB.
 template <int BNB, typename Epi>
 __global__ void __launch_bounds__(kWsThreads, 1)
-gemm_ws_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CUtensorMap tm_x, int M,
+gemm_ws_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CUtensorMap tm_x, int n_tiles,
                const __grid_constant__ Epi epi, const DecState* st, int dbg) {
   static_assert(BNB == 128, "the weight prologue borrows the operand ring: stage bytes must equal one 128-row weight box");
   extern __shared__ uint8_t smem_raw[];
@@ -130,7 +173,6 @@ gemm_ws_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int f0 = blockIdx.x * kSwapBF;
-  const int n_tiles = (M + BNB - 1) / BNB;
   const int my_tiles = ((int)blockIdx.y < n_tiles) ? (n_tiles - 1 - (int)blockIdx.y) / (int)gridDim.y + 1 : 0;
 
   if (warp == 0) {
@@ -189,13 +231,13 @@ gemm_ws_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__
       int s = 0;
       uint32_t ph = 0u;
       for (int i = 0; i < my_tiles; ++i) {
-        const int b0 = ((int)blockIdx.y + i * (int)gridDim.y) * BNB;
+        const int b0 = epi.row0((int)blockIdx.y + i * (int)gridDim.y);
         for (int kb = 0; kb < kWsKB; ++kb, ++s) {
           if (s == stages) { s = 0; ph ^= 1u; }
           ptx::mbar_wait(&empty[s], ph ^ 1u);
           if (ptx::elect_one()) {
             ptx::mbar_expect_tx(&full[s], kXBytes);
-            ptx::tma_load_2d(smem + (size_t)s * kXBytes, &tm_x, &full[s], kb * 64, b0);  // rows >= M arrive as zeros
+            ptx::tma_load_2d(smem + (size_t)s * kXBytes, &tm_x, &full[s], kb * 64, b0);  // rows beyond the matrix arrive as zeros
           }
           __syncwarp();
         }
@@ -239,7 +281,7 @@ gemm_ws_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__
       const SwapEpiPre pre = epi.prepare(f0 + fl);
       for (int i = 0; i < my_tiles; ++i) {
         const int buf = i & 1;
-        const int b0 = ((int)blockIdx.y + i * (int)gridDim.y) * BNB;
+        const int tile = (int)blockIdx.y + i * (int)gridDim.y;
         bf16* stage = reinterpret_cast<bf16*>(out_s + (size_t)buf * ws_out_bytes(BNB));
         if (issuer && i >= 2) ptx::bulk_wait_read1();  // the store of tile i-2 has read this staging buffer
         ptx::bar_sync(1, kWsEpi);
@@ -251,7 +293,10 @@ gemm_ws_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__
           ptx::tmem_ld32(t_lane + (uint32_t)(buf * BNB + c0), v);
           if (!(dbg & 1)) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) stage[(c0 + j) * kSwapBF + fl] = __float2bfloat16_rn(epi.value(v[j], pre));
+            for (int j = 0; j < 32; ++j) {
+              const int at = epi.stage_index(c0 + j, fl);  // where (row j of the tile, feature fl) sits in the staged box
+              if (at >= 0) stage[at] = __float2bfloat16_rn(epi.value(v[j], pre));
+            }
           }
         }
         ptx::tc_fence_before();
@@ -260,7 +305,7 @@ gemm_ws_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__
         ptx::fence_proxy_async();
         ptx::bar_sync(1, kWsEpi);
         if (issuer && !(dbg & 1)) {  // rows >= M are clipped by the store maps
-          epi.store(stage, f0, b0, pre);
+          epi.store(stage, f0, tile, pre);
           ptx::bulk_commit();
         }
       }
