@@ -719,7 +719,7 @@ extern "C" int capdec_create(const capdec_config* cfg, int device, capdec_handle
   if (const char* e = getenv("CAPDEC_NO_WS_PREFILL")) h->no_ws_prefill = atoi(e) != 0;
   if (const char* e = getenv("CAPDEC_WS_MIN_CTAS")) h->ws_min_ctas = atoi(e);
   if (const char* e = getenv("CAPDEC_WS_MIN_M")) h->ws_min_m = std::max(128, atoi(e));
-  if (const char* e = getenv("CAPDEC_WS_DBG")) h->ws_dbg = atoi(e);  // tuning aid: 1 = skip the output stores, 2 = skip the weight load (wrong results)
+  if (const char* e = getenv("CAPDEC_WS_DBG")) h->ws_dbg = atoi(e);  // tuning aid (wrong results): 1 = no output staging/stores, 2 = no weight load, 4 = no activation loads after tile 0, 8 = no bulk stores, 16 = no staging
   if (const char* e = getenv("CAPDEC_NO_WHOLE_K")) h->no_whole_k = atoi(e) != 0;
   if (const char* e = getenv("CAPDEC_FFN2_FUSE")) h->no_ffn2_fuse = atoi(e) == 0;
   if (const char* e = getenv("CAPDEC_HEAD_RW")) { const int v = atoi(e); h->force_head_rw = (v == 1 || v == 2 || v == 4 || v == 6) ? v : 0; }
@@ -863,27 +863,9 @@ static int prefill_chunk(capdec_handle h, cudaStream_t s, const float* memory_ch
     h->launches_this_enqueue++;
   }
   if (h->fast && !h->no_ws && !h->no_ws_prefill) {
-    // persistent weight-stationary GEMM (gemm_ws.cuh): 128-row tiles, per-image bulk tensor stores straight into the
-    // cross cache layout (WsCrossKV)
-    const int box_s = std::min(mem_len, 128);
-    WsCrossKV epi{};
-    {
-      EncodeTiledFn fn = encode_tiled_fn();
-      if (!fn) return fail(h, CAPDEC_ERR_CUDA, "cuTensorMapEncodeTiled entry point unavailable");
-      const cuuint64_t S = (cuuint64_t)mem_len;
-      cuuint64_t dims[5] = {(cuuint64_t)kHD, S, (cuuint64_t)kH, (cuuint64_t)n_images, (cuuint64_t)h->cfg.n_layer * 2};
-      cuuint64_t strides[4] = {(cuuint64_t)kHD * 2, S * kHD * 2, (cuuint64_t)kH * S * kHD * 2, (cuuint64_t)n_images * kH * S * kHD * 2};
-      cuuint32_t estr[5] = {1, 1, 1, 1, 1};
-      for (int k = -1; k < 7; ++k) {  // -1: the whole-box view; k: the box of 2^k positions (never used when 2^k > S)
-        cuuint32_t box[5] = {(cuuint32_t)kHD, (cuuint32_t)(k < 0 ? box_s : std::min(1 << k, mem_len)), 1, 1, 1};
-        CUresult r = fn(k < 0 ? &epi.ts : &epi.ts_p2[k], CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, h->cross_kv, dims, strides, box, estr,
-                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
-                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-        if (r != CUDA_SUCCESS)
-          return fail(h, CAPDEC_ERR_CUDA, "cuTensorMapEncodeTiled (cross cache store view %d) failed (%d) S=%d images=%d", k, (int)r, mem_len, n_images);
-      }
-    }
-    epi.bias = h->b_ckv; epi.S = mem_len; epi.box = box_s; epi.img0 = img0; epi.rows = M;
+    // persistent weight-stationary GEMM (gemm_ws.cuh): 128-row tiles, per-image bulk stores straight into the cross
+    // cache layout (WsCrossKV)
+    WsCrossKV epi{(bf16*)h->cross_kv, h->b_ckv, mem_len, n_images, img0, M};
     CUtensorMap tm_x;
     TRY(make_map(h, &tm_x, (bf16*)h->mem_b + off, M, kD, 128));
     set_tag(h, "prefill_gemm_cross_kv", gemm_bytes(M, N, kD, h->esz, h->esz, h->esz));

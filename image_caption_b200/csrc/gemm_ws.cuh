@@ -114,39 +114,32 @@ struct WsQKV {
 };
 
 // Prefill: rows = (image, memory position), features = layer*1024 + kv*512 + head*64 + d; destination = the
-// cross cache [L*2][n_images][H][S][64], seen as a 5-D tensor {64, S, H, n_images, L*2}.  A tile is 128 consecutive rows,
-// staged as [head][128 rows][64]; it overlaps a few images, and each overlap (image i, positions [s_lo, s_lo + n)) is stored
-// per head with bulk tensor stores that fit it exactly: one box of min(S, 128) positions when n is that, else the binary
-// decomposition of n over the boxes of 64, 32, ... 1 positions (ts_p2[k] = box of 2^k positions).  Nothing relies on the
-// copy engine clipping a box: a store at a negative position faults on B200 (measured: illegal instruction).
+// cross cache [L*2][n_images][H][S][64].  A tile is 128 consecutive rows, staged as [head][128 rows][64]; it overlaps a few
+// images, and each overlap (image i, positions [pos, pos + n)) is, per head, n * 128 contiguous bytes both in the staged
+// plane and in the cache: one 1-D bulk store each.  (First attempt, kept as a measurement: 5-D bulk tensor stores.  A box
+// at a negative position faults on B200 - illegal instruction - so partial overlaps were decomposed into exact boxes of
+// 64, 32 ... 1 positions; ~16 small tensor stores per tile cost 137 of 470 us at 1024 x 49.)
 struct WsCrossKV {
-  alignas(64) CUtensorMap ts;
-  alignas(64) CUtensorMap ts_p2[7];
+  bf16* cache;
   const float* bias;
-  int S, box, img0, rows;  // box = min(S, 128); img0 = first image of this chunk; rows = n_chunk * S rows of X
+  int S, n_images, img0, rows;  // img0 = first image of this chunk; rows = n_chunk * S rows of X
   __device__ __forceinline__ SwapEpiPre prepare(int f) const { return SwapEpiPre{__ldg(bias + f), 0}; }
   __device__ __forceinline__ float value(float acc, const SwapEpiPre& pre) const { return acc + pre.bias; }
   __device__ __forceinline__ int row0(int tile) const { return tile * 128; }
   __device__ __forceinline__ int stage_index(int j, int fl) const { return ((fl >> 6) * 128 + j) * 64 + (fl & 63); }
-  __device__ __forceinline__ void put(const CUtensorMap* m, uint32_t src, int jrow, int pos, int head0, int img, int lk) const {
-#pragma unroll
-    for (int hh = 0; hh < 2; ++hh)
-      asm volatile("cp.async.bulk.tensor.5d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5, %6}], [%1];"
-                   ::"l"(reinterpret_cast<uint64_t>(m)), "r"(src + (uint32_t)((hh * 128 + jrow) * 128)), "r"(0), "r"(pos),
-                     "r"(head0 + hh), "r"(img), "r"(lk)
-                   : "memory");
-  }
   __device__ __forceinline__ void store(const void* stage, int f0, int tile, const SwapEpiPre&) const {
     const int lk = f0 >> 9, head0 = (f0 & (kD - 1)) >> 6;
     const int r0 = tile * 128, r1 = min(r0 + 128, rows);
     const uint32_t src = ptx::smem_u32(stage);
     for (int i = r0 / S; i * S < r1; ++i) {
       const int a = max(i * S, r0), b = min((i + 1) * S, r1);  // rows [a, b) of the tile belong to image i
-      int n = b - a, pos = a - i * S, jrow = a - r0;
-      if (n == box) { put(&ts, src, jrow, pos, head0, img0 + i, lk); continue; }
-#pragma unroll 1
-      for (int k = 6; k >= 0; --k)
-        if (n & (1 << k)) { put(&ts_p2[k], src, jrow, pos, head0, img0 + i, lk); pos += 1 << k; jrow += 1 << k; }
+      const int n = b - a, pos = a - i * S, jrow = a - r0;
+#pragma unroll
+      for (int hh = 0; hh < 2; ++hh) {
+        bf16* dst = cache + ((((size_t)lk * n_images + img0 + i) * kH + head0 + hh) * S + pos) * kHD;
+        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+                     ::"l"(dst), "r"(src + (uint32_t)((hh * 128 + jrow) * 128)), "r"(n * 128) : "memory");
+      }
     }
   }
 };
@@ -236,8 +229,11 @@ gemm_ws_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__
           if (s == stages) { s = 0; ph ^= 1u; }
           ptx::mbar_wait(&empty[s], ph ^ 1u);
           if (ptx::elect_one()) {
-            ptx::mbar_expect_tx(&full[s], kXBytes);
-            ptx::tma_load_2d(smem + (size_t)s * kXBytes, &tm_x, &full[s], kb * 64, b0);  // rows beyond the matrix arrive as zeros
+            if ((dbg & 4) && i > 0) ptx::mbar_arrive(&full[s]);  // tuning aid: no activation traffic after the first tile (wrong results)
+            else {
+              ptx::mbar_expect_tx(&full[s], kXBytes);
+              ptx::tma_load_2d(smem + (size_t)s * kXBytes, &tm_x, &full[s], kb * 64, b0);  // rows beyond the matrix arrive as zeros
+            }
           }
           __syncwarp();
         }
@@ -291,7 +287,7 @@ gemm_ws_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__
         for (int c0 = chalf * (BNB / 2); c0 < (chalf + 1) * (BNB / 2); c0 += 32) {
           float v[32];
           ptx::tmem_ld32(t_lane + (uint32_t)(buf * BNB + c0), v);
-          if (!(dbg & 1)) {
+          if (!(dbg & 17)) {
 #pragma unroll
             for (int j = 0; j < 32; ++j) {
               const int at = epi.stage_index(c0 + j, fl);  // where (row j of the tile, feature fl) sits in the staged box
@@ -304,7 +300,7 @@ gemm_ws_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__
         if (lane == 0) ptx::mbar_arrive(&acc_empty[buf]);  // the accumulator may be overwritten
         ptx::fence_proxy_async();
         ptx::bar_sync(1, kWsEpi);
-        if (issuer && !(dbg & 1)) {  // rows >= M are clipped by the store maps
+        if (issuer && !(dbg & 9)) {  // rows >= M are clipped by the store maps
           epi.store(stage, f0, tile, pre);
           ptx::bulk_commit();
         }
