@@ -22,6 +22,7 @@ EXPORTS = (
     "capdec_prefill", "capdec_decode", "capdec_generate_host", "capdec_sample_logits", "capdec_launch_count",
     "capdec_debug_gemm", "capdec_debug_cross_kv", "capdec_profile_enable", "capdec_profile_report",
     "capdec_beam_search", "capdec_set_memory_projection", "capdec_prefill_tokens", "capdec_gemm_static", "capdec_cider_d",
+    "capdec_forward_full",
 )
 
 
@@ -65,6 +66,11 @@ class BeamArgs(C.Structure):
                 ("score_out", _fp), ("steps_out", C.POINTER(C.c_int32))]
 
 
+class ForwardArgs(C.Structure):
+    _fields_ = [("group", C.c_int32), ("max_len", C.c_int32), ("end_token", C.c_int32), ("reserved", C.c_int32),
+                ("ids", _fp), ("logp_out", _fp), ("logits_out", _fp)]
+
+
 class CiderArgs(C.Structure):
     _fields_ = [("hyp_ids", _fp), ("ref_ids", _fp), ("ref_offsets", C.POINTER(C.c_int32)),
                 ("n_images", C.c_int32), ("group", C.c_int32), ("hyp_len", C.c_int32), ("n_refs", C.c_int32),
@@ -106,6 +112,8 @@ def load() -> C.CDLL:
         lib.capdec_set_memory_projection.argtypes = [H, C.c_void_p, C.c_void_p, C.c_int32, C.POINTER(C.c_void_p),
                                                      C.POINTER(C.c_void_p), C.c_void_p]
         lib.capdec_prefill_tokens.argtypes = [H, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_void_p]
+    if hasattr(lib, "capdec_forward_full"):
+        lib.capdec_forward_full.argtypes = [H, C.POINTER(ForwardArgs), C.c_void_p]
     lib.capdec_launch_count.restype = C.c_int64
     lib.capdec_launch_count.argtypes = [H]
     lib.capdec_debug_gemm.argtypes = [H, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32,

@@ -20,6 +20,8 @@
 #include "pointwise.cuh"
 #include "layer_chain.cuh"
 #include "cider.cuh"
+#include "attention_dense.cuh"
+#include "full_pass.cuh"
 
 using namespace capdec;
 
@@ -408,6 +410,9 @@ static cudaError_t configure_fast_kernels() {
   if (e == cudaSuccess) e = configure_ws_epi<WsLinear<true>>();
   if (e == cudaSuccess) e = configure_ws_epi<WsQKV>();
   if (e == cudaSuccess) e = configure_ws_epi<WsCrossKV>();
+  if (e == cudaSuccess) e = configure_ws_epi<WsQKVFull>();
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(dense_attn_kernel<26>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dense_attn_smem(26));
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(dense_attn_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dense_attn_smem(32));
   if (e == cudaSuccess) e = configure_swap_ln_ks<32, 2>();
   if (e == cudaSuccess) e = configure_swap_ln_ks<64, 2>();
   if (e == cudaSuccess) e = configure_swap_ln_ks<128, 2>();
@@ -1490,6 +1495,161 @@ extern "C" int capdec_decode(capdec_handle h, const capdec_decode_args* a, void*
     *a->steps_out = steps;
   }
   return CAPDEC_OK;
+}
+
+// ------------------------------------------------------------------ full-sequence teacher-forced pass
+// The step kernels' activation buffers and tensor maps live in the handle; the full pass runs the same GEMM launchers over
+// (sequences x positions) rows, so it swaps its own workspace in for the duration of the call and puts the step state back.
+namespace {
+struct ActState {
+  float *x, *logits;
+  void *xb, *q, *a, *hbuf;
+  int maps_for_m, bnb, ln_tma_store;
+  bool chain, chain_now;
+  CUtensorMap tm_xb, tm_a, tm_h, ts_q, ts_h, ts_x, ts_xb, tx_ws, tc_xb, tc_a;
+  ActMaps tx_xb, tx_a, tx_h;
+};
+void save_act(capdec_handle h, ActState* o) {
+  o->x = h->x; o->logits = h->logits; o->xb = h->xb; o->q = h->q; o->a = h->a; o->hbuf = h->hbuf;
+  o->maps_for_m = h->maps_for_m; o->bnb = h->bnb; o->ln_tma_store = h->ln_tma_store; o->chain = h->chain; o->chain_now = h->chain_now;
+  o->tm_xb = h->tm_xb; o->tm_a = h->tm_a; o->tm_h = h->tm_h; o->ts_q = h->ts_q; o->ts_h = h->ts_h; o->ts_x = h->ts_x;
+  o->ts_xb = h->ts_xb; o->tx_ws = h->tx_ws; o->tc_xb = h->tc_xb; o->tc_a = h->tc_a; o->tx_xb = h->tx_xb; o->tx_a = h->tx_a; o->tx_h = h->tx_h;
+}
+void restore_act(capdec_handle h, const ActState& o) {
+  h->x = o.x; h->logits = o.logits; h->xb = o.xb; h->q = o.q; h->a = o.a; h->hbuf = o.hbuf;
+  h->maps_for_m = o.maps_for_m; h->bnb = o.bnb; h->ln_tma_store = o.ln_tma_store; h->chain = o.chain; h->chain_now = o.chain_now;
+  h->tm_xb = o.tm_xb; h->tm_a = o.tm_a; h->tm_h = o.tm_h; h->ts_q = o.ts_q; h->ts_h = o.ts_h; h->ts_x = o.ts_x;
+  h->ts_xb = o.ts_xb; h->tx_ws = o.tx_ws; h->tc_xb = o.tc_xb; h->tc_a = o.tc_a; h->tx_xb = o.tx_xb; h->tx_a = o.tx_a; h->tx_h = o.tx_h;
+}
+}  // namespace
+
+static int ensure_full_workspace(capdec_handle h) {
+  if (h->full_x) return 0;
+  size_t cap = 65536;  // rows (sequence positions) per chunk of images: 9.7 KB of workspace each
+  if (const char* e = getenv("CAPDEC_FULL_ROWS")) cap = (size_t)std::max(256, atoi(e));
+  TRY(dev_alloc(h, &h->full_x, cap * kD));
+  TRY(dev_alloc(h, &h->full_logits, cap * kVPad));
+  TRY(dev_alloc_bytes(h, &h->full_xb, cap * kD * 2));
+  TRY(dev_alloc_bytes(h, &h->full_q, cap * kD * 2));
+  TRY(dev_alloc_bytes(h, &h->full_a, cap * kD * 2));
+  TRY(dev_alloc_bytes(h, &h->full_h, cap * (size_t)h->cfg.d_ff * 2));
+  h->full_rows_cap = cap;
+  return 0;
+}
+
+static int launch_dense_attn(capdec_handle h, cudaStream_t s, const DenseAttnArgs& A, int units, const char* tag, double bytes) {
+  set_tag(h, tag, bytes);
+  ProfScope ps(h, s);
+  const dim3 grid(units, kH), block(kAdWarps * 32);
+  if (A.nk <= 64) dense_attn_kernel<8><<<grid, block, dense_attn_smem(8), s>>>(A);
+  else if (A.nk <= 128) dense_attn_kernel<16><<<grid, block, dense_attn_smem(16), s>>>(A);
+  else if (A.nk <= 208) dense_attn_kernel<26><<<grid, block, dense_attn_smem(26), s>>>(A);
+  else dense_attn_kernel<32><<<grid, block, dense_attn_smem(32), s>>>(A);
+  CUDA_TRY(h, cudaGetLastError());
+  h->launches_this_enqueue++;
+  return 0;
+}
+
+// One chunk of images [img0, img0 + nc): every decoder layer over Mc = nc * group * T rows, then the vocabulary head.
+static int full_pass_chunk(capdec_handle h, cudaStream_t s, const capdec_forward_args* a, int img0, int nc) {
+  const int G = a->group, T = a->max_len - 1, S = h->mem_len, n_images = h->n_images, L = h->cfg.n_layer, F = h->cfg.d_ff;
+  const int seq0 = img0 * G, n_seq = nc * G, Mc = n_seq * T;
+  h->maps_for_m = -1;
+  TRY(ensure_activation_maps(h, Mc));
+  // the weight-stationary GEMM's views, for any Mc (the step path builds them from 512 rows up)
+  TRY(make_store_map(h, &h->ts_q, h->q, Mc, kD, 128, false));
+  TRY(make_store_map(h, &h->ts_h, h->hbuf, Mc, F, 128, false));
+  TRY(make_map(h, &h->tx_ws, h->xb, Mc, kD, 128));
+  const SwapLNParams no_ln{};
+  (void)no_ln;
+  {
+    set_tag(h, "full_embed", (double)Mc * kD * (4 + 4 + 4 + 2));
+    ProfScope ps(h, s);
+    const size_t n4 = (size_t)Mc * (kD / 4);
+    embed_full_kernel<<<(unsigned)((n4 + 255) / 256), 256, 0, s>>>((const long long*)a->ids, a->max_len, h->cfg.vocab, seq0, n_seq, T,
+                                                                 h->emb, h->pe, h->x, (bf16*)h->xb);
+    CUDA_TRY(h, cudaGetLastError());
+    h->launches_this_enqueue++;
+  }
+  const double ln_extra = (double)Mc * kD * (4 + 4 + 2);
+  const size_t plane = (size_t)n_images * kH * S * kHD;
+  for (int l = 0; l < L; ++l) {
+    LayerParams& lp = h->layer[l];
+    bf16* kc = (bf16*)h->self_k + (size_t)l * h->self_layer_elems;
+    bf16* vc = (bf16*)h->self_v + (size_t)l * h->self_layer_elems;
+    {  // self-attention block
+      WsQKVFull eq{};
+      eq.ts_q = h->ts_q; eq.kc = kc; eq.vc = vc; eq.bias = lp.b_qkv; eq.T = T; eq.t_pad = h->t_pad; eq.seq0 = seq0; eq.rows = Mc;
+      set_tag(h, "full_gemm_qkv", gemm_bytes(Mc, 3 * kD, kD, 2, 2, 2));
+      TRY(launch_ws(h, s, lp.m_qkv, h->tx_ws, Mc, 3 * kD, eq, nullptr));
+      DenseAttnArgs A{(const bf16*)h->q, (bf16*)h->a, kc, vc, (long long)h->t_pad * kHD, kD, kD, seq0, T, T, T};
+      TRY(launch_dense_attn(h, s, A, n_seq, "full_self_attn", (double)Mc * kD * 2 * 4));
+      SwapLNParams ln{h->x, (bf16*)h->xb, lp.b_so, lp.ln_w[0], lp.ln_b[0], h->ts_x, h->ts_xb, h->ln_tma_store};
+      set_tag(h, "full_gemm_self_out_ln", gemm_bytes(Mc, kD, kD, 2, 2, 0) + ln_extra);
+      TRY((launch_swap<true>(h, s, lp.m_so, h->tx_a, Mc, kD, kD, SwapNoLN{}, ln, nullptr)));
+    }
+    {  // cross-attention block
+      set_tag(h, "full_gemm_cross_q", gemm_bytes(Mc, kD, kD, 2, 2, 2));
+      TRY(launch_ws(h, s, lp.m_cq, h->tx_ws, Mc, kD, WsLinear<false>{h->ts_q, lp.b_cq}, nullptr));
+      const bf16* ck = (const bf16*)h->cross_kv + (size_t)(2 * l) * plane;
+      DenseAttnArgs A{(const bf16*)h->q, (bf16*)h->a, ck, ck + plane, (long long)S * kHD, kD, kD, img0, G * T, S, 0};
+      TRY(launch_dense_attn(h, s, A, nc, "full_cross_attn", (double)nc * S * 2 * kD * 2 + (double)Mc * kD * 2 * 2));
+      SwapLNParams ln{h->x, (bf16*)h->xb, lp.b_co, lp.ln_w[1], lp.ln_b[1], h->ts_x, h->ts_xb, h->ln_tma_store};
+      set_tag(h, "full_gemm_cross_out_ln", gemm_bytes(Mc, kD, kD, 2, 2, 0) + ln_extra);
+      TRY((launch_swap<true>(h, s, lp.m_co, h->tx_a, Mc, kD, kD, SwapNoLN{}, ln, nullptr)));
+    }
+    {  // feed-forward block
+      set_tag(h, "full_gemm_ffn1", gemm_bytes(Mc, F, kD, 2, 2, 2));
+      TRY(launch_ws(h, s, lp.m_1, h->tx_ws, Mc, F, WsLinear<true>{h->ts_h, lp.b_1}, nullptr));
+      SwapLNParams ln{h->x, (bf16*)h->xb, lp.b_2, lp.ln_w[2], lp.ln_b[2], h->ts_x, h->ts_xb, h->ln_tma_store};
+      set_tag(h, "full_gemm_ffn2_ln", gemm_bytes(Mc, kD, F, 2, 2, 0) + ln_extra);
+      TRY((launch_swap<true>(h, s, lp.m_2, h->tx_h, Mc, kD, F, SwapNoLN{}, ln, nullptr)));
+    }
+  }
+  // vocabulary head on the fp32 residual stream (as the step head), then log-softmax + gather
+  EpiLinear<float, false> ev{h->logits, h->fc_b, kVPad};
+  set_tag(h, "full_gemm_vocab", gemm_bytes(Mc, kVPad, kD, 4, 4, 4));
+  TRY((launch_simt<float, float, EpiLinear<float, false>>(h, s, h->x, kD, h->fc_w, kD, Mc, kVPad, kD, ev, nullptr)));
+  {
+    set_tag(h, "full_logp", (double)Mc * (kVPad * 4 + 8 + 4) + (a->logits_out ? (double)Mc * h->cfg.vocab * 4 : 0.0));
+    ProfScope ps(h, s);
+    logp_full_kernel<<<(Mc + 3) / 4, 128, 0, s>>>(h->logits, (const long long*)a->ids, a->max_len, h->cfg.vocab, seq0, n_seq, T,
+                                                  a->end_token, a->logp_out, a->logits_out);
+    CUDA_TRY(h, cudaGetLastError());
+    h->launches_this_enqueue++;
+  }
+  return 0;
+}
+
+extern "C" int capdec_forward_full(capdec_handle h, const capdec_forward_args* a, void* stream) {
+  if (!h || !a || !a->ids) return fail(h, CAPDEC_ERR_INVALID, "null argument");
+  if (!a->logp_out && !a->logits_out) return fail(h, CAPDEC_ERR_INVALID, "neither logp_out nor logits_out given");
+  if (!h->prefilled) return fail(h, CAPDEC_ERR_STATE, "capdec_forward_full before capdec_prefill");
+  if (!h->fast) return fail(h, CAPDEC_ERR_STATE, "the full-sequence pass needs the bf16 tcgen05 engine (CAPDEC_PRECISION_BF16 on sm_100, v2 step)");
+  if (h->cfg.d_ff % 128 != 0) return fail(h, CAPDEC_ERR_STATE, "the full-sequence pass needs d_ff %% 128 == 0 (have %d)", h->cfg.d_ff);
+  if (a->group < 1 || a->group > h->cfg.max_group) return fail(h, CAPDEC_ERR_CAPACITY, "group %d outside [1,%d]", a->group, h->cfg.max_group);
+  if (a->max_len < 2 || a->max_len > h->cfg.max_len) return fail(h, CAPDEC_ERR_CAPACITY, "max_len %d outside [2,%d]", a->max_len, h->cfg.max_len);
+  const int T = a->max_len - 1;
+  if (T > h->cfg.pe_rows) return fail(h, CAPDEC_ERR_INVALID, "max_len %d needs %d positional rows, table has %d", a->max_len, T, h->cfg.pe_rows);
+  if (T > h->t_pad || T > 256) return fail(h, CAPDEC_ERR_CAPACITY, "%d positions exceed the self cache (%d) or the attention kernel (256)", T, h->t_pad);
+  if (h->mem_len > 256) return fail(h, CAPDEC_ERR_CAPACITY, "memory length %d > 256", h->mem_len);
+  if (a->end_token < 0 || a->end_token >= h->cfg.vocab) return fail(h, CAPDEC_ERR_INVALID, "end token outside the vocabulary");
+  cudaStream_t s = (cudaStream_t)stream;
+  CUDA_TRY(h, cudaSetDevice(h->device));
+  TRY(ensure_full_workspace(h));
+  const size_t per_image = (size_t)a->group * T;
+  if (per_image > h->full_rows_cap) return fail(h, CAPDEC_ERR_CAPACITY, "group * positions = %zu exceeds the workspace (%zu rows; CAPDEC_FULL_ROWS)", per_image, h->full_rows_cap);
+  const int chunk = (int)std::min<size_t>((size_t)h->n_images, h->full_rows_cap / per_image);
+  ActState saved;
+  save_act(h, &saved);
+  h->x = h->full_x; h->logits = h->full_logits; h->xb = h->full_xb; h->q = h->full_q; h->a = h->full_a; h->hbuf = h->full_h;
+  h->chain = false;
+  h->launches_this_enqueue = 0;
+  int rc = 0;
+  for (int i0 = 0; i0 < h->n_images && rc == 0; i0 += chunk) rc = full_pass_chunk(h, s, a, i0, std::min(chunk, h->n_images - i0));
+  restore_act(h, saved);
+  h->launches += h->launches_this_enqueue;
+  return rc;
 }
 
 // ------------------------------------------------------------------ beam search (beam.cuh)

@@ -125,6 +125,11 @@ struct capdec_engine {
   float* chain_part = nullptr;     // [row tiles][CS][BNB][512] fp32 linear2 partial products
   CUtensorMap tc_xb, tc_a;         // [64, M, 8] views of xb / a, box = 64 x chain_bnb x 8
 
+  // ---- full-sequence teacher-forced pass (capdec_forward_full): its own activation workspace, allocated on first use
+  float *full_x = nullptr, *full_logits = nullptr;
+  void *full_xb = nullptr, *full_q = nullptr, *full_a = nullptr, *full_h = nullptr;
+  size_t full_rows_cap = 0;        // rows (sequence positions) per chunk of images (env CAPDEC_FULL_ROWS, default 65536)
+
   // ---- CIDEr-D reward workspace (cider.cuh), grown on demand
   unsigned long long* cider_keys = nullptr;
   unsigned int* cider_cnt = nullptr;

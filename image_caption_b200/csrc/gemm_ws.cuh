@@ -90,7 +90,7 @@ struct WsLinear {
     return kRelu ? fmaxf(r, 0.f) : r;
   }
   __device__ __forceinline__ int row0(int tile) const { return tile * 128; }
-  __device__ __forceinline__ int stage_index(int j, int fl) const { return j * kSwapBF + fl; }  // row-major [128 rows][128 features]
+  __device__ __forceinline__ int stage_index(int j, int fl, int) const { return j * kSwapBF + fl; }  // row-major [128 rows][128 features]
   __device__ __forceinline__ void store(const void* stage, int f0, int tile, const SwapEpiPre&) const { ptx::tma_store_2d(&ts, stage, f0, tile * 128); }
 };
 // self-attention in_proj: features [0,512) -> q, [512,1024) -> K cache position st->step, [1024,1536) -> V cache.
@@ -104,7 +104,7 @@ struct WsQKV {
   __device__ __forceinline__ SwapEpiPre prepare(int f) const { return SwapEpiPre{__ldg(bias + f), st->step}; }
   __device__ __forceinline__ float value(float acc, const SwapEpiPre& pre) const { return acc + pre.bias; }
   __device__ __forceinline__ int row0(int tile) const { return tile * 128; }
-  __device__ __forceinline__ int stage_index(int j, int fl) const { return j * kSwapBF + fl; }
+  __device__ __forceinline__ int stage_index(int j, int fl, int) const { return j * kSwapBF + fl; }
   __device__ __forceinline__ void store(const void* stage, int f0, int tile, const SwapEpiPre& pre) const {
     const int b0 = tile * 128;
     const int which = f0 >> 9, c = f0 & (kD - 1);
@@ -126,7 +126,7 @@ struct WsCrossKV {
   __device__ __forceinline__ SwapEpiPre prepare(int f) const { return SwapEpiPre{__ldg(bias + f), 0}; }
   __device__ __forceinline__ float value(float acc, const SwapEpiPre& pre) const { return acc + pre.bias; }
   __device__ __forceinline__ int row0(int tile) const { return tile * 128; }
-  __device__ __forceinline__ int stage_index(int j, int fl) const { return ((fl >> 6) * 128 + j) * 64 + (fl & 63); }
+  __device__ __forceinline__ int stage_index(int j, int fl, int) const { return ((fl >> 6) * 128 + j) * 64 + (fl & 63); }
   __device__ __forceinline__ void store(const void* stage, int f0, int tile, const SwapEpiPre&) const {
     const int lk = f0 >> 9, head0 = (f0 & (kD - 1)) >> 6;
     const int r0 = tile * 128, r1 = min(r0 + 128, rows);
@@ -137,6 +137,42 @@ struct WsCrossKV {
 #pragma unroll
       for (int hh = 0; hh < 2; ++hh) {
         bf16* dst = cache + ((((size_t)lk * n_images + img0 + i) * kH + head0 + hh) * S + pos) * kHD;
+        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+                     ::"l"(dst), "r"(src + (uint32_t)((hh * 128 + jrow) * 128)), "r"(n * 128) : "memory");
+      }
+    }
+  }
+};
+
+// Full-sequence pass, self-attention in_proj over rows = (sequence, position), sequence-major: features
+// [0,512) -> q [rows,512] (2-D tensor store); [512,1024) / [1024,1536) -> this layer's self K / V cache
+// [cache rows][H][t_pad][64] at (seq0 + sequence, head, position): like the prefill, each overlap of the tile with a
+// sequence is n * 128 contiguous bytes per head on both sides, one 1-D bulk store each.
+struct WsQKVFull {
+  alignas(64) CUtensorMap ts_q;
+  bf16* kc;
+  bf16* vc;
+  const float* bias;
+  int T, t_pad, seq0, rows;  // T positions per sequence; rows = sequences * T
+  __device__ __forceinline__ SwapEpiPre prepare(int f) const { return SwapEpiPre{__ldg(bias + f), 0}; }
+  __device__ __forceinline__ float value(float acc, const SwapEpiPre& pre) const { return acc + pre.bias; }
+  __device__ __forceinline__ int row0(int tile) const { return tile * 128; }
+  __device__ __forceinline__ int stage_index(int j, int fl, int f0) const {
+    return f0 < kD ? j * kSwapBF + fl : ((fl >> 6) * 128 + j) * 64 + (fl & 63);
+  }
+  __device__ __forceinline__ void store(const void* stage, int f0, int tile, const SwapEpiPre&) const {
+    const int which = f0 >> 9, c = f0 & (kD - 1);
+    if (which == 0) { ptx::tma_store_2d(&ts_q, stage, c, tile * 128); return; }
+    bf16* cache = which == 1 ? kc : vc;
+    const int head0 = c >> 6;
+    const int r0 = tile * 128, r1 = min(r0 + 128, rows);
+    const uint32_t src = ptx::smem_u32(stage);
+    for (int i = r0 / T; i * T < r1; ++i) {
+      const int a = max(i * T, r0), b = min((i + 1) * T, r1);  // rows [a, b) of the tile belong to sequence i
+      const int n = b - a, pos = a - i * T, jrow = a - r0;
+#pragma unroll
+      for (int hh = 0; hh < 2; ++hh) {
+        bf16* dst = cache + (((size_t)(seq0 + i) * kH + head0 + hh) * t_pad + pos) * kHD;
         asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
                      ::"l"(dst), "r"(src + (uint32_t)((hh * 128 + jrow) * 128)), "r"(n * 128) : "memory");
       }
@@ -290,7 +326,7 @@ gemm_ws_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__
           if (!(dbg & 17)) {
 #pragma unroll
             for (int j = 0; j < 32; ++j) {
-              const int at = epi.stage_index(c0 + j, fl);  // where (row j of the tile, feature fl) sits in the staged box
+              const int at = epi.stage_index(c0 + j, fl, f0);  // where (row j of the tile, feature fl) sits in the staged box
               if (at >= 0) stage[at] = __float2bfloat16_rn(epi.value(v[j], pre));
             }
           }

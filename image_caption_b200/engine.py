@@ -266,12 +266,19 @@ class CaptionDecodeEngine:
         return Rollout(ids=ids, logp=logp, steps=n, logits=logits)
 
     def score(self, memory: torch.Tensor, ids: torch.Tensor, end_token: int, group: int = 1,
-              return_logits: bool = True, pad_token: int = 0):
+              return_logits: bool = True, pad_token: int = 0, mode: str = "steps"):
         """Teacher-forced pass over given sequences (CAPDEC_DECODE_TEACHER_FORCED): ``ids`` (B*group, L) int64 with
         column 0 = <start>; returns ``(logits (M, L-1, V) or None, logp (M, L-1))`` where ``logits[:, k]`` is what the
         reference's ``model.decoder(ids[:, :k+1], memory, tgt_mask=causal)[:, -1]`` returns (scst:223-226, vit:312-315)
         and ``logp[:, k] = log_softmax(logits[:, k])[ids[:, k+1]]``, zero after a row's <end> (scst:236-239).
-        Inference only: no autograd graph is built."""
+        Inference only: no autograd graph is built.
+
+        ``mode="steps"`` replays the L-1 decode steps with forced tokens (any engine).  ``mode="full"`` is the
+        full-sequence pass (capdec_forward_full): the whole-caption decoder call of the training forward
+        (vit:216-255) as ONE pass over (sequences x positions) rows - every projection a single large tcgen05 GEMM, K/V
+        read once per sequence instead of once per step; bf16 tensor-core engine only (CapdecError otherwise)."""
+        if mode not in ("steps", "full"):
+            raise ValueError(f"mode must be 'steps' or 'full', got {mode!r}")
         if memory.dim() != 3 or memory.shape[2] != self.d_model or not memory.is_cuda:
             raise ValueError(f"memory must be CUDA (B, S, {self.d_model}), got {tuple(memory.shape)}")
         n_images, mem_len = memory.shape[0], memory.shape[1]
@@ -297,18 +304,25 @@ class CaptionDecodeEngine:
         args.logits_out = logits.data_ptr() if return_logits else None
         stream = _stream_ptr(self.device)
         _lib.check(self._h, self._lib.capdec_prefill(self._h, memory.data_ptr(), n_images, mem_len, stream))
-        _lib.check(self._h, self._lib.capdec_decode(self._h, C.byref(args), stream))
+        if mode == "full":
+            fa = _lib.ForwardArgs(group=group, max_len=max_len, end_token=end_token)
+            fa.ids = ids.data_ptr()
+            fa.logp_out = logp.data_ptr()
+            fa.logits_out = logits.data_ptr() if return_logits else None
+            _lib.check(self._h, self._lib.capdec_forward_full(self._h, C.byref(fa), stream))
+        else:
+            _lib.check(self._h, self._lib.capdec_decode(self._h, C.byref(args), stream))
         self._keep_ids = ids
         return logits, logp
 
     @torch.no_grad()
-    def decoder_forward(self, tgt: torch.Tensor, memory: torch.Tensor) -> torch.Tensor:
+    def decoder_forward(self, tgt: torch.Tensor, memory: torch.Tensor, mode: str = "steps") -> torch.Tensor:
         """``model.decoder(tgt, memory, tgt_mask=causal)`` (vit:155-182 as called at vit:312 / scst:223) on the
         engine: (B, t) token ids -> (B, t, V) logits.  Causal mask only (the hot path's call shape); no autograd."""
         b, t = tgt.shape
         ids = torch.cat([tgt.to(self.device, torch.int64),
                          torch.zeros((b, 1), dtype=torch.int64, device=self.device)], dim=1)  # step t-1 scores a dummy token
-        logits, _ = self.score(memory, ids, end_token=0)  # the end token only shapes the (discarded) log-probs
+        logits, _ = self.score(memory, ids, end_token=0, mode=mode)  # the end token only shapes the (discarded) log-probs
         return logits
 
     def beam_search_from_memory(self, memory: torch.Tensor, start_token: int, end_token: int, max_len: int = 50,

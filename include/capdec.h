@@ -215,6 +215,30 @@ int64_t capdec_launch_count(capdec_handle h);
 int capdec_profile_enable(capdec_handle h, int32_t on);
 int capdec_profile_report(capdec_handle h, char* buf, int32_t buf_len);
 
+/* ---- Full-sequence teacher-forced pass (forward only).
+ * Replaces the reference's whole-caption decoder call `self.decoder(captions[:, :-1], memory, tgt_mask=causal)`
+ * (models/vit_transformer_model.py:216-255 training forward; utils/scst_loss.py:223-226 is the same call on a growing
+ * prefix) plus `log_softmax(...).gather(...)` with finished rows zeroed (utils/scst_loss.py:226-239), for GIVEN token
+ * sequences: one pass over (sequences x positions) rows instead of max_len-1 decode steps.  Same results as
+ * capdec_decode with CAPDEC_DECODE_TEACHER_FORCED (same weights, caches and head arithmetic; the attention and GEMM
+ * summation orders differ, so logits agree to the bf16 tolerance, not bit for bit).  Needs capdec_prefill first and a bf16
+ * tcgen05 engine (CAPDEC_ERR_STATE otherwise: there is no fallback).  Leaves the self K/V cache holding positions
+ * [0, max_len-1) of every sequence.  Images are processed in chunks of <= CAPDEC_FULL_ROWS (default 65536) rows.
+ *   ids        DEVICE int64 [n_images*group, max_len], column 0 = <start> (values outside the vocabulary are clamped)
+ *   logp_out   DEVICE fp32 [n_images*group, max_len-1] or NULL: log p(ids[:, k+1] | ids[:, :k+1]), 0 once a row's
+ *              ids[:, 1..k] contains end_token
+ *   logits_out DEVICE fp32 [n_images*group, max_len-1, vocab] or NULL                                             */
+typedef struct capdec_forward_args {
+  int32_t group;
+  int32_t max_len;
+  int32_t end_token;
+  int32_t reserved;
+  const int64_t* ids;
+  float* logp_out;
+  float* logits_out;
+} capdec_forward_args;
+int capdec_forward_full(capdec_handle h, const capdec_forward_args* a, void* cuda_stream);
+
 /* ---- diagnostics (used by the parity tests; not part of the reference-facing surface) ---- */
 
 /* C[M,N] = A[M,K] * W[N,K]^T + bias through the engine's GEMM of the handle's precision

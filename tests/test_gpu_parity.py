@@ -760,6 +760,90 @@ def test_teacher_forced_grouped_and_v1(dev):
         eng.close()
 
 
+# ---------------------------------------------------------------- full-sequence pass (capdec_forward_full)
+def test_full_sequence_pass_against_the_reference(dev, golden_case):
+    """engine.score(mode="full") / decoder_forward(mode="full") against outputs of the REAL reference (tests/golden): the
+    whole-caption decoder call `model.decoder(tgt, memory, tgt_mask)` (vit:216-255 / scst:223) in ONE pass over
+    (sequences x positions) rows, its log-probs with finished rows zeroed (scst:236-239), and the step replay of the same
+    sequences (same weights and head arithmetic, different summation order)."""
+    name, z, dec, mem = golden_case
+    max_len = int(z["max_len"])
+    tol = TOL["bf16"]
+    eng = make_engine(dec.to(dev), "bf16", max_images=8, max_mem=int(z["mem_len"]), max_len=max_len)
+    tf_ids = torch.from_numpy(z["tf_ids"]).to(dev)
+    logits, _ = eng.score(mem.to(dev), tf_ids, END, mode="full")
+    err = np.abs(logits.cpu().numpy() - z["tf_logits"]).max()
+    _record(tol, err)
+    assert err < tol
+    fwd = eng.decoder_forward(tf_ids[:, :-1], mem.to(dev), mode="full")
+    assert fwd.shape == (tf_ids.shape[0], max_len - 1, VOCAB) and torch.equal(fwd, logits)
+    s_ids = torch.from_numpy(z["sample_ids"]).to(dev)
+    logits, logp = eng.score(mem.to(dev), s_ids, END, mode="full")
+    assert np.abs(logits.cpu().numpy() - z["sample_logits"]).max() < tol
+    assert np.abs(logp.cpu().numpy() - z["sample_logp"]).max() < tol
+    assert ((z["sample_logp"] == 0.0) == (logp.cpu().numpy() == 0.0)).all()  # finished rows: exactly zero (scst:239)
+    logits_s, logp_s = eng.score(mem.to(dev), s_ids, END, mode="steps")
+    assert (logits - logits_s).abs().max() < tol and (logp - logp_s).abs().max() < tol
+    assert torch.equal(logp == 0.0, logp_s == 0.0)
+    # the step state is put back: an ordinary rollout afterwards equals one from a fresh engine
+    out = eng.decode_from_memory(mem.to(dev), START, END, max_len=max_len)
+    eng.close()
+    eng2 = make_engine(dec.to(dev), "bf16", max_images=8, max_mem=int(z["mem_len"]), max_len=max_len)
+    out2 = eng2.decode_from_memory(mem.to(dev), START, END, max_len=max_len)
+    assert torch.equal(out.ids, out2.ids)
+    eng2.close()
+
+
+@pytest.mark.parametrize("n_img,mem_len,group,max_len", [(3, 49, 1, 12), (4, 196, 6, 24), (5, 100, 2, 20), (1, 7, 1, 3),
+                                                         (2, 130, 3, 9), (40, 49, 5, 24)])
+def test_full_sequence_pass_shapes(dev, n_img, mem_len, group, max_len):
+    """The full pass over several (images, memory length, rollouts, length) shapes against the oracle: tiles that straddle
+    sequences and images (T = 11, 23, 19, 2, 8 positions against 128-row tiles), every key-tile width of the dense
+    attention (49 / 100 / 130 / 196 keys), a ragged last tile, more rows than one CTA group."""
+    dec = small_decoder(layers=2, pe_rows=max_len)
+    w = torch_port.weights_to_numpy(dec)
+    mem = torch_port.synthetic_memory(n_img, mem_len)
+    g = torch.Generator().manual_seed(3)
+    ids = torch.randint(0, VOCAB, (n_img * group, max_len), generator=g)
+    ids[:, 0] = START
+    ref = decoder_np.decoder_forward(w, ids[:, :-1].numpy(), np.repeat(mem.numpy(), group, 0))
+    eng = make_engine(dec.to(dev), "bf16", max_images=n_img, max_group=group, max_mem=mem_len, max_len=max_len)
+    logits, logp = eng.score(mem.to(dev), ids.to(dev), END, group=group, mode="full")
+    err = np.abs(logits.cpu().numpy() - ref).max()
+    _record(TOL["bf16"], err)
+    assert err < TOL["bf16"]
+    lsm = torch.log_softmax(logits, -1).gather(2, ids.to(dev)[:, 1:, None]).squeeze(2)
+    ended = ids[:, 1:] == END
+    before = ((ended.cumsum(1) - ended.long()) > 0).to(dev)
+    assert (logp - lsm.masked_fill(before, 0.0)).abs().max() < 1e-4
+    assert bool((logp[before] == 0.0).all())
+    _, logp_only = eng.score(mem.to(dev), ids.to(dev), END, group=group, return_logits=False, mode="full")
+    assert torch.equal(logp_only, logp)
+    eng.close()
+
+
+def test_full_sequence_pass_chunks_and_limits(dev, monkeypatch):
+    """Image chunks (CAPDEC_FULL_ROWS) change nothing: every row's arithmetic is the same whatever chunk it is in.  No
+    fallback: an fp32 engine refuses the call."""
+    from image_caption_b200._lib import CapdecError
+    dec = small_decoder(layers=2, pe_rows=16)
+    mem = torch_port.synthetic_memory(12, 49)
+    g = torch.Generator().manual_seed(4)
+    ids = torch.randint(0, VOCAB, (36, 14), generator=g)
+    ids[:, 0] = START
+    outs = []
+    for cap in ("65536", "256"):  # 256 rows = 6 images of 3 x 13 rows per chunk
+        monkeypatch.setenv("CAPDEC_FULL_ROWS", cap)
+        eng = make_engine(dec.to(dev), "bf16", max_images=12, max_group=3, max_mem=49, max_len=14)
+        outs.append(eng.score(mem.to(dev), ids.to(dev), END, group=3, mode="full"))
+        eng.close()
+    assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
+    eng = make_engine(dec.to(dev), "fp32", max_images=12, max_group=3, max_mem=49, max_len=14)
+    with pytest.raises(CapdecError):
+        eng.score(mem.to(dev), ids.to(dev), END, group=3, mode="full")
+    eng.close()
+
+
 # ---------------------------------------------------------------- BASELINE.json sizes: size-independent properties
 FULL_SIZE = {  # images, memory length, rollouts per image, sampled rollouts, max_len (bench.py WORKLOADS)
     "cfg2": (256, 49, 1, 0, 50),
