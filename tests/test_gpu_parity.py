@@ -844,6 +844,37 @@ def test_full_sequence_pass_chunks_and_limits(dev, monkeypatch):
     eng.close()
 
 
+@pytest.mark.parametrize("mode", ["rollout", "full"])
+def test_many_row_tiles(dev, mode):
+    """More than two waves of LayerNorm-GEMM CTAs (98 row tiles of 128 = 392 CTAs on 148 SMs): 12 544 rows, as a decode
+    batch and as the rows of a full-sequence pass.  Regression for a launch failure of that kernel at odd ring depths
+    (capdec.cu swap_stages)."""
+    dec = small_decoder(layers=2, pe_rows=52)
+    w = torch_port.weights_to_numpy(dec)
+    if mode == "rollout":
+        n_img, mem_len, max_len = 12544, 7, 4
+    else:
+        n_img, mem_len, max_len = 256, 49, 50
+    mem = torch_port.synthetic_memory(n_img, mem_len)
+    eng = make_engine(dec.to(dev), "bf16", max_images=n_img, max_group=1, max_mem=mem_len, max_len=max_len)
+    sel = np.linspace(0, n_img - 1, 12).astype(np.int64)
+    if mode == "rollout":
+        out = eng.decode_from_memory(mem.to(dev), START, END, max_len=max_len, group=1, n_sample=0, return_logits=True,
+                                     early_stop=False, trim=False)
+        ids, logits = out.ids.cpu().numpy(), out.logits.cpu().numpy()
+    else:
+        g = torch.Generator().manual_seed(6)
+        ids = torch.randint(0, VOCAB, (n_img, max_len), generator=g)
+        ids[:, 0] = START
+        logits, _ = eng.score(mem.to(dev), ids.to(dev), END, mode="full")
+        ids, logits = ids.numpy(), logits.cpu().numpy()
+    ref = decoder_np.decoder_forward(w, ids[sel, :-1], mem.numpy()[sel])
+    err = np.abs(logits[sel] - ref).max()
+    _record(TOL["bf16"], err)
+    assert err < TOL["bf16"]
+    eng.close()
+
+
 # ---------------------------------------------------------------- BASELINE.json sizes: size-independent properties
 FULL_SIZE = {  # images, memory length, rollouts per image, sampled rollouts, max_len (bench.py WORKLOADS)
     "cfg2": (256, 49, 1, 0, 50),
