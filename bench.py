@@ -228,6 +228,88 @@ def torch_eager_gpu(name: str, steps: int, warmup: int, local: int, images_overr
                     "one B200, greedy for every sequence (sampling costs the same decoder calls)"}
 
 
+def teacher_forced(name: str, local: int, reps: int = 3) -> dict:
+    """SURVEY 8f-4 sub-record: log-probs of GIVEN captions (the SCST gradient pass's forward, scst:183-191 / vit:216-255)
+    for the whole workload batch -- the engine's step replay, its full-sequence pass (capdec_forward_full), and the
+    reference's single causal decoder call in eager PyTorch fp32 on the same B200.  Device time (CUDA events, L2 flushed
+    between runs), prefill included in both engine figures."""
+    import torch
+    from image_caption_b200 import CaptionDecodeEngine
+    from image_caption_b200.synthetic import random_decoder, random_memory
+    from oracle import torch_port
+    desc, n_img, S, G, ns, max_len, scaling = WORKLOADS[name]
+    dev = torch.device("cuda", local)
+    dec = random_decoder(0, pe_rows=max(52, max_len)).to(dev)
+    mem = random_memory(n_img, S, seed=1234).to(dev)
+    eng = CaptionDecodeEngine(dec, precision="bf16", max_images=n_img, max_group=G, max_mem=S, max_len=max_len)
+    ids = eng.decode_from_memory(mem, START, END, max_len=max_len, group=G, n_sample=ns, seed=1, trim=False).ids.clone()
+    flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)
+    M, T = n_img * G, max_len - 1
+
+    def timed(fn, n):
+        ts = []
+        for _ in range(n):
+            flush.zero_()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(); out = fn(); e1.record()
+            torch.cuda.synchronize(dev)
+            ts.append(e0.elapsed_time(e1))
+        return sorted(ts)[len(ts) // 2], out
+
+    rec = {"metric": "captions/s", "unit": "captions/s", "dtype": "bf16", "sequences": M, "positions": T,
+           "what": "log p(ids[:, k+1] | ids[:, :k+1]) for every position of every sequence of the workload batch"}
+    outs = {}
+    for mode in ("steps", "full"):
+        for _ in range(2):
+            eng.score(mem, ids, END, group=G, return_logits=False, mode=mode)
+        ms, out = timed(lambda: eng.score(mem, ids, END, group=G, return_logits=False, mode=mode), reps)
+        outs[mode] = out[1]
+        rec[mode] = {"ms": ms, "value": M / (ms * 1e-3)}
+    rec["value"] = rec["full"]["value"]
+    rec["speedup_full_over_steps"] = rec["steps"]["ms"] / rec["full"]["ms"]
+    rec["max_abs_logp_diff_full_vs_steps"] = float((outs["full"] - outs["steps"]).abs().max())
+    eng.profile(True)
+    eng.score(mem, ids, END, group=G, return_logits=False, mode="full")
+    rep = eng.profile_report()
+    eng.profile(False)
+    tot = sum(v["ms"] for v in rep.values())
+    rec["kernels"] = {k: {"launches": v["launches"], "us_per_launch": 1e3 * v["ms"] / v["launches"], "share": v["ms"] / tot}
+                      for k, v in sorted(rep.items(), key=lambda kv: -kv[1]["ms"])}
+    # tensor roofline of the projections: 2 * rows * (1536 + 512 + 512 + 2048 + 2048) * 512 ... per layer
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except (OSError, ValueError):
+        pass
+    peak = float(peaks.get("bf16_tflops_sustained", 1355.1))
+    flops = 2.0 * M * T * 512 * (1536 + 512 + 512 + 512 + 2048 + 2048) * 6
+    gemm_ms = sum(v["ms"] for k, v in rep.items() if k.startswith("full_gemm") and k != "full_gemm_vocab")
+    rec["roofline"] = {"kernel": "full_gemm_* (the six projections of every layer)", "bound": "tensor",
+                       "achieved": flops / (gemm_ms * 1e-3) / 1e12, "peak": peak, "unit": "TFLOP/s",
+                       "frac": flops / (gemm_ms * 1e-3) / 1e12 / peak, "traffic": None,
+                       "peak_source": "measured sustained bf16 (MEASURED_PEAKS.json)" if peaks else "fallback (B200_PROFILING.md)"}
+    eng.close()
+    del eng
+    # the reference's own call: one causal decoder pass in eager fp32 (oracle/torch_port), chunked over sequences to bound memory
+    pdec = torch_port.build_decoder(0, max_len=max(52, max_len)).to(dev)
+    memr = mem.repeat_interleave(G, 0) if G > 1 else mem
+
+    def eager():
+        with torch.no_grad():
+            outs = []
+            for lo in range(0, M, 512):
+                lg = torch_port.teacher_forced_logits(pdec, ids[lo:lo + 512], memr[lo:lo + 512])
+                outs.append(torch.log_softmax(lg, -1).gather(2, ids[lo:lo + 512, 1:, None]).squeeze(2))
+            return torch.cat(outs)
+    eager()
+    ms, _ = timed(eager, 2)
+    rec["torch_eager_gpu_fp32"] = {"ms": ms, "value": M / (ms * 1e-3),
+                                   "note": "reference decoder, one causal pass per 512 sequences, eager torch fp32 on the same B200"}
+    del pdec, memr, mem, flush
+    torch.cuda.empty_cache()
+    return rec
+
+
 def run_torch_gpu_arm(args) -> None:
     if int(os.environ.get("RANK", "0")) != 0:
         return
@@ -482,6 +564,7 @@ def run_b200_arm(args) -> None:
             sub[f"{name}_fp32"] = r
             if rank == 0:
                 sub[f"torch_eager_gpu_{name}"] = torch_eager_gpu(name, 1, 1, local)
+                sub[f"teacher_forced_{name}"] = teacher_forced(name, local)
         line["sub"] = sub
     if rank == 0:
         if world == 1 and not args.no_cpu:
