@@ -22,7 +22,7 @@ EXPORTS = (
     "capdec_prefill", "capdec_decode", "capdec_generate_host", "capdec_sample_logits", "capdec_launch_count",
     "capdec_debug_gemm", "capdec_debug_cross_kv", "capdec_profile_enable", "capdec_profile_report",
     "capdec_beam_search", "capdec_set_memory_projection", "capdec_prefill_tokens", "capdec_gemm_static", "capdec_cider_d",
-    "capdec_forward_full",
+    "capdec_forward_full", "capdec_prefetch_host",
 )
 
 
@@ -112,6 +112,8 @@ def load() -> C.CDLL:
         lib.capdec_set_memory_projection.argtypes = [H, C.c_void_p, C.c_void_p, C.c_int32, C.POINTER(C.c_void_p),
                                                      C.POINTER(C.c_void_p), C.c_void_p]
         lib.capdec_prefill_tokens.argtypes = [H, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_void_p]
+    if hasattr(lib, "capdec_prefetch_host"):
+        lib.capdec_prefetch_host.argtypes = [H, C.c_void_p, C.c_int32, C.c_int32]
     if hasattr(lib, "capdec_forward_full"):
         lib.capdec_forward_full.argtypes = [H, C.POINTER(ForwardArgs), C.c_void_p]
     lib.capdec_launch_count.restype = C.c_int64

@@ -534,7 +534,8 @@ static void free_all(capdec_handle h) {
   for (void* p : h->allocs) cudaFree(p);
   h->allocs.clear();
   if (h->copy_stream) { cudaStreamDestroy(h->copy_stream); h->copy_stream = nullptr; }
-  for (auto& e : h->copy_ev) if (e) { cudaEventDestroy(e); e = nullptr; }
+  for (auto& slot : h->copy_ev)
+    for (auto& e : slot) if (e) { cudaEventDestroy(e); e = nullptr; }
   if (h->copy_start) { cudaEventDestroy(h->copy_start); h->copy_start = nullptr; }
 }
 
@@ -1459,8 +1460,10 @@ extern "C" int capdec_decode(capdec_handle h, const capdec_decode_args* a, void*
   cp.forced = (a->flags & CAPDEC_DECODE_TEACHER_FORCED) ? 1 : 0;
   cp.n_sample_rows = n_images * a->n_sample;
   cp.n_greedy_rows = M - cp.n_sample_rows;
-  // pageable source: the runtime stages it before returning, so `cp` may die with this frame
-  CUDA_TRY(h, cudaMemcpyAsync(h->cp, &cp, sizeof cp, cudaMemcpyHostToDevice, s));
+  // by value through a one-thread kernel, not a host -> device copy: a copy would queue on the H2D copy engine behind a
+  // capdec_prefetch_host transfer in flight (205 MB at cfg3) and hold the whole rollout back until it has landed
+  set_call_params_kernel<<<1, 1, 0, s>>>(h->cp, cp);
+  CUDA_TRY(h, cudaGetLastError());
   init_rollout_kernel<<<std::min((M * a->max_len + 255) / 256, 1024), 256, 0, s>>>(h->st, h->cp, h->fin, M);
   CUDA_TRY(h, cudaGetLastError());
   h->launches++;
@@ -1718,7 +1721,8 @@ extern "C" int capdec_beam_search(capdec_handle h, const capdec_beam_args* a, vo
   cp.pad_token = a->pad_token;
   cp.n_greedy_rows = M;
   cp.vocab = V;
-  CUDA_TRY(h, cudaMemcpyAsync(h->cp, &cp, sizeof cp, cudaMemcpyHostToDevice, s));
+  set_call_params_kernel<<<1, 1, 0, s>>>(h->cp, cp);
+  CUDA_TRY(h, cudaGetLastError());
   init_rollout_kernel<<<std::min((M * a->max_len + 255) / 256, 1024), 256, 0, s>>>(h->st, h->cp, h->fin, M);
   beam_init_kernel<<<std::min((2 * M * h->t_pad + 255) / 256, 1024), 256, 0, s>>>(h->beam, h->cp, n_images, beam, h->t_pad);
   CUDA_TRY(h, cudaGetLastError());
@@ -1771,6 +1775,47 @@ extern "C" int capdec_beam_search(capdec_handle h, const capdec_beam_args* a, vo
 // Host buffers in, host buffers out (what generate() / SCSTLoss see when their tensors live on the CPU).
 // The memory is copied in up to 8 image chunks on a private copy stream; each chunk's K/V projection starts as soon
 // as its copy has landed, so the host link and the prefill overlap instead of running back to back.
+static int ensure_host_staging(capdec_handle h) {
+  if (h->stage_mem[0]) return 0;
+  const size_t Mmax = (size_t)h->cfg.max_images * h->cfg.max_group;
+  for (int i = 0; i < 2; ++i) TRY(dev_alloc(h, &h->stage_mem[i], (size_t)h->cfg.max_images * h->cfg.max_mem * kD));
+  TRY(dev_alloc(h, &h->stage_ids, Mmax * h->cfg.max_len));
+  TRY(dev_alloc(h, &h->stage_logp, Mmax * h->cfg.max_len));
+  CUDA_TRY(h, cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+  for (auto& slot : h->copy_ev)
+    for (auto& e : slot) CUDA_TRY(h, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  CUDA_TRY(h, cudaEventCreateWithFlags(&h->copy_start, cudaEventDisableTiming));
+  return 0;
+}
+
+// The memory of one call, host -> staging slot, in image chunks on the copy stream; one event per chunk.
+static int enqueue_host_copy(capdec_handle h, int slot, const float* memory_host, int n_images, int mem_len) {
+  const int n_chunks = std::min<int>(kHostCopyChunks, n_images);
+  const int per = (n_images + n_chunks - 1) / n_chunks;
+  for (int c = 0, img0 = 0; img0 < n_images; ++c, img0 += per) {
+    const int n = std::min(per, n_images - img0);
+    const size_t off = (size_t)img0 * mem_len * kD;
+    CUDA_TRY(h, cudaMemcpyAsync(h->stage_mem[slot] + off, memory_host + off, (size_t)n * mem_len * kD * sizeof(float),
+                                cudaMemcpyHostToDevice, h->copy_stream));
+    CUDA_TRY(h, cudaEventRecord(h->copy_ev[slot][c], h->copy_stream));
+  }
+  return 0;
+}
+
+extern "C" int capdec_prefetch_host(capdec_handle h, const float* memory_host, int32_t n_images, int32_t mem_len) {
+  TRY(check_prefill_args(h, memory_host, n_images, mem_len));
+  CUDA_TRY(h, cudaSetDevice(h->device));
+  TRY(ensure_host_staging(h));
+  // the slot the newest outstanding prefetch (or, with none, the last capdec_generate_host) did NOT use; its last
+  // reader - a prefill two calls back - has completed, because capdec_generate_host returns synchronised
+  const int slot = h->last_slot ^ 1;
+  if (h->pf[slot].valid) return fail(h, CAPDEC_ERR_STATE, "two prefetches are already outstanding (each capdec_generate_host consumes one)");
+  TRY(enqueue_host_copy(h, slot, memory_host, n_images, mem_len));
+  h->pf[slot] = {memory_host, n_images, mem_len, true, ++h->pf_seq};
+  h->last_slot = slot;
+  return CAPDEC_OK;
+}
+
 extern "C" int capdec_generate_host(capdec_handle h, const float* memory_host, int32_t n_images, int32_t mem_len,
                                     const capdec_decode_args* ah, void* stream) {
   if (!h || !memory_host || !ah) return fail(h, CAPDEC_ERR_INVALID, "null argument");
@@ -1782,19 +1827,26 @@ extern "C" int capdec_generate_host(capdec_handle h, const float* memory_host, i
     return fail(h, CAPDEC_ERR_CAPACITY, "group/max_len outside capacity");
   cudaStream_t s = (cudaStream_t)stream;
   CUDA_TRY(h, cudaSetDevice(h->device));
-  const size_t Mmax = (size_t)h->cfg.max_images * h->cfg.max_group;
-  if (!h->stage_mem) {
-    TRY(dev_alloc(h, &h->stage_mem, (size_t)h->cfg.max_images * h->cfg.max_mem * kD));
-    TRY(dev_alloc(h, &h->stage_ids, Mmax * h->cfg.max_len));
-    TRY(dev_alloc(h, &h->stage_logp, Mmax * h->cfg.max_len));
-    CUDA_TRY(h, cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
-    for (auto& e : h->copy_ev) CUDA_TRY(h, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-    CUDA_TRY(h, cudaEventCreateWithFlags(&h->copy_start, cudaEventDisableTiming));
-  }
+  TRY(ensure_host_staging(h));
   const size_t M = (size_t)n_images * ah->group;
-  // the copy stream starts after whatever the caller's stream still does with the staging buffer
-  CUDA_TRY(h, cudaEventRecord(h->copy_start, s));
-  CUDA_TRY(h, cudaStreamWaitEvent(h->copy_stream, h->copy_start, 0));
+  // the oldest outstanding prefetch of this very buffer, if any: its copy is already under way (or done)
+  int slot = -1;
+  for (int i = 0; i < 2; ++i)
+    if (h->pf[i].valid && h->pf[i].host == memory_host && h->pf[i].n_images == n_images && h->pf[i].mem_len == mem_len &&
+        (slot < 0 || h->pf[i].seq < h->pf[slot].seq))
+      slot = i;
+  if (slot >= 0) {
+    h->pf[slot].valid = false;
+  } else {
+    // no prefetch: copy now, into the slot no outstanding prefetch holds (both held: this call matches neither, drop them)
+    slot = !h->pf[0].valid ? 0 : (!h->pf[1].valid ? 1 : 0);
+    if (h->pf[0].valid && h->pf[1].valid) h->pf[0].valid = h->pf[1].valid = false;
+    // the copy stream starts after whatever the caller's stream still does with the staging buffer
+    CUDA_TRY(h, cudaEventRecord(h->copy_start, s));
+    CUDA_TRY(h, cudaStreamWaitEvent(h->copy_stream, h->copy_start, 0));
+    TRY(enqueue_host_copy(h, slot, memory_host, n_images, mem_len));
+    if (!h->pf[slot ^ 1].valid) h->last_slot = slot;
+  }
   h->prefilled = false;
   h->launches_this_enqueue = 0;
   const int n_chunks = std::min<int>(kHostCopyChunks, n_images);
@@ -1802,11 +1854,8 @@ extern "C" int capdec_generate_host(capdec_handle h, const float* memory_host, i
   for (int c = 0, img0 = 0; img0 < n_images; ++c, img0 += per) {
     const int n = std::min(per, n_images - img0);
     const size_t off = (size_t)img0 * mem_len * kD;
-    CUDA_TRY(h, cudaMemcpyAsync(h->stage_mem + off, memory_host + off, (size_t)n * mem_len * kD * sizeof(float),
-                                cudaMemcpyHostToDevice, h->copy_stream));
-    CUDA_TRY(h, cudaEventRecord(h->copy_ev[c], h->copy_stream));
-    CUDA_TRY(h, cudaStreamWaitEvent(s, h->copy_ev[c], 0));
-    TRY(prefill_chunk(h, s, h->stage_mem + off, img0, n, n_images, mem_len));
+    CUDA_TRY(h, cudaStreamWaitEvent(s, h->copy_ev[slot][c], 0));
+    TRY(prefill_chunk(h, s, h->stage_mem[slot] + off, img0, n, n_images, mem_len));
   }
   TRY(finish_prefill(h, n_images, mem_len));
   capdec_decode_args ad = *ah;

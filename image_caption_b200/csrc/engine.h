@@ -138,11 +138,15 @@ struct capdec_engine {
   int cider_off_cap = 0;
 
   // ---- host-buffer entry point staging (device side)
-  float* stage_mem = nullptr;
+  float* stage_mem[2] = {nullptr, nullptr};   // two slots: capdec_prefetch_host fills one while the other is decoded
   long long* stage_ids = nullptr;
   float* stage_logp = nullptr;
   cudaStream_t copy_stream = nullptr;          // host -> device chunks of the memory, overlapped with the prefill
-  cudaEvent_t copy_ev[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  cudaEvent_t copy_ev[2][8] = {};              // [slot][chunk]
+  struct Prefetch { const float* host; int n_images, mem_len; bool valid; unsigned long long seq; };
+  Prefetch pf[2] = {{nullptr, 0, 0, false, 0}, {nullptr, 0, 0, false, 0}};
+  unsigned long long pf_seq = 0;
+  int last_slot = 1;                           // slot of the newest prefetch / un-prefetched copy
   cudaEvent_t copy_start = nullptr;
 
   // ---- current rollout

@@ -32,6 +32,9 @@ __global__ void init_rollout_kernel(DecState* st, const CallParams* cp, unsigned
 
 // x[m,:] = emb[tok]*sqrt(512) + pe[n,:]; separate multiply and add (no FMA contraction) so the
 // fp32 mode reproduces the reference's two-op rounding.
+// The per-call parameters reach the device as a kernel argument (see capdec_decode).
+__global__ void set_call_params_kernel(CallParams* dst, const CallParams src) { *dst = src; }
+
 template <typename Elem>
 __global__ void embed_pe_kernel(const DecState* st, const CallParams* cp, const float* __restrict__ emb,
                                 const float* __restrict__ pe, float* __restrict__ x, Elem* __restrict__ xb, int M) {

@@ -265,6 +265,18 @@ class CaptionDecodeEngine:
             logits = logits[:, :n] if logits is not None else None
         return Rollout(ids=ids, logp=logp, steps=n, logits=logits)
 
+    def prefetch_memory(self, memory: torch.Tensor) -> None:
+        """Start the host -> device copy of a CPU ``memory`` (B, S, 512) float32 that a LATER ``decode_from_memory`` call
+        will be given (capdec_prefetch_host): the copy runs underneath whatever the engine decodes in between.  The tensor
+        must be contiguous float32 (pin it for a truly asynchronous copy) and stay unchanged until that call returns."""
+        if memory.is_cuda or memory.dim() != 3 or memory.shape[2] != self.d_model or memory.dtype != torch.float32 \
+                or not memory.is_contiguous():
+            raise ValueError(f"memory must be a contiguous CPU float32 (B, S, {self.d_model}) tensor")
+        self._ensure_capacity(memory.shape[0], 1, memory.shape[1], 2)
+        self.sync_weights()
+        _lib.check(self._h, self._lib.capdec_prefetch_host(self._h, memory.data_ptr(), memory.shape[0], memory.shape[1]))
+        self._keep_prefetch = getattr(self, "_keep_prefetch", [])[-1:] + [memory]
+
     def score(self, memory: torch.Tensor, ids: torch.Tensor, end_token: int, group: int = 1,
               return_logits: bool = True, pad_token: int = 0, mode: str = "steps"):
         """Teacher-forced pass over given sequences (CAPDEC_DECODE_TEACHER_FORCED): ``ids`` (B*group, L) int64 with

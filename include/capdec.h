@@ -177,6 +177,14 @@ int capdec_decode(capdec_handle h, const capdec_decode_args* args, void* cuda_st
 int capdec_generate_host(capdec_handle h, const float* memory_host, int32_t n_images, int32_t mem_len,
                          const capdec_decode_args* args_host, void* cuda_stream);
 
+/* Optional overlap for back-to-back capdec_generate_host calls (no counterpart in the reference, whose memory never leaves
+ * the device; it exists for the host-buffer boundary above): start the host -> device copy of the memory that a LATER
+ * capdec_generate_host call will be given, on the engine's copy stream, so that it runs underneath the decode of the call
+ * in between.  That later call (same pointer, n_images and mem_len) then waits for this copy instead of issuing its own.
+ * At most two prefetches may be outstanding (CAPDEC_ERR_STATE beyond); the host buffer must stay unchanged (and should be
+ * pinned) until the call that consumes it returns; a capdec_generate_host that matches no prefetch copies as before. */
+int capdec_prefetch_host(capdec_handle h, const float* memory_host, int32_t n_images, int32_t mem_len);
+
 /* Batched beam search over the images of the last prefill: the third `generate` method of the reference,
  * `_beam_search` (models/vit_transformer_model.py:327-420, models/grid_transformer_model.py:253-322), which the
  * reference runs one image at a time and without a KV cache.  Same rules: scores are sums of log-softmax values

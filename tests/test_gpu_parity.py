@@ -427,6 +427,39 @@ def test_host_buffer_entry_point(dev):
     eng.close()
 
 
+def test_host_prefetch_overlaps_and_changes_nothing(dev):
+    """capdec_prefetch_host: a prefetched host buffer gives the same rollout as an un-prefetched one (two staging slots,
+    oldest matching prefetch consumed first, a non-matching call still copies by itself); a third outstanding prefetch
+    is refused."""
+    from image_caption_b200._lib import CapdecError
+    dec = small_decoder(layers=2, end_bias=0.5)
+    mems = [torch_port.synthetic_memory(9, 49, seed=s).pin_memory() for s in (1, 2, 3)]
+    eng = make_engine(dec.to(dev), "bf16", max_images=9, max_group=2, max_mem=49, max_len=10)
+    kw = dict(max_len=10, group=2, n_sample=1, trim=False, early_stop=False)
+    plain = [eng.decode_from_memory(m, START, END, seed=7 + i, **kw) for i, m in enumerate(mems)]
+    eng.prefetch_memory(mems[0])
+    outs = []
+    for i, m in enumerate(mems):
+        if i + 1 < len(mems):
+            eng.prefetch_memory(mems[i + 1])
+        outs.append(eng.decode_from_memory(m, START, END, seed=7 + i, **kw))
+    for a, b in zip(plain, outs):
+        assert torch.equal(a.ids, b.ids) and torch.equal(a.logp, b.logp)
+    # a call that matches no outstanding prefetch copies by itself; the prefetch is consumed later
+    eng.prefetch_memory(mems[2])
+    o1 = eng.decode_from_memory(mems[1], START, END, seed=8, **kw)
+    o2 = eng.decode_from_memory(mems[2], START, END, seed=9, **kw)
+    assert torch.equal(o1.ids, plain[1].ids) and torch.equal(o2.ids, plain[2].ids)
+    eng.prefetch_memory(mems[0])
+    eng.prefetch_memory(mems[1])
+    with pytest.raises(CapdecError):
+        eng.prefetch_memory(mems[2])
+    o0 = eng.decode_from_memory(mems[0], START, END, seed=7, **kw)
+    o1 = eng.decode_from_memory(mems[1], START, END, seed=8, **kw)
+    assert torch.equal(o0.ids, plain[0].ids) and torch.equal(o1.logp, plain[1].logp)
+    eng.close()
+
+
 def test_capacity_grows_and_limits_raise(dev):
     dec = small_decoder(layers=1, pe_rows=10).to(dev)
     eng = make_engine(dec, "fp32", max_images=2, max_mem=8, max_len=6)
