@@ -265,18 +265,33 @@ static cudaError_t launch_ex(void (*kern)(KArgs...), dim3 grid, dim3 block, size
 
 static int swap_stages(capdec_handle h, int bnb, int K, int ctas, bool ln = false) {
   const int num_kb = K / kSwapBK;
-  if (h->force_stages > 0) return std::min(num_kb, std::min(h->force_stages, 12));
-  // few CTAs: everything in flight at once; more CTAs than SMs: leave room for two per SM
-  const int budget = (ctas > 148 && !ln ? 100 : 200) * 1024;
-  int stages = std::min(num_kb, 12);
-  while (stages > 2 && swap_smem_bytes(bnb, stages) > budget) --stages;
-  // KNOWN ISSUE (B200, found by the full-sequence pass, the first caller with ~400 LayerNorm-GEMM CTAs): with 128-row
-  // tiles and an ODD ring depth (3 or 5) the LayerNorm kernel dies with "unspecified launch failure" once the grid is
-  // ~2.2 waves or more (80 row tiles: sometimes, 98: always; 62 and fewer: never, which covers every BASELINE config);
-  // with 4 or 6 stages the same launches pass (90+ in a row).  Root cause not found (no trap of ours fires, there is no
-  // compute-sanitizer on this pool); multi-wave LayerNorm launches therefore take an even depth.
-  if (ln && ctas > 148 && (stages & 1) && stages > 2) --stages;
+  int stages;
+  if (h->force_stages > 0) {
+    stages = std::min(num_kb, std::min(h->force_stages, 12));
+  } else {
+    // few CTAs: everything in flight at once; more CTAs than SMs: leave room for two per SM (the LayerNorm kernel is
+    // one per SM by its registers anyway)
+    const int budget = (ctas > 148 && !ln ? 100 : 200) * 1024;
+    stages = std::min(num_kb, 12);
+    while (stages > 2 && swap_smem_bytes(bnb, stages) > budget) --stages;
+  }
   return stages;
+}
+
+// With two MMA issuer warps (even / odd k-blocks) the ring depth must be EVEN whenever the ring wraps.  Each issuer waits
+// on full[slot] by phase PARITY.  With an even depth a slot is always drained by the same issuer, which therefore sees
+// every phase of it.  With an odd depth the slot's fills alternate between the issuers, so an issuer waits for phase
+// p + 2 having last seen phase p - and parity cannot tell "p + 1 still in flight" from "p + 2 complete".  The producer
+// issues the copies in order, but they may LAND out of order: if k-block 4 lands before k-block 3 (3 stages), issuer 0
+// drains 4, reaches 6, finds full[0] in (incomplete) phase 1, takes parity 0 as complete and issues MMAs on a slot still
+// being written, then arrives on empty[0] a second time in one phase: an mbarrier over-arrival, which the hardware
+// reports as "unspecified launch failure".  Found by the full-sequence pass (the first caller with ~400 such CTAs: 98 row
+// tiles always failed at depths 3 and 5, 80 sometimes, and 4 / 6 never); a 12 544-row decode batch hit it too, and
+// every 128-row LayerNorm GEMM of round 1-2 (depth 5) carried the race at low odds.
+static int even_ring_for_two_issuers(int stages, int num_kb, int issuers, int bnb, int ksplit = 1) {
+  if (issuers != 2 || stages >= num_kb || (stages & 1) == 0) return stages;
+  if (stages + 1 <= num_kb && swap_smem_bytes(bnb, stages + 1, ksplit) <= kMaxDynSmem && stages < 4) return stages + 1;
+  return stages > 2 ? stages - 1 : stages + 1;
 }
 
 // All of a CTA's K range in three copies (two weight halves + the activations) when it is exactly 8 k-blocks and the
@@ -292,6 +307,7 @@ static int launch_swap_ks(capdec_handle h, cudaStream_t s, const WeightMaps& tw,
   int stages = swap_stages(h, BNB, K / KSPLIT, grid.x * grid.y, kLN);
   while (stages > 2 && swap_smem_bytes(BNB, stages, KSPLIT) > kMaxDynSmem) --stages;
   while (kLN && stages * swap_stage_bytes(BNB) < swap_ln_stage_out_bytes(BNB)) ++stages;  // the output tile is staged in the ring
+  stages = even_ring_for_two_issuers(stages, K / kSwapBK / KSPLIT, swap_issuers(BNB, kLN), BNB, KSPLIT);
   const int whole = swap_whole_k(h, BNB, K / kSwapBK / KSPLIT, stages);
   ProfScope ps(h, s);
   cudaError_t e = launch_ex(gemm_swap_kernel<BNB, kLN, Epi, KSPLIT>, grid, dim3(swap_threads(BNB, kLN)), swap_smem_bytes(BNB, stages, KSPLIT), s,
@@ -327,6 +343,7 @@ static int launch_swap_bnb(capdec_handle h, cudaStream_t s, const WeightMaps& tw
   dim3 grid(n_out / kSwapBF, (M + BNB - 1) / BNB, zsplit);
   int stages = swap_stages(h, BNB, K / zsplit, grid.x * grid.y * grid.z, kLN);
   while (kLN && stages * swap_stage_bytes(BNB) < swap_ln_stage_out_bytes(BNB)) ++stages;  // the output tile is staged in the ring
+  stages = even_ring_for_two_issuers(stages, K / kSwapBK / zsplit, swap_issuers(BNB, kLN), BNB);
   const int whole = swap_whole_k(h, BNB, K / kSwapBK / zsplit, stages);
   ProfScope ps(h, s);
   cudaError_t e = launch_ex(gemm_swap_kernel<BNB, kLN, Epi>, grid, dim3(swap_threads(BNB, kLN)), swap_smem_bytes(BNB, stages), s,
