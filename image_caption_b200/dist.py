@@ -106,3 +106,29 @@ def sharded_rollout(local_decode: Callable[..., Tuple[torch.Tensor, Optional[tor
     ids = ids[:, :width]
     logp = logp[:, : width - 1] if logp is not None else None
     return ids, logp
+
+
+class HostFeeder:
+    """Double-buffered host -> device feed for back-to-back sharded rollouts: ``prefetch(t)`` starts the copy of a pinned
+    CPU tensor on a side stream, ``take()`` returns the oldest prefetched copy once the current stream may read it.  Calling
+    ``prefetch(next)`` before decoding ``take()``'s result puts the next rollout's copy underneath the current decode (the
+    single-GPU host entry point does the same inside the C ABI: capdec_prefetch_host).  Plumbing only: no kernels."""
+
+    def __init__(self, device: torch.device):
+        self.device = device
+        self.stream = torch.cuda.Stream(device=device)
+        self._queue = []
+
+    def prefetch(self, host_tensor: torch.Tensor) -> None:
+        with torch.cuda.stream(self.stream):
+            dev_tensor = host_tensor.to(self.device, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(self.stream)
+        self._queue.append((dev_tensor, ev))
+
+    def take(self) -> torch.Tensor:
+        dev_tensor, ev = self._queue.pop(0)
+        cur = torch.cuda.current_stream(self.device)
+        cur.wait_event(ev)
+        dev_tensor.record_stream(cur)
+        return dev_tensor

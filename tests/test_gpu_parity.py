@@ -460,6 +460,20 @@ def test_host_prefetch_overlaps_and_changes_nothing(dev):
     eng.close()
 
 
+def test_host_feeder_hands_over_in_order(dev):
+    """dist.HostFeeder: prefetched host tensors come back in order, complete, on the device."""
+    from image_caption_b200.dist import HostFeeder
+    feeder = HostFeeder(dev)
+    hosts = [torch.full((64, 49, 512), float(i)).pin_memory() for i in range(3)]
+    feeder.prefetch(hosts[0])
+    feeder.prefetch(hosts[1])
+    a = feeder.take()
+    feeder.prefetch(hosts[2])
+    b, c = feeder.take(), feeder.take()
+    for i, t in enumerate((a, b, c)):
+        assert t.is_cuda and torch.equal(t.cpu(), hosts[i])
+
+
 def test_capacity_grows_and_limits_raise(dev):
     dec = small_decoder(layers=1, pe_rows=10).to(dev)
     eng = make_engine(dec, "fp32", max_images=2, max_mem=8, max_len=6)
