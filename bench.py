@@ -2,7 +2,7 @@
 """bench.py - captions/s of batched caption decoding on B200 (BASELINE.json metric).
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--workload auto|cfg2|cfg3|cfg4|cfg5|vit_greedy]
-                    [--precision bf16|fp32] [--impl b200|reference|torch_gpu] [--no-sub] [--no-verify]
+                    [--precision bf16|fp32|tf32] [--impl b200|reference|torch_gpu] [--no-sub] [--no-verify]
 
 A "step" is one whole rollout of the hot path over one batch: cross-K/V prefill plus max_len-1 decode
 steps (BASELINE.json configs).
@@ -448,7 +448,7 @@ def measure(name: str, precision: str, steps: int, warmup: int, world: int, rank
     #     ids teacher-forced; sampled log-probs within the bf16 tolerance, greedy tokens = its argmax outside the tie tolerance;
     # (2) with CAPDEC_FLAG_BATCH_INVARIANT (one route for every batch size): bit-equal at every N.
     if verify and world > 1:
-        tol = 4e-2 if precision == "bf16" else 2e-4
+        tol = {"bf16": 4e-2, "tf32": 2e-2}.get(precision, 2e-4)
         ok = {}
         for mode in ("as_measured", "batch_invariant"):
             inv = mode == "batch_invariant"
@@ -574,6 +574,8 @@ def run_b200_arm(args) -> None:
         if world == 1:
             r = measure(name, "fp32", 3, 3, world, rank, local, profile=False)
             sub[f"{name}_fp32"] = r
+            r = measure(name, "tf32", 3, 3, world, rank, local, profile=False)  # fp32 storage, tcgen05 kind::tf32 projections
+            sub[f"{name}_tf32"] = r
             if rank == 0:
                 sub[f"torch_eager_gpu_{name}"] = torch_eager_gpu(name, 1, 1, local)
                 sub[f"teacher_forced_{name}"] = teacher_forced(name, local)
@@ -595,7 +597,7 @@ def main() -> None:
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference", "torch_gpu"])
     ap.add_argument("--workload", default="auto", choices=["auto"] + sorted(WORKLOADS))
-    ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
+    ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32", "tf32"])
     ap.add_argument("--images", type=int, default=0, help="override the workload's image count")
     ap.add_argument("--cpu-sample", type=int, default=0, help="images in the bounded CPU-baseline sample (0 = per workload)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")

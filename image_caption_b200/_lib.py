@@ -10,7 +10,7 @@ LIB_PATH = os.environ.get("CAPDEC_LIB") or os.path.join(_HERE, "libcapdec.so")  
 
 ABI_VERSION = 1
 MAX_LAYERS = 12
-PREC_FP32, PREC_BF16 = 0, 1
+PREC_FP32, PREC_BF16, PREC_TF32 = 0, 1, 2
 FLAG_NO_GRAPH, FLAG_NO_UMMA, FLAG_V1_STEP, FLAG_NO_PDL = 1, 2, 4, 8
 FLAG_BATCH_INVARIANT = 32
 DECODE_NO_EARLY_STOP = 1

@@ -90,16 +90,18 @@ static EncodeTiledFn encode_tiled_fn() {
   return fn;
 }
 
-// bf16 [rows, cols] row-major matrix; box = box_rows x 64 columns, 128B swizzle (one UMMA atom row).
-static int make_map(capdec_handle h, CUtensorMap* m, const void* ptr, int rows, int cols, int box_rows) {
+// [rows, cols] row-major matrix, bf16 (or fp32 for the TF32 route); box = box_rows x one 128-byte swizzle row
+// (64 bf16 / 32 fp32 columns = one UMMA atom row).
+static int make_map(capdec_handle h, CUtensorMap* m, const void* ptr, int rows, int cols, int box_rows, bool f32 = false) {
   EncodeTiledFn fn = encode_tiled_fn();
   if (!fn) return fail(h, CAPDEC_ERR_CUDA, "cuTensorMapEncodeTiled entry point unavailable");
+  const cuuint64_t es = f32 ? 4 : 2;
   cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
-  cuuint64_t strides[1] = {(cuuint64_t)cols * 2};
-  cuuint32_t box[2] = {(cuuint32_t)kUmmaBK, (cuuint32_t)box_rows};
+  cuuint64_t strides[1] = {(cuuint64_t)cols * es};
+  cuuint32_t box[2] = {(cuuint32_t)(128 / es), (cuuint32_t)box_rows};
   cuuint32_t estr[2] = {1, 1};
-  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+  CUresult r = fn(m, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims,
+                  strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return fail(h, CAPDEC_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d) rows=%d cols=%d", (int)r, rows, cols);
   return 0;
@@ -139,14 +141,14 @@ static int make_map3(capdec_handle h, CUtensorMap* m, const void* ptr, int rows,
   return 0;
 }
 
-static int make_weight_maps(capdec_handle h, WeightMaps* wm, const void* ptr, int n, int k) {
+static int make_weight_maps(capdec_handle h, WeightMaps* wm, const void* ptr, int n, int k, bool f32 = false) {
   wm->raw = ptr; wm->rows = n; wm->k = k;
   const int bns[3] = {32, 64, 128};
   for (int i = 0; i < 3; ++i) {
-    int rc = make_map(h, &wm->bn[i], ptr, n, k, bns[i]);
+    int rc = make_map(h, &wm->bn[i], ptr, n, k, bns[i], f32);
     if (rc) return rc;
   }
-  if (n % kSwapBF == 0 && (k / kUmmaBK) % kSwapWholeKB == 0) {
+  if (!f32 && n % kSwapBF == 0 && (k / kUmmaBK) % kSwapWholeKB == 0) {
     return make_map3(h, &wm->w3, ptr, n, k, kSwapBF, kSwapWholeKB / 2);
   }
   return 0;
@@ -155,11 +157,11 @@ static int make_weight_maps(capdec_handle h, WeightMaps* wm, const void* ptr, in
 // ------------------------------------------------------------------ GEMM dispatch
 static const int kMaxDynSmem = 227 * 1024;
 
-template <int BN, typename Epi>
+template <int BN, typename Epi, typename In = bf16>
 static int launch_umma_bn(capdec_handle h, cudaStream_t s, const CUtensorMap& ta, const CUtensorMap& tw, int M, int N,
                           int K, const Epi& epi, const DecState* st) {
-  auto kern = gemm_umma_kernel<BN, Epi>;  // dynamic-smem limit raised once in configure_umma_kernels()
-  const int num_kb = K / kUmmaBK;
+  auto kern = gemm_umma_kernel<BN, Epi, In>;  // dynamic-smem limit raised once in configure_umma_kernels()
+  const int num_kb = K / (128 / (int)sizeof(In));
   int stages = std::min(num_kb, 8);
   dim3 grid(N / BN, (M + kUmmaBM - 1) / kUmmaBM);
   // many tiles per SM (prefill): two CTAs per SM, so that one's epilogue overlaps the other's main loop
@@ -174,14 +176,14 @@ static int launch_umma_bn(capdec_handle h, cudaStream_t s, const CUtensorMap& ta
 
 // Pick the widest N tile that still yields at least one CTA per SM (the step GEMMs have few
 // M tiles: M = number of live sequences).
-template <typename Epi>
+template <typename Epi, typename In = bf16>
 static int launch_umma(capdec_handle h, cudaStream_t s, const CUtensorMap& ta, const WeightMaps& wm, int M, int N, int K,
                        const Epi& epi, const DecState* st) {
   if (K % kUmmaBK != 0 || N % 128 != 0) return fail(h, CAPDEC_ERR_INVALID, "tcgen05 GEMM needs K%%64==0, N%%128==0 (N=%d K=%d)", N, K);
   const int tiles_m = (M + kUmmaBM - 1) / kUmmaBM;
-  if (tiles_m * (N / 128) >= 148) return launch_umma_bn<128, Epi>(h, s, ta, wm.bn[2], M, N, K, epi, st);
-  if (tiles_m * (N / 64) >= 148) return launch_umma_bn<64, Epi>(h, s, ta, wm.bn[1], M, N, K, epi, st);
-  return launch_umma_bn<32, Epi>(h, s, ta, wm.bn[0], M, N, K, epi, st);
+  if (tiles_m * (N / 128) >= 148) return launch_umma_bn<128, Epi, In>(h, s, ta, wm.bn[2], M, N, K, epi, st);
+  if (tiles_m * (N / 64) >= 148) return launch_umma_bn<64, Epi, In>(h, s, ta, wm.bn[1], M, N, K, epi, st);
+  return launch_umma_bn<32, Epi, In>(h, s, ta, wm.bn[0], M, N, K, epi, st);
 }
 
 template <typename TA, typename TW, typename Epi>
@@ -203,6 +205,20 @@ static cudaError_t configure_umma_epi() {
   if (e == cudaSuccess) e = cudaFuncSetAttribute(gemm_umma_kernel<128, Epi>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
   return e;
 }
+template <typename Epi>
+static cudaError_t configure_umma_epi_tf32() {
+  cudaError_t e = cudaFuncSetAttribute(gemm_umma_kernel<32, Epi, float>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(gemm_umma_kernel<64, Epi, float>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(gemm_umma_kernel<128, Epi, float>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
+  return e;
+}
+static cudaError_t configure_umma_kernels_tf32() {
+  cudaError_t e = configure_umma_epi_tf32<EpiLinear<float, false>>();
+  if (e == cudaSuccess) e = configure_umma_epi_tf32<EpiLinear<float, true>>();
+  if (e == cudaSuccess) e = configure_umma_epi_tf32<EpiQKV<float>>();
+  if (e == cudaSuccess) e = configure_umma_epi_tf32<EpiCrossKV<float>>();
+  return e;
+}
 static cudaError_t configure_umma_kernels() {
   cudaError_t e = configure_umma_epi<EpiLinear<float, false>>();
   if (e == cudaSuccess) e = configure_umma_epi<EpiLinear<float, true>>();
@@ -218,8 +234,12 @@ static cudaError_t configure_umma_kernels() {
 template <typename EpiF32, typename EpiB16>
 static int gemm(capdec_handle h, cudaStream_t s, const void* a_ptr, const CUtensorMap* a_map, const void* w_ptr,
                 const WeightMaps* w_maps, int M, int N, int K, const EpiF32& e32, const EpiB16& e16, const DecState* st) {
-  if (!h->bf16)
+  if (!h->bf16) {
+    // fp32 storage: CUDA cores (the strict-parity mode), or tcgen05 kind::tf32 straight from the fp32 buffers
+    if (h->umma_f32 && a_map != nullptr && w_maps != nullptr && N % 128 == 0)
+      return launch_umma<EpiF32, float>(h, s, *a_map, *w_maps, M, N, K, e32, st);
     return launch_simt<float, float, EpiF32>(h, s, (const float*)a_ptr, K, (const float*)w_ptr, K, M, N, K, e32, st);
+  }
   if (h->use_umma) return launch_umma<EpiB16>(h, s, *a_map, *w_maps, M, N, K, e16, st);
   return launch_simt<bf16, bf16, EpiB16>(h, s, (const bf16*)a_ptr, K, (const bf16*)w_ptr, K, M, N, K, e16, st);
 }
@@ -663,6 +683,7 @@ static int create_impl(capdec_handle h) {
   TRY(dev_alloc(h, &h->cp, 1));
   CUDA_TRY(h, cudaMemset(h->st, 0, sizeof(DecState)));
   if (h->use_umma) CUDA_TRY(h, configure_umma_kernels());
+  if (h->umma_f32) CUDA_TRY(h, configure_umma_kernels_tf32());
   if (h->fast) {
     TRY(dev_alloc(h, &h->fc_wT, (size_t)kD * kVPad));
     h->part_rows = (int)std::min<size_t>(M, 512);
@@ -701,7 +722,7 @@ extern "C" int capdec_create(const capdec_config* cfg, int device, capdec_handle
   if (cfg->max_len < 2 || cfg->max_len > 128) return fail(nullptr, CAPDEC_ERR_INVALID, "max_len %d must be in [2,128]", cfg->max_len);
   if (cfg->pe_rows < 1 || cfg->max_mem < 1 || cfg->max_images < 1 || cfg->max_group < 1)
     return fail(nullptr, CAPDEC_ERR_INVALID, "sizes must be positive");
-  if (cfg->precision != CAPDEC_PREC_FP32 && cfg->precision != CAPDEC_PREC_BF16)
+  if (cfg->precision != CAPDEC_PREC_FP32 && cfg->precision != CAPDEC_PREC_BF16 && cfg->precision != CAPDEC_PREC_TF32)
     return fail(nullptr, CAPDEC_ERR_INVALID, "unknown precision %d", cfg->precision);
 
   int ndev = 0;
@@ -719,6 +740,7 @@ extern "C" int capdec_create(const capdec_config* cfg, int device, capdec_handle
   h->device = device;
   h->bf16 = cfg->precision == CAPDEC_PREC_BF16;
   h->use_umma = h->bf16 && !(cfg->flags & CAPDEC_FLAG_NO_UMMA);
+  h->umma_f32 = cfg->precision == CAPDEC_PREC_TF32;  // fp32 storage and step kernels, projections on tcgen05 kind::tf32
   h->use_graph = !(cfg->flags & CAPDEC_FLAG_NO_GRAPH);
   h->esz = h->bf16 ? 2 : 4;
   h->t_pad = cfg->max_len <= 64 ? 64 : 128;
@@ -836,16 +858,17 @@ extern "C" int capdec_set_weights(capdec_handle h, const capdec_weights* w, void
       TRY(copy_f32(h, s, lw.norm_w[j], lp.ln_w[j], kD));
       TRY(copy_f32(h, s, lw.norm_b[j], lp.ln_b[j], kD));
     }
-    if (h->use_umma) {
-      TRY(make_weight_maps(h, &lp.m_qkv, lp.w_qkv, 3 * kD, kD));
-      TRY(make_weight_maps(h, &lp.m_so, lp.w_so, kD, kD));
-      TRY(make_weight_maps(h, &lp.m_cq, lp.w_cq, kD, kD));
-      TRY(make_weight_maps(h, &lp.m_co, lp.w_co, kD, kD));
-      TRY(make_weight_maps(h, &lp.m_1, lp.w_1, F, kD));
-      TRY(make_weight_maps(h, &lp.m_2, lp.w_2, kD, F));
+    if (h->use_umma || h->umma_f32) {
+      const bool f32 = h->umma_f32;
+      TRY(make_weight_maps(h, &lp.m_qkv, lp.w_qkv, 3 * kD, kD, f32));
+      TRY(make_weight_maps(h, &lp.m_so, lp.w_so, kD, kD, f32));
+      TRY(make_weight_maps(h, &lp.m_cq, lp.w_cq, kD, kD, f32));
+      TRY(make_weight_maps(h, &lp.m_co, lp.w_co, kD, kD, f32));
+      TRY(make_weight_maps(h, &lp.m_1, lp.w_1, F, kD, f32));
+      TRY(make_weight_maps(h, &lp.m_2, lp.w_2, kD, F, f32));
     }
   }
-  if (h->use_umma) TRY(make_weight_maps(h, &h->m_ckv, h->w_ckv, L * 2 * kD, kD));
+  if (h->use_umma || h->umma_f32) TRY(make_weight_maps(h, &h->m_ckv, h->w_ckv, L * 2 * kD, kD, h->umma_f32));
   if (h->chain) {
     ChainPackSrc src{};
     src.n_layer = L;
@@ -904,6 +927,7 @@ static int prefill_chunk(capdec_handle h, cudaStream_t s, const float* memory_ch
   EpiCrossKV<bf16> e16{(bf16*)h->cross_kv, h->b_ckv, n_images, mem_len, img0};
   CUtensorMap tm_mem;
   if (h->use_umma) TRY(make_map(h, &tm_mem, (bf16*)h->mem_b + off, M, kD, kUmmaBM));
+  if (h->umma_f32) TRY(make_map(h, &tm_mem, memory_chunk, M, kD, kUmmaBM, true));  // TF32 route: straight from the fp32 memory
   set_tag(h, "prefill_gemm_cross_kv", gemm_bytes(M, N, kD, h->esz, h->esz, h->esz));
   return gemm(h, s, h->bf16 ? (const void*)((bf16*)h->mem_b + off) : (const void*)memory_chunk, &tm_mem, h->w_ckv, &h->m_ckv, M, N,
               kD, e32, e16, nullptr);
@@ -965,9 +989,9 @@ extern "C" int capdec_set_memory_projection(capdec_handle h, const float* proj_w
   }
   h->launches += h->launches_this_enqueue;
   TRY(pack_matrix(h, s, prod, h->w_ckv_f, N, in_dim, N));
-  if (h->use_umma) {
+  if (h->use_umma || h->umma_f32) {
     const int bns[3] = {32, 64, 128};
-    for (int i = 0; i < 3; ++i) TRY(make_map(h, &h->m_ckv_f.bn[i], h->w_ckv_f, N, in_dim, bns[i]));
+    for (int i = 0; i < 3; ++i) TRY(make_map(h, &h->m_ckv_f.bn[i], h->w_ckv_f, N, in_dim, bns[i], h->umma_f32));
   }
   return CAPDEC_OK;
 }
@@ -1000,7 +1024,7 @@ extern "C" int capdec_prefill_tokens(capdec_handle h, const float* tokens, int32
   EpiCrossKV<float> e32{(float*)h->cross_kv, h->b_ckv_f, n_images, mem_len};
   EpiCrossKV<bf16> e16{(bf16*)h->cross_kv, h->b_ckv_f, n_images, mem_len};
   CUtensorMap tm_tok;
-  if (h->use_umma) TRY(make_map(h, &tm_tok, h->tok_b, M, E, kUmmaBM));
+  if (h->use_umma || h->umma_f32) TRY(make_map(h, &tm_tok, h->tok_b, M, E, kUmmaBM, h->umma_f32));
   set_tag(h, "prefill_gemm_cross_kv", gemm_bytes(M, N, E, h->esz, h->esz, h->esz));
   TRY(gemm(h, s, h->tok_b, &tm_tok, h->w_ckv_f, &h->m_ckv_f, M, N, E, e32, e16, nullptr));
   return finish_prefill(h, n_images, mem_len);
@@ -1361,6 +1385,14 @@ static int enqueue_step(capdec_handle h, cudaStream_t s, int n_images, int S, in
 }
 
 static int ensure_activation_maps(capdec_handle h, int M) {
+  if (h->umma_f32) {  // TF32 route: the fp32 step buffers themselves are the TMA operands (x stands where xb does in bf16 mode)
+    if (h->maps_for_m == M) return 0;
+    TRY(make_map(h, &h->tm_xb, h->x, M, kD, kUmmaBM, true));
+    TRY(make_map(h, &h->tm_a, h->a, M, kD, kUmmaBM, true));
+    TRY(make_map(h, &h->tm_h, h->hbuf, M, h->cfg.d_ff, kUmmaBM, true));
+    h->maps_for_m = M;
+    return 0;
+  }
   if (!h->use_umma || h->maps_for_m == M) return 0;
   TRY(make_map(h, &h->tm_xb, h->xb, M, kD, kUmmaBM));
   TRY(make_map(h, &h->tm_a, h->a, M, kD, kUmmaBM));
@@ -1947,7 +1979,16 @@ extern "C" int capdec_debug_gemm(capdec_handle h, const float* a, const float* w
   CUDA_TRY(h, cudaSetDevice(h->device));
   h->launches_this_enqueue = 0;
   int rc = 0;
-  if (!h->bf16) {
+  if (h->umma_f32 && k % kUmmaBK == 0 && n % 128 == 0) {  // TF32 route: the caller's fp32 matrices are the TMA operands
+    CUtensorMap ta;
+    WeightMaps wm;
+    rc = make_map(h, &ta, a, m, k, kUmmaBM, true);
+    if (!rc) rc = make_weight_maps(h, &wm, w, n, k, true);
+    if (!rc) {
+      if (relu) { EpiLinear<float, true> e{c, bias, n}; rc = launch_umma<EpiLinear<float, true>, float>(h, s, ta, wm, m, n, k, e, nullptr); }
+      else { EpiLinear<float, false> e{c, bias, n}; rc = launch_umma<EpiLinear<float, false>, float>(h, s, ta, wm, m, n, k, e, nullptr); }
+    }
+  } else if (!h->bf16) {
     if (relu) { EpiLinear<float, true> e{c, bias, n}; rc = launch_simt<float, float, EpiLinear<float, true>>(h, s, a, k, w, k, m, n, k, e, nullptr); }
     else { EpiLinear<float, false> e{c, bias, n}; rc = launch_simt<float, float, EpiLinear<float, false>>(h, s, a, k, w, k, m, n, k, e, nullptr); }
   } else {

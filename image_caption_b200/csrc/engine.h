@@ -49,6 +49,7 @@ struct capdec_engine {
   int device = 0;
   bool bf16 = false;
   bool use_umma = false;
+  bool umma_f32 = false;   // CAPDEC_PREC_TF32: fp32 storage, projections on tcgen05 kind::tf32 (gemm_umma_kernel<.., float>)
   bool use_graph = true;
   size_t esz = 4;
   int t_pad = 64;

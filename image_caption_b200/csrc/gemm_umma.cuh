@@ -1,5 +1,5 @@
-// gemm_umma.cuh - tcgen05 GEMM, C[M,N] = A[M,K] * W[N,K]^T with bf16 operands and fp32
-// accumulation in TMEM.  Both operands are K-major (A = activations, W = nn.Linear weight),
+// gemm_umma.cuh - tcgen05 GEMM, C[M,N] = A[M,K] * W[N,K]^T with bf16 operands (kind::f16) or fp32 operands read as
+// TF32 (kind::tf32, the fp32-class throughput mode CAPDEC_PREC_TF32) and fp32 accumulation in TMEM.  Both operands are K-major (A = activations, W = nn.Linear weight),
 // staged by TMA into 128B-swizzled shared-memory tiles.
 //
 // One 128 x BLOCK_N output tile per CTA; 6 warps:
@@ -23,7 +23,8 @@ __host__ __device__ constexpr int umma_smem_bytes(int block_n, int stages) {
   return stages * umma_stage_bytes(block_n) + 1024 /*alignment slack*/ + 256 /*barriers*/;
 }
 
-template <int BLOCK_N, typename Epi>
+// In = operand element type in global / shared memory: bf16 (64 per 128-byte swizzle row) or float (32 per row)
+template <int BLOCK_N, typename Epi, typename In = bf16>
 __global__ void __launch_bounds__(kUmmaThreads, 2)
 gemm_umma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_w,
                  int M, int N, int K, int stages, Epi epi, const DecState* st) {
@@ -44,7 +45,8 @@ gemm_umma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int m0 = blockIdx.y * kUmmaBM, n0 = blockIdx.x * BLOCK_N;
-  const int num_kb = K / kUmmaBK;
+  constexpr int kBKe = 128 / (int)sizeof(In);  // elements per k-block (one 128-byte swizzle row)
+  const int num_kb = K / kBKe;
 
   // TMA / tcgen05 instructions are issued by the converged warp under elect.sync (see gemm_swap.cuh: under
   // `if (lane == 0)` every instruction is wrapped in a uniformity loop and costs ~150 cycles)
@@ -71,13 +73,14 @@ gemm_umma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
       ptx::mbar_wait(&empty[s], ph ^ 1);
       if (ptx::elect_one()) {
         ptx::mbar_expect_tx(&full[s], kABytes + kBBytes);
-        ptx::tma_load_2d(smem_a + (size_t)s * kABytes, &tm_a, &full[s], kb * kUmmaBK, m0);
-        ptx::tma_load_2d(smem_b + (size_t)s * kBBytes, &tm_w, &full[s], kb * kUmmaBK, n0);
+        ptx::tma_load_2d(smem_a + (size_t)s * kABytes, &tm_a, &full[s], kb * kBKe, m0);
+        ptx::tma_load_2d(smem_b + (size_t)s * kBBytes, &tm_w, &full[s], kb * kBKe, n0);
       }
       __syncwarp();
     }
   } else if (warp == 1) {
-    constexpr uint32_t idesc = ptx::umma_idesc_bf16(BLOCK_N);
+    constexpr bool kTf32 = sizeof(In) == 4;
+    constexpr uint32_t idesc = kTf32 ? ptx::umma_idesc_tf32(BLOCK_N) : ptx::umma_idesc_bf16(BLOCK_N);
     for (int kb = 0; kb < num_kb; ++kb) {
       const int s = kb % stages;
       const uint32_t ph = (kb / stages) & 1;
@@ -88,9 +91,13 @@ gemm_umma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
         const uint32_t b_addr = ptx::smem_u32(smem_b + (size_t)s * kBBytes);
 #pragma unroll
         for (int k = 0; k < kUmmaBK / kUmmaK; ++k) {
-          // advance inside the 128 B swizzle atom: 16 bf16 = 32 B per MMA
-          ptx::umma_f16(tmem_base, ptx::umma_desc_sw128(a_addr + k * kUmmaK * 2),
-                        ptx::umma_desc_sw128(b_addr + k * kUmmaK * 2), idesc, (kb | k) != 0 ? 1u : 0u);
+          // advance inside the 128 B swizzle atom: 16 bf16 = 8 tf32 = 32 B per MMA
+          if constexpr (kTf32)
+            ptx::umma_tf32(tmem_base, ptx::umma_desc_sw128(a_addr + k * 32), ptx::umma_desc_sw128(b_addr + k * 32), idesc,
+                           (kb | k) != 0 ? 1u : 0u);
+          else
+            ptx::umma_f16(tmem_base, ptx::umma_desc_sw128(a_addr + k * kUmmaK * 2),
+                          ptx::umma_desc_sw128(b_addr + k * kUmmaK * 2), idesc, (kb | k) != 0 ? 1u : 0u);
         }
         ptx::umma_commit(&empty[s]);                        // smem slot reusable once these MMAs retire
         if (kb == num_kb - 1) ptx::umma_commit(tmem_full);  // accumulator complete (same thread as its MMAs)

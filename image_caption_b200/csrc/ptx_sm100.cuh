@@ -149,6 +149,15 @@ __device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t desc_a, uint6
       ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// kind::tf32: fp32 words in shared memory, read as TF32 (10-bit mantissa), fp32 accumulate; K = 8 per instruction.
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
 // Same, with the shared-memory descriptors given as (low, high) words.  The high word of a 128B-swizzle K-major
 // descriptor is a constant and the low word is (address >> 4) | 1 << 16, so stepping through a tile is one integer
 // add per operand instead of rebuilding (shift, mask, or) the 64-bit descriptor in the issuing thread -- the issue
@@ -254,6 +263,11 @@ __device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
 // kind::f16 instruction descriptor: D=f32, A=B=bf16, both K-major, M=128, N=n.
 __device__ __host__ constexpr uint32_t umma_idesc_bf16(int n) {
   return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+}
+
+// kind::tf32 instruction descriptor: D=f32, A=B=tf32 (format 2), both K-major, M=128, N=n.
+__device__ __host__ constexpr uint32_t umma_idesc_tf32(int n) {
+  return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
 }
 
 }  // namespace ptx

@@ -76,8 +76,8 @@ class CaptionDecodeEngine:
         self.pe_rows = sd["pos_encoder.pe"].shape[1]
         if getattr(first, "norm_first", False):
             raise ValueError("only post-LN decoder layers (norm_first=False) are supported, as in the reference")
-        if precision not in ("bf16", "fp32"):
-            raise ValueError(f"precision must be 'bf16' or 'fp32', got {precision!r}")
+        if precision not in ("bf16", "fp32", "tf32"):
+            raise ValueError(f"precision must be 'bf16', 'fp32' or 'tf32', got {precision!r}")
         self.precision = precision
         if step_impl not in ("v1", "v2"):
             raise ValueError(f"step_impl must be 'v1' or 'v2', got {step_impl!r}")
@@ -96,7 +96,7 @@ class CaptionDecodeEngine:
                           d_ff=self.d_ff, pe_rows=self.pe_rows, max_mem=self._cap["max_mem"],
                           max_images=self._cap["max_images"], max_group=self._cap["max_group"],
                           max_len=self._cap["max_len"],
-                          precision=_lib.PREC_BF16 if self.precision == "bf16" else _lib.PREC_FP32,
+                          precision={"bf16": _lib.PREC_BF16, "fp32": _lib.PREC_FP32, "tf32": _lib.PREC_TF32}[self.precision],
                           flags=self._flags)
         h = C.c_void_p()
         rc = self._lib.capdec_create(C.byref(cfg), self.device.index or 0, C.byref(h))

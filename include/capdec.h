@@ -53,7 +53,9 @@ typedef enum {
 
 typedef enum {
   CAPDEC_PREC_FP32 = 0, /* fp32 weights / KV / CUDA-core GEMMs: the strict-parity mode         */
-  CAPDEC_PREC_BF16 = 1  /* bf16 weights / KV, tcgen05 GEMMs with fp32 accumulate; fp32 residual */
+  CAPDEC_PREC_BF16 = 1, /* bf16 weights / KV, tcgen05 GEMMs with fp32 accumulate; fp32 residual */
+  CAPDEC_PREC_TF32 = 2  /* fp32 weights / KV / step kernels as FP32, but every projection on tcgen05 kind::tf32 (operands read
+                           with a 10-bit mantissa, fp32 accumulate): the fp32-class throughput mode                       */
 } capdec_precision;
 
 typedef struct {
