@@ -683,7 +683,7 @@ static int create_impl(capdec_handle h) {
   TRY(dev_alloc(h, &h->cp, 1));
   CUDA_TRY(h, cudaMemset(h->st, 0, sizeof(DecState)));
   if (h->use_umma) CUDA_TRY(h, configure_umma_kernels());
-  if (h->umma_f32) CUDA_TRY(h, configure_umma_kernels_tf32());
+  if (h->umma_f32 || h->use_umma) CUDA_TRY(h, configure_umma_kernels_tf32());
   if (h->fast) {
     TRY(dev_alloc(h, &h->fc_wT, (size_t)kD * kVPad));
     h->part_rows = (int)std::min<size_t>(M, 512);
@@ -767,6 +767,8 @@ extern "C" int capdec_create(const capdec_config* cfg, int device, capdec_handle
   if (const char* e = getenv("CAPDEC_LN_TMA_STORE")) h->force_ln_tma_store = atoi(e) != 0 ? 1 : 0;
   if (const char* e = getenv("CAPDEC_NO_CROSS_STREAM")) h->no_cross_stream = atoi(e) != 0;
   if (const char* e = getenv("CAPDEC_NO_WS")) h->no_ws = atoi(e) != 0;
+  if (const char* e = getenv("CAPDEC_NO_TF32_HEAD")) h->no_tf32_head = atoi(e) != 0;
+  if (const char* e = getenv("CAPDEC_TF32_HEAD_MIN_M")) h->tf32_head_min_m = std::max(1, atoi(e));
   if (const char* e = getenv("CAPDEC_NO_WS_PREFILL")) h->no_ws_prefill = atoi(e) != 0;
   if (const char* e = getenv("CAPDEC_WS_MIN_CTAS")) h->ws_min_ctas = atoi(e);
   if (const char* e = getenv("CAPDEC_WS_MIN_M")) h->ws_min_m = std::max(128, atoi(e));
@@ -786,6 +788,7 @@ extern "C" int capdec_create(const capdec_config* cfg, int device, capdec_handle
     h->no_ws = true;
     h->force_bnb = 64;
     h->no_ffn2_split = true;
+    h->no_tf32_head = true;  // (the fused CUDA-core head at every batch size)
   }
   int rc = create_impl(h);
   if (rc) {
@@ -869,6 +872,7 @@ extern "C" int capdec_set_weights(capdec_handle h, const capdec_weights* w, void
     }
   }
   if (h->use_umma || h->umma_f32) TRY(make_weight_maps(h, &h->m_ckv, h->w_ckv, L * 2 * kD, kD, h->umma_f32));
+  if (h->fast || h->umma_f32) TRY(make_weight_maps(h, &h->m_fc, h->fc_w, kVPad, kD, true));  // vocabulary projection on kind::tf32
   if (h->chain) {
     ChainPackSrc src{};
     src.n_layer = L;
@@ -1031,6 +1035,17 @@ extern "C" int capdec_prefill_tokens(capdec_handle h, const float* tokens, int32
 }
 
 // ------------------------------------------------------------------ one decode step
+// Vocabulary projection logits[M, kVPad] = x[M,512] (fp32 residual stream) * fc_w^T + b.  fp32 engine: CUDA cores (strict
+// parity).  bf16 / tf32 engines with `tx` (fp32 TMA view of x): tcgen05 kind::tf32 - the operands keep 10 mantissa bits,
+// which moves a logit by ~5e-4 (K = 512, |w| ~ 0.05), far inside either mode's tolerance.
+static int vocab_logits(capdec_handle h, cudaStream_t s, const float* x, const CUtensorMap* tx, float* logits, int M, const DecState* st) {
+  EpiLinear<float, false> ev{logits, h->fc_b, kVPad};
+  set_tag(h, "gemm_vocab", gemm_bytes(M, kVPad, kD, 4, 4, 4));
+  if (tx != nullptr && (h->fast || h->umma_f32) && !h->no_tf32_head)
+    return launch_umma<EpiLinear<float, false>, float>(h, s, *tx, h->m_fc, M, kVPad, kD, ev, st);
+  return launch_simt<float, float, EpiLinear<float, false>>(h, s, x, kD, h->fc_w, kD, M, kVPad, kD, ev, st);
+}
+
 template <typename Elem>
 static int launch_self_attn(capdec_handle h, cudaStream_t s, int l, int M) {
   const Elem* kc = (const Elem*)h->self_k + (size_t)l * h->self_layer_elems;
@@ -1145,9 +1160,7 @@ static int enqueue_step_t(capdec_handle h, cudaStream_t s, int n_images, int S, 
     }
   }
   // vocabulary projection in fp32 on the fp32 residual stream, then pick/sample
-  EpiLinear<float, false> ev{h->logits, h->fc_b, kVPad};
-  set_tag(h, "gemm_vocab", gemm_bytes(M, kVPad, kD, 4, 4, 4));
-  TRY((launch_simt<float, float, EpiLinear<float, false>>(h, s, h->x, kD, h->fc_w, kD, M, kVPad, kD, ev, st)));
+  TRY(vocab_logits(h, s, h->x, h->umma_f32 ? &h->tm_xb : nullptr, h->logits, M, st));  // (tf32 mode: tm_xb views x)
   if (h->beam_mode) {
     set_tag(h, "beam_head", (double)M * (kVPad * 4 + 8 + 4 + 2 * h->t_pad * 4));
     ProfScope ps(h, s);
@@ -1220,13 +1233,31 @@ static int fast_head(capdec_handle h, cudaStream_t s, int n_images, int group) {
   cudaError_t e;
   if (h->beam_mode) {
     // beam search: logits to memory (fp32, as in the v1 step), per-image top-k head, then the next step's embedding
-    EpiLinear<float, false> ev{h->logits, h->fc_b, kVPad};
-    set_tag(h, "gemm_vocab", gemm_bytes(M, kVPad, kD, 4, 4, 4));
-    TRY((launch_simt<float, float, EpiLinear<float, false>>(h, s, h->x, kD, h->fc_w, kD, M, kVPad, kD, ev, st)));
+    TRY(vocab_logits(h, s, h->x, &h->tm_x32, h->logits, M, st));
     {
       set_tag(h, "beam_head", (double)M * (kVPad * 4 + 8 + 4 + 2 * h->t_pad * 4));
       ProfScope ps(h, s);
       beam_head_kernel<<<n_images, group * 32, 0, s>>>(h->st, h->cp, h->beam, h->logits, n_images, group, h->cfg.vocab, h->t_pad, h->beam_grid_rule);
+    }
+    CUDA_TRY(h, cudaGetLastError());
+    h->launches_this_enqueue++;
+    {
+      set_tag(h, "embed_pe", (double)M * kD * (4 + 4 + 2));
+      ProfScope ps(h, s);
+      embed_pe_kernel<bf16><<<(M * (kD / 4) + 255) / 256, 256, 0, s>>>(h->st, h->cp, h->emb, h->pe, h->x, (bf16*)h->xb, M);
+    }
+    CUDA_TRY(h, cudaGetLastError());
+    h->launches_this_enqueue++;
+    return 0;
+  }
+  if (M >= h->tf32_head_min_m && !h->no_tf32_head) {
+    // large batches: logits on tcgen05 kind::tf32, then the v1 head (pick / sample / bookkeeping) and the next step's
+    // embedding - three short launches instead of the fused CUDA-core head, whose 0.4 GFLOP of fp32 FMAs take ~33 us
+    TRY(vocab_logits(h, s, h->x, &h->tm_x32, h->logits, M, st));
+    {
+      set_tag(h, "head", (double)M * (kVPad * 4 + 8 + 4));
+      ProfScope ps(h, s);
+      head_kernel<<<(M + 3) / 4, 128, 0, s>>>(h->st, h->cp, h->logits, h->fin, M, h->cfg.vocab);
     }
     CUDA_TRY(h, cudaGetLastError());
     h->launches_this_enqueue++;
@@ -1410,6 +1441,7 @@ static int ensure_activation_maps(capdec_handle h, int M) {
     // measured (B200): staging + bulk stores win for 32-row tiles (cfg2 372.6 -> 368.6 us/step), per-thread stores
     // for wider ones (cfg3 974 -> 958, cfg5 627 -> 620): the 96 KB tile takes ~3.3k cycles to drain
     h->ln_tma_store = h->force_ln_tma_store >= 0 ? h->force_ln_tma_store : (h->bnb == 32 ? 1 : 0);
+    TRY(make_map(h, &h->tm_x32, h->x, M, kD, kUmmaBM, true));  // fp32 view of the residual stream: the kind::tf32 vocabulary projection
     TRY(make_store_map(h, &h->ts_x, h->x, M, kD, h->bnb, true));
     TRY(make_store_map(h, &h->ts_xb, h->xb, M, kD, h->bnb, false));
     if (M >= h->ws_min_m) {  // output views of the weight-stationary GEMM's bulk stores; its X tiles are always 128 rows
@@ -1682,9 +1714,9 @@ static int full_pass_chunk(capdec_handle h, cudaStream_t s, const capdec_forward
     }
   }
   // vocabulary head on the fp32 residual stream (as the step head), then log-softmax + gather
-  EpiLinear<float, false> ev{h->logits, h->fc_b, kVPad};
-  set_tag(h, "full_gemm_vocab", gemm_bytes(Mc, kVPad, kD, 4, 4, 4));
-  TRY((launch_simt<float, float, EpiLinear<float, false>>(h, s, h->x, kD, h->fc_w, kD, Mc, kVPad, kD, ev, nullptr)));
+  CUtensorMap tm_x32;
+  TRY(make_map(h, &tm_x32, h->x, Mc, kD, kUmmaBM, true));
+  TRY(vocab_logits(h, s, h->x, &tm_x32, h->logits, Mc, nullptr));
   {
     set_tag(h, "full_logp", (double)Mc * (kVPad * 4 + 8 + 4) + (a->logits_out ? (double)Mc * h->cfg.vocab * 4 : 0.0));
     ProfScope ps(h, s);

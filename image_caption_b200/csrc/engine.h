@@ -99,6 +99,10 @@ struct capdec_engine {
   int force_ln_tma_store = -1;     // env CAPDEC_LN_TMA_STORE
   int force_head_rw = 0;           // env CAPDEC_HEAD_RW: rows per warp of the vocabulary head (1, 2, 4, 6)
   int ws_dbg = 0;
+  capdec::WeightMaps m_fc;         // fc_w [128, 512] fp32 as a kind::tf32 operand (vocabulary projection of large batches)
+  CUtensorMap tm_x32;              // fp32 view of x [M,512], box = 32 x 128
+  bool no_tf32_head = false;       // env CAPDEC_NO_TF32_HEAD: vocabulary projection on CUDA cores everywhere
+  int tf32_head_min_m = 2048;      // env CAPDEC_TF32_HEAD_MIN_M (B200: cfg3, 3072 rows, 807 -> 800 us/step; level at 1024 rows)
   bool no_ws_prefill = false;      // env CAPDEC_NO_WS_PREFILL: prefill through the one-tile-per-CTA GEMM (gemm_umma.cuh)
   int ws_min_ctas = 96;
   int ws_min_m = 512;             // smallest batch that takes the weight-stationary GEMM (env CAPDEC_WS_MIN_M)
