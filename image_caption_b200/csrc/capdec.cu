@@ -310,7 +310,9 @@ static int swap_stages(capdec_handle h, int bnb, int K, int ctas, bool ln = fals
 // every 128-row LayerNorm GEMM of round 1-2 (depth 5) carried the race at low odds.
 static int even_ring_for_two_issuers(int stages, int num_kb, int issuers, int bnb, int ksplit = 1) {
   if (issuers != 2 || stages >= num_kb || (stages & 1) == 0) return stages;
-  if (stages + 1 <= num_kb && swap_smem_bytes(bnb, stages + 1, ksplit) <= kMaxDynSmem && stages < 4) return stages + 1;
+  // one deeper when it fits (B200, 128-row LayerNorm tiles: depth 6 beats 4 by 4 % over the ~400-CTA launches of the
+  // full-sequence pass and is level at cfg3's 96), else one shallower
+  if (stages + 1 <= num_kb && swap_smem_bytes(bnb, stages + 1, ksplit) <= kMaxDynSmem) return stages + 1;
   return stages > 2 ? stages - 1 : stages + 1;
 }
 
