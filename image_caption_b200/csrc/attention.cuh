@@ -103,7 +103,7 @@ __device__ __forceinline__ uint4 ld_stream16(const void* p) {
   asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
   return r;
 }
-template <bool kAnc>  // kAnc: beam search, rows are read through the ancestry table (a separate instantiation: the
+template <bool kAnc, int kIts = 8>  // kIts: positions per chunk / 4 (registers: 8 per it); kAnc: beam search, rows are read through the ancestry table (a separate instantiation: the
                       // indirection costs ~50 registers, which the plain rollout's occupancy should not pay)
 __global__ void __launch_bounds__(kAttnWarps * 32)
 self_attn_stream_kernel(const bf16* __restrict__ q, const bf16* __restrict__ kc, const bf16* __restrict__ vc,
@@ -137,10 +137,10 @@ self_attn_stream_kernel(const bf16* __restrict__ q, const bf16* __restrict__ kc,
   }
   float m_run = -INFINITY, l_run = 0.f;
   float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-  for (int p0 = 0; p0 <= n; p0 += 32) {
-    uint4 kr[8], vr[8];
+  for (int p0 = 0; p0 <= n; p0 += 4 * kIts) {
+    uint4 kr[kIts], vr[kIts];
 #pragma unroll
-    for (int it = 0; it < 8; ++it) {
+    for (int it = 0; it < kIts; ++it) {
       const int pos = p0 + it * 4 + g;
       if (pos <= n) {
         const long long sh = row_shift(pos);
@@ -151,10 +151,10 @@ self_attn_stream_kernel(const bf16* __restrict__ q, const bf16* __restrict__ kc,
         vr[it] = make_uint4(0u, 0u, 0u, 0u);
       }
     }
-    float s[8];
+    float s[kIts];
     float mc = -INFINITY;
 #pragma unroll
-    for (int it = 0; it < 8; ++it) {
+    for (int it = 0; it < kIts; ++it) {
       const uint32_t w[4] = {kr[it].x, kr[it].y, kr[it].z, kr[it].w};
       float d = 0.f;
 #pragma unroll
@@ -176,7 +176,7 @@ self_attn_stream_kernel(const bf16* __restrict__ q, const bf16* __restrict__ kc,
 #pragma unroll
     for (int i = 0; i < 8; ++i) acc[i] *= corr;
 #pragma unroll
-    for (int it = 0; it < 8; ++it) {
+    for (int it = 0; it < kIts; ++it) {
       const float pr = __expf(s[it] - m_new);      // 0 for masked positions
       l_run += pr;
       const uint32_t w[4] = {vr[it].x, vr[it].y, vr[it].z, vr[it].w};

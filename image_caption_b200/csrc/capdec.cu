@@ -769,6 +769,7 @@ extern "C" int capdec_create(const capdec_config* cfg, int device, capdec_handle
   if (const char* e = getenv("CAPDEC_LN_TMA_STORE")) h->force_ln_tma_store = atoi(e) != 0 ? 1 : 0;
   if (const char* e = getenv("CAPDEC_NO_CROSS_STREAM")) h->no_cross_stream = atoi(e) != 0;
   if (const char* e = getenv("CAPDEC_NO_WS")) h->no_ws = atoi(e) != 0;
+  if (const char* e = getenv("CAPDEC_SELF_ATTN_ITS")) h->self_attn_its = atoi(e);
   if (const char* e = getenv("CAPDEC_NO_TF32_HEAD")) h->no_tf32_head = atoi(e) != 0;
   if (const char* e = getenv("CAPDEC_TF32_HEAD_MIN_M")) h->tf32_head_min_m = std::max(1, atoi(e));
   if (const char* e = getenv("CAPDEC_NO_WS_PREFILL")) h->no_ws_prefill = atoi(e) != 0;
@@ -1190,6 +1191,9 @@ static int fast_self_attn(capdec_handle h, cudaStream_t s, int l, int M) {
     if (h->beam_mode)
       e = launch_ex(self_attn_stream_kernel<true>, dim3(blocks), dim3(kAttnWarps * 32), 0, s, 1, h->use_pdl, (const bf16*)h->q,
                     (const bf16*)kc, (const bf16*)vc, (bf16*)h->a, M, h->t_pad, st, (const int*)h->beam.anc);
+    else if (h->self_attn_its == 4)
+      e = launch_ex(self_attn_stream_kernel<false, 4>, dim3(blocks), dim3(kAttnWarps * 32), 0, s, 1, h->use_pdl, (const bf16*)h->q,
+                    (const bf16*)kc, (const bf16*)vc, (bf16*)h->a, M, h->t_pad, st, (const int*)nullptr);
     else
       e = launch_ex(self_attn_stream_kernel<false>, dim3(blocks), dim3(kAttnWarps * 32), 0, s, 1, h->use_pdl, (const bf16*)h->q,
                     (const bf16*)kc, (const bf16*)vc, (bf16*)h->a, M, h->t_pad, st, (const int*)nullptr);

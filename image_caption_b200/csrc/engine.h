@@ -101,6 +101,8 @@ struct capdec_engine {
   int ws_dbg = 0;
   capdec::WeightMaps m_fc;         // fc_w [128, 512] fp32 as a kind::tf32 operand (vocabulary projection of large batches)
   CUtensorMap tm_x32;              // fp32 view of x [M,512], box = 32 x 128
+  int self_attn_its = 4;           // env CAPDEC_SELF_ATTN_ITS: cached positions per chunk / 4 of the streaming self-attention: 4 (16
+                                   // positions, 56 registers, 9 CTAs per SM) or 8 (32 positions, 72 registers, 7 CTAs per SM)
   bool no_tf32_head = false;       // env CAPDEC_NO_TF32_HEAD: vocabulary projection on CUDA cores everywhere
   int tf32_head_min_m = 1024;      // env CAPDEC_TF32_HEAD_MIN_M (B200: cfg3, 3072 rows, 807 -> 800 us/step; level at 1024 rows; 1024 keeps the 1536-row shards of cfg4 at N = 2 on the route of the unsharded batch)
   bool no_ws_prefill = false;      // env CAPDEC_NO_WS_PREFILL: prefill through the one-tile-per-CTA GEMM (gemm_umma.cuh)

@@ -1,5 +1,2 @@
-python tools/step_time.py cfg3 --variants v2 --reps 5 2>&1 | tail -1
-python tools/step_time.py cfg5 --variants v2 --reps 5 2>&1 | tail -1
-python tools/step_time.py cfg2 --variants v2 --reps 5 2>&1 | tail -1
-python tools/full_time.py cfg3 2>&1 | grep "mode=full"
-python -m pytest tests/test_gpu_parity.py -m gpu -x -q -k "many_row or full_size or split_k or tile_widths" 2>&1 | tail -2
+for wl in cfg3 cfg5; do for v in 8 4 2 8 4; do echo "== $wl SELF_ATTN_ITS=$v"; CAPDEC_SELF_ATTN_ITS=$v python tools/step_time.py $wl --variants v2 --reps 5 2>&1 | tail -1; done; done
+CAPDEC_SELF_ATTN_ITS=4 python -m pytest tests/test_gpu_parity.py -m gpu -x -q -k "full_size or greedy_rollout or grouped" 2>&1 | tail -2
