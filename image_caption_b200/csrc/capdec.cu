@@ -687,6 +687,18 @@ static int create_impl(capdec_handle h) {
   if (h->use_umma) CUDA_TRY(h, configure_umma_kernels());
   if (h->umma_f32 || h->use_umma) CUDA_TRY(h, configure_umma_kernels_tf32());
   if (h->fast) {
+    {  // does dynamic shared memory start on a 1 KB boundary?  (lets the cross-attention drop its alignment slack)
+      unsigned* d = nullptr;
+      unsigned off = 1;
+      if (cudaMalloc(&d, sizeof(unsigned)) == cudaSuccess) {
+        smem_base_probe_kernel<<<1, 32, 4096>>>(d);
+        if (cudaMemcpy(&off, d, sizeof off, cudaMemcpyDeviceToHost) != cudaSuccess) off = 1;
+        cudaFree(d);
+      }
+      cudaGetLastError();
+      h->dyn_smem_aligned = off == 0;
+    }
+    if (const char* e = getenv("CAPDEC_NO_CA_COMPACT")) h->no_ca_compact = atoi(e) != 0;
     TRY(dev_alloc(h, &h->fc_wT, (size_t)kD * kVPad));
     h->part_rows = (int)std::min<size_t>(M, 512);
     TRY(dev_alloc(h, &h->part, (size_t)4 * h->part_rows * kD));
@@ -1209,6 +1221,8 @@ static int fast_cross_attn(capdec_handle h, cudaStream_t s, int l, int n_images,
   set_tag(h, "cross_attn", (double)n_images * S * 2 * kD * 2 + (double)M * kD * 2 * 2);
   const int KT = ca_key_rows(S) / 16;
   const int per_warp = (KT + 3) / 4;
+  const int ca_compact = (!h->no_ca_compact && ca_compact_ok(S, group)) ? 1 : 0;
+  const size_t ca_bytes = ca_compact ? ca_smem_bytes_compact(S, h->dyn_smem_aligned) : ca_smem_bytes(S, group);
   cudaError_t e;
   {
     ProfScope ps(h, s);
@@ -1218,14 +1232,14 @@ static int fast_cross_attn(capdec_handle h, cudaStream_t s, int l, int n_images,
       e = launch_ex(cross_attn_stream_kernel, dim3((n_images * kH + kAttnWarps - 1) / kAttnWarps), dim3(kAttnWarps * 32), 0,
                     s, 1, h->use_pdl, (const bf16*)h->q, (const bf16*)h->cross_kv, (bf16*)h->a, l, n_images, S, st);
     else if (per_warp <= 1)
-      e = launch_ex(cross_attn_tma_kernel<1>, dim3(n_images * kH), dim3(kCaThreads), ca_smem_bytes(S, group), s, 1, h->use_pdl,
-                    h->tm_ckv, (const bf16*)h->q, (bf16*)h->a, l, n_images, group, S, st);
+      e = launch_ex(cross_attn_tma_kernel<1>, dim3(n_images * kH), dim3(kCaThreads), ca_bytes, s, 1, h->use_pdl,
+                    h->tm_ckv, (const bf16*)h->q, (bf16*)h->a, l, n_images, group, S, st, ca_compact);
     else if (per_warp <= 2)
-      e = launch_ex(cross_attn_tma_kernel<2>, dim3(n_images * kH), dim3(kCaThreads), ca_smem_bytes(S, group), s, 1, h->use_pdl,
-                    h->tm_ckv, (const bf16*)h->q, (bf16*)h->a, l, n_images, group, S, st);
+      e = launch_ex(cross_attn_tma_kernel<2>, dim3(n_images * kH), dim3(kCaThreads), ca_bytes, s, 1, h->use_pdl,
+                    h->tm_ckv, (const bf16*)h->q, (bf16*)h->a, l, n_images, group, S, st, ca_compact);
     else
-      e = launch_ex(cross_attn_tma_kernel<4>, dim3(n_images * kH), dim3(kCaThreads), ca_smem_bytes(S, group), s, 1, h->use_pdl,
-                    h->tm_ckv, (const bf16*)h->q, (bf16*)h->a, l, n_images, group, S, st);
+      e = launch_ex(cross_attn_tma_kernel<4>, dim3(n_images * kH), dim3(kCaThreads), ca_bytes, s, 1, h->use_pdl,
+                    h->tm_ckv, (const bf16*)h->q, (bf16*)h->a, l, n_images, group, S, st, ca_compact);
   }
   CUDA_TRY(h, e);
   h->launches_this_enqueue++;

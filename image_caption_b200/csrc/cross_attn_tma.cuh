@@ -26,6 +26,19 @@ __host__ __device__ constexpr int ca_q_rows(int group) { return group < 16 ? gro
 __host__ __device__ constexpr int ca_smem_bytes(int S, int group) {
   return 1024 + 2 * ca_key_rows(S) * 128 + 16 * kCaQStride * 2 + 4 * ca_q_rows(group) * kCaOStride * 4 + 4 * 16 * 2 * 4 + 64;
 }
+// Compact form: the warps' partial outputs alias the K tile (dead once every warp has its scores; one query tile per
+// item, the K tile large enough) and, when the dynamic shared memory is known to start 1 KB-aligned (probed once per
+// process, capdec.cu), no alignment slack: 56.1 KB instead of 63.7 KB at S = 196, so four CTAs share an SM, not three.
+__host__ __device__ constexpr bool ca_compact_ok(int S, int group) {
+  return group <= 16 && ca_key_rows(S) * 128 >= 4 * ca_q_rows(group) * kCaOStride * 4;
+}
+__host__ __device__ constexpr int ca_smem_bytes_compact(int S, bool aligned) {
+  return (aligned ? 0 : 1024) + 2 * ca_key_rows(S) * 128 + 16 * kCaQStride * 2 + 4 * 16 * 2 * 4 + 64;
+}
+__global__ void smem_base_probe_kernel(unsigned* out) {
+  extern __shared__ uint8_t probe_raw[];
+  if (threadIdx.x == 0) *out = (unsigned)(reinterpret_cast<uintptr_t>(probe_raw) & 1023u);
+}
 
 namespace ptx {
 __device__ __forceinline__ void ldsm_x4(uint32_t addr, uint32_t (&r)[4]) {
@@ -49,7 +62,7 @@ __device__ __forceinline__ void mma_bf16_16816(float (&d)[4], const uint32_t (&a
 template <int kKT>
 __global__ void __launch_bounds__(kCaThreads)
 cross_attn_tma_kernel(const __grid_constant__ CUtensorMap tm_kv, const bf16* __restrict__ q, bf16* __restrict__ out,
-                      int layer, int n_images, int group, int S, const DecState* st) {
+                      int layer, int n_images, int group, int S, const DecState* st, int compact) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   const int SB = ca_key_rows(S);
@@ -57,8 +70,9 @@ cross_attn_tma_kernel(const __grid_constant__ CUtensorMap tm_kv, const bf16* __r
   uint8_t* v_s = smem + (size_t)SB * 128;
   bf16* q_s = reinterpret_cast<bf16*>(v_s + (size_t)SB * 128);
   const int GP = ca_q_rows(group);
-  float* o_part = reinterpret_cast<float*>(q_s + 16 * kCaQStride);  // [4][GP][kCaOStride]
-  float* ml_part = o_part + 4 * GP * kCaOStride;                    // [4][16][2]
+  // [4][GP][kCaOStride]; compact: over the K tile, written only after the block-wide barrier that follows the scores
+  float* o_part = compact ? reinterpret_cast<float*>(k_s) : reinterpret_cast<float*>(q_s + 16 * kCaQStride);
+  float* ml_part = compact ? reinterpret_cast<float*>(q_s + 16 * kCaQStride) : o_part + 4 * GP * kCaOStride;  // [4][16][2]
   uint64_t* bar = reinterpret_cast<uint64_t*>(ml_part + 4 * 16 * 2);  // [2]: K landed, V landed
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -208,6 +222,7 @@ cross_attn_tma_kernel(const __grid_constant__ CUtensorMap tm_kv, const bf16* __r
     l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
 
     // ---- merge the 4 warps
+    if (compact) __syncthreads();  // every warp has left the K tile
     float* op = o_part + (size_t)warp * GP * kCaOStride;
 #pragma unroll
     for (int d = 0; d < 8; ++d) {

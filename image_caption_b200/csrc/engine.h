@@ -111,6 +111,8 @@ struct capdec_engine {
   CUtensorMap tx_ws;               // xb as [M,512], box = 64 x 128 rows
   bool no_ws = false;              // env CAPDEC_NO_WS: never use the weight-stationary persistent GEMM (gemm_ws.cuh)
   bool no_whole_k = false;         // env CAPDEC_NO_WHOLE_K: one TMA copy per k-block instead of whole-K copies
+  bool dyn_smem_aligned = false;   // dynamic shared memory starts 1 KB-aligned on this device (probed at create)
+  bool no_ca_compact = false;      // env CAPDEC_NO_CA_COMPACT: cross-attention with separate merge scratch and alignment slack (3 CTAs per SM at S = 196)
   bool no_cross_stream = false;    // env CAPDEC_NO_CROSS_STREAM: keep the tensor-core cross-attention for group == 1
   CUtensorMap tm_ckv;              // whole cross cache as [rows,64], box = 64 x ca_key_rows(S)
   float* fc_wT = nullptr;          // [512][kVPad] fp32: fc_out.weight transposed + padded
