@@ -1271,20 +1271,13 @@ static int fast_head(capdec_handle h, cudaStream_t s, int n_images, int group) {
     return 0;
   }
   if (M >= h->tf32_head_min_m && !h->no_tf32_head) {
-    // large batches: logits on tcgen05 kind::tf32, then the v1 head (pick / sample / bookkeeping) and the next step's
-    // embedding - three short launches instead of the fused CUDA-core head, whose 0.4 GFLOP of fp32 FMAs take ~33 us
+    // large batches: logits on tcgen05 kind::tf32, then the v1 head (pick / sample / bookkeeping + the next step's
+    // embedding) - two short launches instead of the fused CUDA-core head, whose 0.4 GFLOP of fp32 FMAs take ~33 us
     TRY(vocab_logits(h, s, h->x, &h->tm_x32, h->logits, M, st));
     {
-      set_tag(h, "head", (double)M * (kVPad * 4 + 8 + 4));
+      set_tag(h, "head", (double)M * (kVPad * 4 + 8 + 4) + (double)M * kD * (4 + 4 + 2));
       ProfScope ps(h, s);
-      head_kernel<<<(M + 3) / 4, 128, 0, s>>>(h->st, h->cp, h->logits, h->fin, M, h->cfg.vocab);
-    }
-    CUDA_TRY(h, cudaGetLastError());
-    h->launches_this_enqueue++;
-    {
-      set_tag(h, "embed_pe", (double)M * kD * (4 + 4 + 2));
-      ProfScope ps(h, s);
-      embed_pe_kernel<bf16><<<(M * (kD / 4) + 255) / 256, 256, 0, s>>>(h->st, h->cp, h->emb, h->pe, h->x, (bf16*)h->xb, M);
+      head_kernel<<<(M + 3) / 4, 128, 0, s>>>(h->st, h->cp, h->logits, h->fin, M, h->cfg.vocab, h->emb, h->pe, h->x, (bf16*)h->xb);
     }
     CUDA_TRY(h, cudaGetLastError());
     h->launches_this_enqueue++;

@@ -180,7 +180,9 @@ __device__ __forceinline__ void load_logits_row(const float* __restrict__ row, i
 
 // logits: [M, kVPad] fp32 (bias already added).  One warp per sequence.
 __global__ void __launch_bounds__(128)
-head_kernel(DecState* st, const CallParams* cp, const float* __restrict__ logits, unsigned char* fin, int M, int V) {
+head_kernel(DecState* st, const CallParams* cp, const float* __restrict__ logits, unsigned char* fin, int M, int V,
+            const float* __restrict__ emb = nullptr, const float* __restrict__ pe = nullptr, float* __restrict__ x = nullptr,
+            bf16* __restrict__ xb = nullptr) {
   if (st->done) return;
   const CallParams p = *cp;
   const int n = st->step;
@@ -209,6 +211,22 @@ head_kernel(DecState* st, const CallParams* cp, const float* __restrict__ logits
         if (was || ended) atomicAdd(&st->cnt_finished, 1);
       } else if (ended) {
         atomicAdd(&st->cnt_end_now, 1);
+      }
+    }
+    // with `emb`: the embedding of the token just picked = input of the next step (as vocab_head_kernel does; the
+    // bf16 step's kind::tf32 vocabulary route), so that no separate embed_pe launch follows
+    if (emb != nullptr && n + 1 < p.max_len - 1) {
+      const float sc = 22.627416997969522f;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int c = i * 128 + lane * 4;
+        const float4 e4 = __ldg(reinterpret_cast<const float4*>(emb + (size_t)tok * kD + c));
+        const float4 p4 = __ldg(reinterpret_cast<const float4*>(pe + (size_t)(n + 1) * kD + c));
+        float4 o;
+        o.x = __fadd_rn(__fmul_rn(e4.x, sc), p4.x); o.y = __fadd_rn(__fmul_rn(e4.y, sc), p4.y);
+        o.z = __fadd_rn(__fmul_rn(e4.z, sc), p4.z); o.w = __fadd_rn(__fmul_rn(e4.w, sc), p4.w);
+        *reinterpret_cast<float4*>(x + (size_t)m * kD + c) = o;
+        store4(xb + (size_t)m * kD + c, o.x, o.y, o.z, o.w);
       }
     }
   }
