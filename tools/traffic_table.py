@@ -5,12 +5,13 @@ event-pair timings (`ncu_us_per_launch`, `roofline.traffic`).
     python tools/traffic_table.py"""
 import csv, json, os
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-out = {"_source": "profiles/r02_ncu_full_cfg{2,3}.csv: ncu --set full --clock-control none on `bench.py --workload W --steps 1 "
+out = {"_source": "profiles/r02_ncu_full_cfg2.csv, r02_ncu_full_cfg3_final.csv: ncu --set full --clock-control none on `bench.py --workload W --steps 1 "
                   "--warmup 3 --no-cpu --no-sub`, launches of the LAST decode step of a rollout (cached length 48-49: the "
                   "self-attention figure is the largest of the rollout); median over the captured launches of each kernel"}
 unit = lambda s: 1e6 if "Mbyte" in s else (1e3 if "Kbyte" in s else 1)
 for w in ("cfg2", "cfg3"):
-    rows = list(csv.reader(open(os.path.join(ROOT, "profiles", f"r02_ncu_full_{w}.csv"))))
+    final = os.path.join(ROOT, "profiles", f"r02_ncu_full_{w}_final.csv")  # (cfg3: re-captured after the last kernel changes)
+    rows = list(csv.reader(open(final if os.path.exists(final) else os.path.join(ROOT, "profiles", f"r02_ncu_full_{w}.csv"))))
     h = rows[0]
     it = [i for i, x in enumerate(h) if x.startswith("gpu__time_duration")][0]
     ir = [i for i, x in enumerate(h) if x.startswith("dram__bytes_read")][0]
@@ -26,6 +27,8 @@ for w in ("cfg2", "cfg3"):
         elif "SwapLinear<float" in n: t = "gemm_ffn2_part"
         elif "sum_ln" in n: t = "sum_ln"
         elif "vocab_head" in n: t = "vocab_head"
+        elif "gemm_umma_kernel" in n and "float" in n: t = "gemm_vocab"
+        elif n.startswith("head_kernel"): t = "head"
         elif "chain_kernel" in n: t = {"0": "chain_in_proj", "1": "chain_attn_out", "2": "chain_ffn"}[n.split(",")[-1].strip(" >")]
         elif "SwapNoLN" in n:  # order inside a layer: self-out, cross-out, FFN2
             t = "gemm_self_out_ln" if prev == "self_attn" else ("gemm_cross_out_ln" if prev == "cross_attn" else "gemm_ffn2_ln")
