@@ -1,3 +1,8 @@
-python -m pytest tests/test_gpu_parity.py -m gpu -x -q -k "tile_widths or full_size or many_row or split_k or full_sequence" 2>&1 | tail -3
-for v in 1 0 1 0; do echo "== cfg3 NO_PAIR_K=$v"; CAPDEC_NO_PAIR_K=$v python tools/step_time.py cfg3 --variants v2 --reps 5 2>&1 | tail -1; done
-for v in 1 0; do echo "== full cfg3 NO_PAIR_K=$v"; CAPDEC_NO_PAIR_K=$v python tools/full_time.py cfg3 2>&1 | grep "mode=full"; done
+run() { n=$1; shift; echo "== images=$n $*"; env "$@" python tools/step_time.py cfg3 --variants v2 --reps 5 --images $n 2>&1 | tail -1; }
+run 128 A=1
+run 128 CAPDEC_BNB=64
+run 128 CAPDEC_CHAIN=2
+run 128 CAPDEC_WS_MIN_CTAS=64
+run 256 A=1
+run 256 CAPDEC_BNB=128
+run 256 CAPDEC_BNB=32
