@@ -273,7 +273,8 @@ class CaptionDecodeEngine:
                 or not memory.is_contiguous():
             raise ValueError(f"memory must be a contiguous CPU float32 (B, S, {self.d_model}) tensor")
         self._ensure_capacity(memory.shape[0], 1, memory.shape[1], 2)
-        self.sync_weights()
+        if self._weights_sig is None:  # (a handle without weights refuses prefill-type calls; the consuming call re-checks them)
+            self.sync_weights()
         _lib.check(self._h, self._lib.capdec_prefetch_host(self._h, memory.data_ptr(), memory.shape[0], memory.shape[1]))
         self._keep_prefetch = getattr(self, "_keep_prefetch", [])[-1:] + [memory]
 
