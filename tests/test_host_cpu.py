@@ -36,6 +36,31 @@ def test_library_exports_every_declared_symbol():
     assert lib.capdec_abi_version() == _lib.ABI_VERSION
 
 
+def test_binding_constants_match_the_header():
+    """The ctypes stub's enums and struct layouts restate include/capdec.h: precision / flag values, and every
+    `typedef struct` argument block has a ctypes mirror with the same field names in the same order."""
+    import re
+    from image_caption_b200 import _lib
+    hdr = open(os.path.join(ROOT, "include", "capdec.h")).read()
+    vals = dict((k, int(v)) for k, v in re.findall(r"\b(CAPDEC_[A-Z0-9_]+)\s*=\s*(-?\d+)", hdr))
+    vals.update((k, int(v)) for k, v in re.findall(r"#define\s+(CAPDEC_[A-Z0-9_]+)\s+(\d+)\b", hdr))
+    assert (vals["CAPDEC_PREC_FP32"], vals["CAPDEC_PREC_BF16"], vals["CAPDEC_PREC_TF32"]) == (_lib.PREC_FP32, _lib.PREC_BF16, _lib.PREC_TF32)
+    assert vals["CAPDEC_ABI_VERSION"] == _lib.ABI_VERSION
+    assert vals["CAPDEC_FLAG_BATCH_INVARIANT"] == _lib.FLAG_BATCH_INVARIANT
+    for cname, ctype in (("capdec_forward_args", _lib.ForwardArgs), ("capdec_decode_args", _lib.DecodeArgs),
+                         ("capdec_beam_args", _lib.BeamArgs)):
+        end = hdr.index("} " + cname + ";")
+        body = hdr[hdr.rindex("{", 0, end) + 1:end]
+        body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
+        names = []
+        for decl in body.split(";"):
+            if decl.strip():  # "type a, b, c" / "type* a" / "type a[3]"
+                first, *rest = decl.split(",")
+                names.append(re.search(r"(\w+)\s*(?:\[\w+\])?\s*$", first).group(1))
+                names += [re.search(r"(\w+)", r).group(1) for r in rest]
+        assert names == [f[0] for f in ctype._fields_], (cname, names)
+
+
 def test_create_without_gpu_fails_loudly():
     if torch.cuda.is_available():
         pytest.skip("GPU present")
